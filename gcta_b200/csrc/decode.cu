@@ -1,0 +1,381 @@
+// decode.cu - K1 / K1d / K1m: everything that reads the packed 2-bit genotypes.
+//
+// K1  bed_decode      : one pass per SNP row - count alleles (popc over bit planes, shuffle
+//                       reduction), derive 2p and the reference's doubly-rounded standardised
+//                       values as a 4-entry look-up table, and write the 16-bit SNP-major Z
+//                       row that K2 consumes.  Replaces data.cpp:171-185 (unpack), 781-803
+//                       (mu_func), 1001-1007 (make_XMat) and 1030-1043 (std_XMat).
+// K1d diag_accum      : exact float64 diagonal sum_k z_ik^2 and per-individual non-missing
+//                       counts N_ii (grm.cpp:265-275), column-wise over the packed bytes.
+// K1m nonmiss_planes  : bit-packed non-missing indicators, 32 SNPs per word, individual-minor,
+//                       for the AND+popc pair-count kernel K3.
+//
+// All three are HBM-bound byte/bit kernels: 128-bit loads of packed genotypes, 128-bit
+// coalesced stores of Z.  Algorithmic bytes per SNP: ceil(n/4) read + 2*ldz written (K1).
+#include "common.cuh"
+
+namespace gb {
+
+// code (2 bits, low bit first): 00 -> 2 copies of allele 1, 10b -> 1, 11 -> 0, 01b -> missing
+// (data.cpp:176-181: _snp_2 = !low, _snp_1 = !high, missing iff _snp_1 && !_snp_2).
+struct SnpCounts {
+    int cnt, sum, cntM, sumM;
+};
+
+template <bool XCHR>
+__device__ __forceinline__ void count_word(uint32_t w, uint32_t km, uint32_t mm, SnpCounts& c)
+{
+    const uint32_t lo = w & 0x55555555u, hi = (w >> 1) & 0x55555555u;
+    const uint32_t nm = ~(lo & ~hi) & km;  // kept and not missing (even bit positions)
+    c.cnt += __popc(nm);
+    c.sum += __popc(nm & ~hi) + __popc(nm & ~lo);
+    if (XCHR) {
+        const uint32_t nmm = nm & mm;
+        c.cntM += __popc(nmm);
+        c.sumM += __popc(nmm & ~hi) + __popc(nmm & ~lo);
+    }
+}
+
+__device__ __forceinline__ int warp_sum(int v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ uint32_t to16(float z, int bf16)
+{
+    return bf16 ? (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(z)) : (uint32_t)__half_as_ushort(__float2half_rn(z));
+}
+
+struct DecodeParams {
+    const uint8_t* bed;
+    int64_t pitch;
+    int64_t n_file;
+    const uint32_t* keepmask;
+    const int32_t* keep;
+    int64_t n;
+    const uint32_t* sexmale;
+    const int32_t* include;
+    int64_t k0, kc, kc_pad;
+    const double* mu_in;
+    int divide, bf16;
+    uint16_t* Z;
+    int64_t ldz;
+    double* mu;
+    int32_t* cnt;
+    int32_t* sum;
+    float* zlut;
+    unsigned long long* total_missing;
+};
+
+// GROUP threads cooperate on one SNP row; 256/GROUP rows per block.
+template <int GROUP, bool XCHR>
+__global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
+{
+    constexpr int ROWS = 256 / GROUP;
+    const int tid = threadIdx.x % GROUP;
+    const int64_t kk = (int64_t)blockIdx.x * ROWS + threadIdx.x / GROUP;
+    if (kk >= p.kc_pad) return;  // uniform per group (and per block when GROUP == 256)
+    uint4* zrow = reinterpret_cast<uint4*>(p.Z + kk * p.ldz);
+    const int nchunk = (int)(p.ldz / 8);
+    if (kk >= p.kc) {  // padding row of the last 64-SNP block
+        for (int c = tid; c < nchunk; c += GROUP) zrow[c] = make_uint4(0, 0, 0, 0);
+        return;
+    }
+    const int64_t k = p.k0 + kk;
+    const uint8_t* row = p.bed + (int64_t)(p.include ? p.include[k] : (int32_t)k) * p.pitch;
+
+    // ---- pass 1: allele counts ----
+    SnpCounts c = {0, 0, 0, 0};
+    const int nvec = (int)(p.pitch / 16);
+    const uint4* row16 = reinterpret_cast<const uint4*>(row);
+    const uint4* km16 = reinterpret_cast<const uint4*>(p.keepmask);
+    const uint4* mm16 = reinterpret_cast<const uint4*>(p.sexmale);
+    for (int v = tid; v < nvec; v += GROUP) {
+        const uint4 w = __ldg(row16 + v), km = __ldg(km16 + v);
+        uint4 mm = make_uint4(0, 0, 0, 0);
+        if (XCHR) mm = __ldg(mm16 + v);
+        count_word<XCHR>(w.x, km.x, mm.x, c);
+        count_word<XCHR>(w.y, km.y, mm.y, c);
+        count_word<XCHR>(w.z, km.z, mm.z, c);
+        count_word<XCHR>(w.w, km.w, mm.w, c);
+    }
+    c.cnt = warp_sum(c.cnt);
+    c.sum = warp_sum(c.sum);
+    if (XCHR) {
+        c.cntM = warp_sum(c.cntM);
+        c.sumM = warp_sum(c.sumM);
+    }
+    if (GROUP > 32) {
+        __shared__ int red[8][4];
+        const int w = threadIdx.x >> 5;
+        if ((threadIdx.x & 31) == 0) {
+            red[w][0] = c.cnt; red[w][1] = c.sum; red[w][2] = c.cntM; red[w][3] = c.sumM;
+        }
+        __syncthreads();
+        c = {0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < 8; i++) { c.cnt += red[i][0]; c.sum += red[i][1]; c.cntM += red[i][2]; c.sumM += red[i][3]; }
+    }
+
+    // ---- per-SNP constants: mu = 2p and the doubly-rounded z values (data.cpp:801, 1027-1040) ----
+    double mu;
+    if (p.mu_in) mu = p.mu_in[k];
+    else if (XCHR) {
+        // weights 0.5 (male) / 1.0 (female), data.cpp:765-767: (0.5 sM + sF)/(0.5 cM + cF) == (sM + 2 sF)/(cM + 2 cF)
+        const int num = c.sumM + 2 * (c.sum - c.sumM), den = c.cntM + 2 * (c.cnt - c.cntM);
+        mu = den > 0 ? __ddiv_rn((double)num, (double)den) : 0.0;
+    } else
+        mu = c.cnt > 0 ? __ddiv_rn((double)c.sum, (double)c.cnt) : 0.0;
+    const double var = __dmul_rn(mu, __dsub_rn(1.0, __dmul_rn(0.5, mu)));
+    const double isd = fabs(var) < 1.0e-50 ? 0.0 : __dsqrt_rn(__ddiv_rn(1.0, var));
+    float zf[4], zm[4];
+#pragma unroll
+    for (int code = 0; code < 4; code++) {
+        const int x = code == 0 ? 2 : (code == 2 ? 1 : 0);
+        float z = __double2float_rn(__dsub_rn((double)x, mu));                 // X -= mu   (data.cpp:1039)
+        if (p.divide) z = __double2float_rn(__dmul_rn((double)z, isd));        // X *= sd   (data.cpp:1040)
+        if (code == 1) z = 0.0f;                                               // missing contributes nothing
+        zf[code] = z;
+        zm[code] = XCHR ? __double2float_rn(__dmul_rn((double)z, __dsqrt_rn(0.5))) : z;  // data.cpp:1048-1054
+    }
+    uint64_t lutF = 0, lutM = 0;
+#pragma unroll
+    for (int code = 0; code < 4; code++) {
+        lutF |= (uint64_t)to16(zf[code], p.bf16) << (16 * code);
+        lutM |= (uint64_t)to16(zm[code], p.bf16) << (16 * code);
+    }
+    if (tid == 0) {
+        p.mu[k] = mu;
+        p.cnt[k] = c.cnt;
+        p.sum[k] = c.sum;
+#pragma unroll
+        for (int code = 0; code < 4; code++) {
+            p.zlut[k * 8 + code] = zf[code];
+            p.zlut[k * 8 + 4 + code] = zm[code];
+        }
+        atomicAdd(p.total_missing, (unsigned long long)(p.n - c.cnt));
+    }
+
+    // ---- pass 2: write the standardised row (8 individuals = one 16-byte store per lane) ----
+    const uint16_t* row2 = reinterpret_cast<const uint16_t*>(row);
+    const uint16_t* male2 = reinterpret_cast<const uint16_t*>(p.sexmale);
+    for (int ch = tid; ch < nchunk; ch += GROUP) {
+        const int64_t i0 = (int64_t)ch * 8;
+        uint32_t o[4] = {0, 0, 0, 0};
+        if (i0 < p.n) {
+            if (!p.keep) {
+                const uint32_t w = __ldg(row2 + ch);
+                // sexmale marks individual 16w+t at bit 2t, i.e. the same 2-bit slots as the genotypes
+                const uint32_t mb = XCHR ? (uint32_t)__ldg(male2 + ch) : 0u;
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    const uint32_t code = (w >> (2 * e)) & 3u;
+                    const uint64_t lut = (XCHR && ((mb >> (2 * e)) & 1u)) ? lutM : lutF;
+                    uint32_t v = (uint32_t)(lut >> (16 * code)) & 0xFFFFu;
+                    if (i0 + e >= p.n) v = 0;
+                    o[e >> 1] |= v << (16 * (e & 1));
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    uint32_t v = 0;
+                    if (i0 + e < p.n) {
+                        const int f = p.keep[i0 + e];
+                        const uint32_t code = (row[f >> 2] >> ((f & 3) * 2)) & 3u;
+                        const bool male = XCHR && ((p.sexmale[f >> 4] >> ((f & 15) * 2)) & 1u);
+                        v = (uint32_t)((male ? lutM : lutF) >> (16 * code)) & 0xFFFFu;
+                    }
+                    o[e >> 1] |= v << (16 * (e & 1));
+                }
+            }
+        }
+        zrow[ch] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1d: thread = one 32-bit column (16 file individuals), loops over a slice of SNPs.
+// ------------------------------------------------------------------------------------------------
+constexpr int DIAG_SPLIT = 1024;  // SNPs per thread slice
+
+template <bool XCHR>
+__global__ void __launch_bounds__(128) diag_accum_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n_file,
+                                                          const uint32_t* __restrict__ sexmale,
+                                                          const int32_t* __restrict__ include, int64_t k0, int64_t kc,
+                                                          const float* __restrict__ zlut, double* __restrict__ diag,
+                                                          int32_t* __restrict__ nii)
+{
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (col * 16 >= n_file) return;
+    const int64_t kbeg = (int64_t)blockIdx.y * DIAG_SPLIT, kend = min(kbeg + DIAG_SPLIT, kc);
+    const uint32_t mm = XCHR ? sexmale[col] : 0u;
+    double acc[16];
+    int cn[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) { acc[e] = 0.0; cn[e] = 0; }
+    for (int64_t kk = kbeg; kk < kend; kk++) {
+        const int64_t k = k0 + kk;
+        const int64_t frow = include ? include[k] : k;
+        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(bed + frow * pitch) + col);
+        const float4 lf = __ldg(reinterpret_cast<const float4*>(zlut + k * 8));
+        // exact products of two floats in double (grm.cpp:267: static_cast<double>(X) * X)
+        const double q0 = (double)lf.x * (double)lf.x, q2 = (double)lf.z * (double)lf.z, q3 = (double)lf.w * (double)lf.w;
+        double m0 = q0, m2 = q2, m3 = q3;
+        if (XCHR) {
+            const float4 lm = __ldg(reinterpret_cast<const float4*>(zlut + k * 8 + 4));
+            m0 = (double)lm.x * (double)lm.x; m2 = (double)lm.z * (double)lm.z; m3 = (double)lm.w * (double)lm.w;
+        }
+#pragma unroll
+        for (int e = 0; e < 16; e++) {
+            const uint32_t code = (w >> (2 * e)) & 3u;
+            const bool male = XCHR && ((mm >> (2 * e)) & 1u);
+            const double a0 = male ? m0 : q0, a2 = male ? m2 : q2, a3 = male ? m3 : q3;
+            acc[e] += code == 0 ? a0 : (code == 2 ? a2 : (code == 3 ? a3 : 0.0));
+            cn[e] += code != 1u;
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 16; e++) {
+        const int64_t f = col * 16 + e;
+        if (f < n_file) {
+            atomicAdd(diag + f, acc[e]);
+            atomicAdd(nii + f, cn[e]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1m: non-missing bit planes.  thread = (plane word w, 16 individuals); identity keep only.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) nonmiss_planes_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n,
+                                                              const int32_t* __restrict__ include, int64_t k0, int64_t kc,
+                                                              uint32_t* __restrict__ planes, int64_t ldm)
+{
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // 16-individual column
+    if (col * 16 >= ldm) return;
+    const int64_t w = k0 / 32 + blockIdx.y;
+    uint32_t out[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) out[e] = 0;
+    if (col * 4 < pitch) {
+        for (int b = 0; b < 32; b++) {
+            const int64_t k = w * 32 + b;
+            if (k >= k0 + kc) break;
+            const int64_t frow = include ? include[k] : k;
+            const uint32_t g = __ldg(reinterpret_cast<const uint32_t*>(bed + frow * pitch) + col);
+            const uint32_t nm = ~((g & 0x55555555u) & ~((g >> 1) & 0x55555555u)) & 0x55555555u;
+#pragma unroll
+            for (int e = 0; e < 16; e++) out[e] |= ((nm >> (2 * e)) & 1u) << b;
+        }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(planes + w * ldm + col * 16);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) o[e] = (col * 16 + q * 4 + e < n) ? out[q * 4 + e] : 0u;
+        dst[q] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// gather variant for a non-identity keep list: thread = (plane word, kept individual)
+__global__ void __launch_bounds__(128) nonmiss_planes_gather_kernel(const uint8_t* __restrict__ bed, int64_t pitch,
+                                                                     const int32_t* __restrict__ keep, int64_t n,
+                                                                     const int32_t* __restrict__ include, int64_t k0,
+                                                                     int64_t kc, uint32_t* __restrict__ planes, int64_t ldm)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ldm) return;
+    const int64_t w = k0 / 32 + blockIdx.y;
+    uint32_t out = 0;
+    if (i < n) {
+        const int f = keep[i];
+        for (int b = 0; b < 32; b++) {
+            const int64_t k = w * 32 + b;
+            if (k >= k0 + kc) break;
+            const int64_t frow = include ? include[k] : k;
+            const uint32_t code = (bed[frow * pitch + (f >> 2)] >> ((f & 3) * 2)) & 3u;
+            out |= (uint32_t)(code != 1u) << b;
+        }
+    }
+    planes[w * ldm + i] = out;
+}
+
+}  // namespace gb
+
+extern "C" int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_keepmask,
+                                    const int32_t* d_keep, int64_t n, const uint32_t* d_sexmale, const int32_t* d_include,
+                                    int64_t k0, int64_t kc, const double* d_mu_in, int32_t xchr, int32_t alg, int32_t operand,
+                                    void* d_Z, int64_t ldz, double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
+                                    unsigned long long* d_total_missing, void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_bed && d_keepmask && d_Z && d_mu && d_cnt && d_sum && d_zlut && d_total_missing, "bed_decode: null pointer");
+    GB_ARG(pitch > 0 && pitch % 16 == 0 && ((uintptr_t)d_bed & 15) == 0, "bed_decode: bed pitch and pointer must be multiples of 16 bytes");
+    GB_ARG(pitch * 4 >= n_file && n_file > 0, "bed_decode: pitch too small for n_file");
+    GB_ARG(n > 0 && n <= n_file && (d_keep || n == n_file), "bed_decode: n must equal n_file when keep is NULL");
+    GB_ARG(ldz % 256 == 0 && ldz >= n, "bed_decode: ldz must be a multiple of 256 and >= n");
+    GB_ARG(((uintptr_t)d_Z & 15) == 0, "bed_decode: Z must be 16-byte aligned");
+    GB_ARG(kc > 0 && k0 >= 0, "bed_decode: empty SNP range");
+    GB_ARG(!xchr || d_sexmale, "bed_decode: xchr needs the male mask");
+    GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "bed_decode: unknown operand type");
+    DecodeParams p;
+    p.bed = d_bed; p.pitch = pitch; p.n_file = n_file; p.keepmask = d_keepmask; p.keep = d_keep; p.n = n;
+    p.sexmale = d_sexmale; p.include = d_include; p.k0 = k0; p.kc = kc; p.kc_pad = (kc + 63) / 64 * 64;
+    p.mu_in = d_mu_in; p.divide = alg == 0; p.bf16 = operand == GCTA_B200_BF16;
+    p.Z = (uint16_t*)d_Z; p.ldz = ldz; p.mu = d_mu; p.cnt = d_cnt; p.sum = d_sum; p.zlut = d_zlut;
+    p.total_missing = d_total_missing;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool wide = pitch >= 4096;  // one CTA per row when a row is at least 4 KB, else one warp per row
+    if (wide) {
+        const unsigned grid = (unsigned)p.kc_pad;
+        if (xchr) bed_decode_kernel<256, true><<<grid, 256, 0, st>>>(p);
+        else bed_decode_kernel<256, false><<<grid, 256, 0, st>>>(p);
+    } else {
+        const unsigned grid = (unsigned)((p.kc_pad + 7) / 8);
+        if (xchr) bed_decode_kernel<32, true><<<grid, 256, 0, st>>>(p);
+        else bed_decode_kernel<32, false><<<grid, 256, 0, st>>>(p);
+    }
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int gcta_b200_diag_accum(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_sexmale,
+                                    const int32_t* d_include, int64_t k0, int64_t kc, const float* d_zlut, double* d_diag,
+                                    int32_t* d_nii, void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_bed && d_zlut && d_diag && d_nii, "diag_accum: null pointer");
+    GB_ARG(pitch > 0 && pitch % 16 == 0, "diag_accum: pitch must be a multiple of 16");
+    GB_ARG(kc > 0, "diag_accum: empty SNP range");
+    const int64_t cols = (n_file + 15) / 16;
+    dim3 grid((unsigned)((cols + 127) / 128), (unsigned)((kc + DIAG_SPLIT - 1) / DIAG_SPLIT));
+    if (d_sexmale) diag_accum_kernel<true><<<grid, 128, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, d_sexmale, d_include, k0, kc, d_zlut, d_diag, d_nii);
+    else diag_accum_kernel<false><<<grid, 128, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, d_zlut, d_diag, d_nii);
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int gcta_b200_nonmiss_planes(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_keep, int64_t n,
+                                        const int32_t* d_include, int64_t k0, int64_t kc, uint32_t* d_planes, int64_t ldm,
+                                        void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_bed && d_planes, "nonmiss_planes: null pointer");
+    GB_ARG(pitch > 0 && pitch % 16 == 0, "nonmiss_planes: pitch must be a multiple of 16");
+    GB_ARG(k0 % 32 == 0 && kc > 0, "nonmiss_planes: k0 must be a multiple of 32");
+    GB_ARG(ldm % 256 == 0 && ldm >= n, "nonmiss_planes: ldm must be a multiple of 256 and >= n");
+    GB_ARG(d_keep || n == n_file, "nonmiss_planes: n must equal n_file when keep is NULL");
+    const unsigned words = (unsigned)((kc + 31) / 32);
+    if (!d_keep) {
+        dim3 grid((unsigned)((ldm / 16 + 127) / 128), words);
+        nonmiss_planes_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(d_bed, pitch, n, d_include, k0, kc, d_planes, ldm);
+    } else {
+        dim3 grid((unsigned)((ldm + 127) / 128), words);
+        nonmiss_planes_gather_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(d_bed, pitch, d_keep, n, d_include, k0, kc, d_planes, ldm);
+    }
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}

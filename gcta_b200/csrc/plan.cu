@@ -1,0 +1,473 @@
+// plan.cu - orchestration of the --make-grm path on one GPU (one row band of the GRM).
+//
+// Mirrors the sequence inside gcta::make_grm (grm.cpp:219-301):
+//   make_XMat + std_XMat  -> K1 bed_decode, one SNP chunk at a time into a reused Z buffer
+//   triple loop numerator -> K2 syrk_tiles accumulating FP32 S tiles over the chunks
+//   A_N counts            -> K1m + K3 (AND+popc), only when some kept genotype is missing
+//   A = S / N, zero rules -> K4 finalize_tiles into the packed lower triangle
+// Multi-GPU: the caller runs one plan per process / GPU with
+// (part_rank, part_world); each plan owns a contiguous band of rows [row_begin,row_end) of
+// the lower triangle, balanced by tile count, so outputs are disjoint contiguous ranges of
+// the packed triangle and no collective is needed on the data path.
+#include <algorithm>
+#include <thread>
+#include <vector>
+
+#include "common.cuh"
+
+namespace gb {
+
+static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// column blocks needed by row block bi: columns 0 .. 128*bi+127 (clipped to n)
+static int64_t tiles_in_row_block(int64_t bi, int64_t n)
+{
+    const int64_t last_row = std::min<int64_t>(bi * TILE_M + TILE_M - 1, n - 1);
+    return last_row / TILE_N + 1;
+}
+
+constexpr int RASTER_ROWS = 16;  // row blocks per raster group: tiles in flight share 16 A panels
+
+}  // namespace gb
+
+extern "C" const char* gcta_b200_version(void) { return "gcta_b200 0.1.0 (sm_100a)"; }
+
+extern "C" int gcta_b200_device_count(void)
+{
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return c;
+}
+
+extern "C" int gcta_b200_partition(int64_t n, int32_t part_rank, int32_t part_world, int64_t* row_begin, int64_t* row_end)
+{
+    using namespace gb;
+    if (n <= 0 || !row_begin || !row_end) return GCTA_B200_ERR_ARG;
+    if (part_world <= 1) { *row_begin = 0; *row_end = n; return 0; }
+    if (part_rank < 0 || part_rank >= part_world) return GCTA_B200_ERR_ARG;
+    const int64_t nrb = (n + TILE_M - 1) / TILE_M;
+    int64_t total = 0;
+    for (int64_t b = 0; b < nrb; b++) total += tiles_in_row_block(b, n);
+    // boundary g = first row block whose tile prefix reaches g/G of the total
+    auto boundary = [&](int g) -> int64_t {
+        if (g <= 0) return 0;
+        if (g >= part_world) return nrb;
+        const double target = (double)total * g / part_world;
+        int64_t acc = 0;
+        for (int64_t b = 0; b < nrb; b++) {
+            if ((double)acc >= target) return b;
+            acc += tiles_in_row_block(b, n);
+        }
+        return nrb;
+    };
+    *row_begin = std::min<int64_t>(boundary(part_rank) * TILE_M, n);
+    *row_end = std::min<int64_t>(boundary(part_rank + 1) * TILE_M, n);
+    return 0;
+}
+
+extern "C" int64_t gcta_b200_tile_list(int64_t n, int64_t row_begin, int64_t row_end, int32_t* tiles)
+{
+    using namespace gb;
+    if (n <= 0 || row_begin < 0 || row_end > n) return -1;
+    if (row_begin >= row_end) return 0;
+    if (row_begin % TILE_M != 0) return -1;
+    const int64_t b0 = row_begin / TILE_M, b1 = (row_end + TILE_M - 1) / TILE_M;
+    int64_t cnt = 0;
+    for (int64_t g0 = b0; g0 < b1; g0 += RASTER_ROWS) {
+        const int64_t g1 = std::min<int64_t>(g0 + RASTER_ROWS, b1);
+        const int64_t maxcb = tiles_in_row_block(g1 - 1, n);
+        for (int64_t bj = 0; bj < maxcb; bj++)
+            for (int64_t bi = g0; bi < g1; bi++) {
+                if (bj >= tiles_in_row_block(bi, n)) continue;
+                if (tiles) { tiles[2 * cnt] = (int32_t)bi; tiles[2 * cnt + 1] = (int32_t)bj; }
+                cnt++;
+            }
+    }
+    return cnt;
+}
+
+struct gcta_b200_plan {
+    // problem
+    int64_t n_file = 0, m_file = 0, n = 0, m = 0, stride = 0, pitch = 0, ldz = 0;
+    int xchr = 0, alg = 0, operand = 0, device = 0;
+    bool has_keep = false, has_include = false, has_mu = false;
+    int64_t row_begin = 0, row_end = 0, ntiles = 0, chunk = 0, band_count = 0;
+    // device
+    cudaStream_t stream = nullptr;
+    uint8_t* d_bed = nullptr;
+    uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
+    int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
+    int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr;
+    double *d_mu_in = nullptr, *d_mu = nullptr, *d_diag = nullptr;
+    float *d_zlut = nullptr, *d_S = nullptr, *d_A_lower = nullptr;
+    void* d_Z = nullptr;
+    unsigned long long* d_total_missing = nullptr;
+    std::vector<cudaEvent_t> events;
+    bool ran = false;
+    int64_t total_missing = 0;
+    std::vector<void*> allocs;
+};
+
+namespace gb {
+
+template <typename T>
+static int dev_alloc(gcta_b200_plan* p, T** ptr, size_t count, char* err, size_t errcap)
+{
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return set_err(err, errcap, e == cudaErrorMemoryAllocation ? GCTA_B200_ERR_NOMEM : GCTA_B200_ERR_CUDA,
+                       std::string("Error: device allocation of ") + std::to_string(count * sizeof(T)) + " bytes failed: " + cudaGetErrorString(e));
+    }
+    p->allocs.push_back(q);
+    *ptr = (T*)q;
+    return 0;
+}
+
+}  // namespace gb
+
+extern "C" void gcta_b200_plan_destroy(gcta_b200_plan* p)
+{
+    if (!p) return;
+    cudaSetDevice(p->device);
+    if (p->stream) cudaStreamSynchronize(p->stream);
+    for (cudaEvent_t e : p->events) cudaEventDestroy(e);
+    for (void* q : p->allocs) cudaFree(q);
+    if (p->stream) cudaStreamDestroy(p->stream);
+    delete p;
+}
+
+extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** out_plan, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(a && out_plan, "plan_create: null argument");
+    GB_ARG(a->n_file > 0 && a->m_file > 0, "plan_create: empty genotype file");
+    GB_ARG(a->n_file < (1ll << 31) && a->m_file < (1ll << 31), "plan_create: more than 2^31 individuals or SNPs");
+    const int64_t n = a->keep ? a->n : a->n_file, m = a->include ? a->m : a->m_file;
+    if (m <= 0) return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: No SNP is retained for analysis.");           // data.cpp:149
+    if (n <= 0) return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: No individual is retained for analysis.");    // data.cpp:150
+    GB_ARG(n <= a->n_file && m <= a->m_file, "plan_create: more kept than present");
+    GB_ARG(a->alg == 0 || a->alg == 1, "plan_create: alg must be 0 or 1");
+    GB_ARG(a->alg == 0, "plan_create: --grm-alg 1 is not implemented on the device yet");
+    GB_ARG(a->operand == GCTA_B200_FP16 || a->operand == GCTA_B200_BF16, "plan_create: unknown operand type");
+    GB_ARG(!a->xchr || a->sex, "plan_create: xchr needs the sex array");
+    if (gcta_b200_device_count() <= 0)
+        return set_err(err, errcap, GCTA_B200_ERR_NO_DEVICE, "Error: no CUDA device is available (gcta_b200 has no CPU fallback).");
+    GB_ARG(a->device >= 0 && a->device < gcta_b200_device_count(), "plan_create: bad device ordinal");
+    if (a->keep)
+        for (int64_t i = 0; i < n; i++)
+            GB_ARG(a->keep[i] >= 0 && a->keep[i] < a->n_file && (i == 0 || a->keep[i] > a->keep[i - 1]), "plan_create: keep must be ascending file indices");
+    if (a->include)
+        for (int64_t k = 0; k < m; k++)
+            GB_ARG(a->include[k] >= 0 && a->include[k] < a->m_file, "plan_create: include index out of range");
+    if (a->xchr)
+        for (int64_t i = 0; i < n; i++) {
+            const int s = a->sex[a->keep ? a->keep[i] : i];
+            if (s != 1 && s != 2)  // check_sex, grm.cpp:29-34
+                return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: Sex information of some individuals are missing. Use --update-sex option to update the sex information of the individuals.");
+        }
+
+    GB_CUDA(cudaSetDevice(a->device));
+    gcta_b200_plan* p = new gcta_b200_plan();
+    *out_plan = nullptr;
+    p->n_file = a->n_file; p->m_file = a->m_file; p->n = n; p->m = m;
+    p->stride = (a->n_file + 3) / 4;
+    p->pitch = round_up(p->stride, 16);
+    p->ldz = round_up(n, TILE_N);
+    p->xchr = a->xchr; p->alg = a->alg; p->operand = a->operand; p->device = a->device;
+    p->has_keep = a->keep != nullptr && !(n == a->n_file);
+    p->has_include = a->include != nullptr;
+    p->has_mu = a->mu != nullptr;
+#define PLAN_TRY(x) do { int rc_ = (x); if (rc_) { gcta_b200_plan_destroy(p); return rc_; } } while (0)
+#define PLAN_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { gcta_b200_plan_destroy(p); \
+        return set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed: ") + #x + ": " + cudaGetErrorString(e_)); } } while (0)
+    if (gcta_b200_partition(n, a->part_rank, a->part_world, &p->row_begin, &p->row_end) != 0) {
+        gcta_b200_plan_destroy(p);
+        return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: plan_create: bad part_rank / part_world");
+    }
+    p->ntiles = gcta_b200_tile_list(n, p->row_begin, p->row_end, nullptr);
+    p->band_count = p->row_end * (p->row_end + 1) / 2 - p->row_begin * (p->row_begin + 1) / 2;
+    PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+
+    // fixed-size buffers
+    PLAN_TRY(dev_alloc(p, &p->d_bed, (size_t)p->pitch * a->m_file, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_keepmask, (size_t)p->pitch / 4, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_mu, (size_t)m, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_cnt, (size_t)m, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_sum, (size_t)m, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_zlut, (size_t)m * 8, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_diag, (size_t)a->n_file, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_nii, (size_t)a->n_file, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_total_missing, 1, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_tiles, (size_t)p->ntiles * 2, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_S, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap));
+    PLAN_TRY(dev_alloc(p, &p->d_A_lower, (size_t)p->band_count, err, errcap));
+
+    // host-built index structures
+    std::vector<uint32_t> km((size_t)p->pitch / 4, 0u), mm;
+    if (a->xchr) mm.assign((size_t)p->pitch / 4, 0u);
+    for (int64_t i = 0; i < n; i++) {
+        const int64_t f = p->has_keep ? a->keep[i] : i;
+        km[f >> 4] |= 1u << ((f & 15) * 2);
+        if (a->xchr && a->sex[f] == 1) mm[f >> 4] |= 1u << ((f & 15) * 2);
+    }
+    PLAN_CUDA(cudaMemcpy(p->d_keepmask, km.data(), km.size() * 4, cudaMemcpyHostToDevice));
+    if (a->xchr) {
+        PLAN_TRY(dev_alloc(p, &p->d_sexmale, mm.size(), err, errcap));
+        PLAN_CUDA(cudaMemcpy(p->d_sexmale, mm.data(), mm.size() * 4, cudaMemcpyHostToDevice));
+    }
+    if (p->has_keep) {
+        PLAN_TRY(dev_alloc(p, &p->d_keep, (size_t)n, err, errcap));
+        PLAN_CUDA(cudaMemcpy(p->d_keep, a->keep, (size_t)n * 4, cudaMemcpyHostToDevice));
+    }
+    if (p->has_include) {
+        PLAN_TRY(dev_alloc(p, &p->d_include, (size_t)m, err, errcap));
+        PLAN_CUDA(cudaMemcpy(p->d_include, a->include, (size_t)m * 4, cudaMemcpyHostToDevice));
+    }
+    if (p->has_mu) {
+        PLAN_TRY(dev_alloc(p, &p->d_mu_in, (size_t)m, err, errcap));
+        PLAN_CUDA(cudaMemcpy(p->d_mu_in, a->mu, (size_t)m * 8, cudaMemcpyHostToDevice));
+    }
+    {
+        std::vector<int32_t> tl((size_t)p->ntiles * 2 + 2);
+        gcta_b200_tile_list(n, p->row_begin, p->row_end, tl.data());
+        PLAN_CUDA(cudaMemcpy(p->d_tiles, tl.data(), (size_t)p->ntiles * 8, cudaMemcpyHostToDevice));
+    }
+    // SNP chunk: Z buffer of at most ~8 GiB (or what is left of HBM), multiple of 64 SNPs
+    {
+        size_t free_b = 0, total_b = 0;
+        PLAN_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        int64_t budget = std::min<int64_t>((int64_t)(free_b / 3), 8ll << 30);
+        int64_t kc = a->chunk_snps > 0 ? a->chunk_snps : budget / (p->ldz * 2);
+        kc = std::max<int64_t>(64, kc / 64 * 64);
+        kc = std::min<int64_t>(kc, round_up(m, 64));
+        p->chunk = kc;
+        PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Z, (size_t)kc * p->ldz, err, errcap));
+    }
+    *out_plan = p;
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_upload(gcta_b200_plan* p, const uint8_t* bed_host, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && bed_host, "plan_upload: null argument");
+    GB_CUDA(cudaSetDevice(p->device));
+    // re-pitch rows to a multiple of 16 bytes so K1 can use 128-bit loads; pad bytes are zero
+    if (p->pitch != p->stride) GB_CUDA(cudaMemsetAsync(p->d_bed, 0, (size_t)p->pitch * p->m_file, p->stream));
+    GB_CUDA(cudaMemcpy2DAsync(p->d_bed, (size_t)p->pitch, bed_host, (size_t)p->stride, (size_t)p->stride, (size_t)p->m_file,
+                              cudaMemcpyHostToDevice, p->stream));
+    GB_CUDA(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
+namespace gb {
+__device__ __forceinline__ uint64_t mix64(uint64_t x)
+{
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
+    x ^= x >> 27; x *= 0x94D049BB133111EBull;
+    x ^= x >> 31;
+    return x;
+}
+// same generator as gcta_b200/synth.py:bed_rows - one thread per packed byte
+__global__ void synth_bed_kernel(uint8_t* bed, int64_t pitch, int64_t stride, int64_t n, int64_t m, uint64_t seed, const uint4* thr)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= pitch * m) return;
+    const int64_t k = idx / pitch, b = idx % pitch;
+    uint32_t byte = 0;
+    if (b < stride) {
+        const uint4 t = thr[k];
+        for (int e = 0; e < 4; e++) {
+            const int64_t i = b * 4 + e;
+            if (i >= n) break;
+            const uint64_t h = mix64(seed + (uint64_t)k * 0x9E3779B97F4A7C15ull + (uint64_t)i * 0xC2B2AE3D27D4EB4Full);
+            const uint32_t g = (uint32_t)h, r = (uint32_t)(h >> 32);
+            uint32_t code = 3;
+            if (g < t.y) code = 2;
+            if (g < t.x) code = 0;
+            if (r < t.z) code = 1;
+            byte |= code << (2 * e);
+        }
+    }
+    bed[idx] = (uint8_t)byte;
+}
+}  // namespace gb
+
+extern "C" int gcta_b200_plan_synth(gcta_b200_plan* p, uint64_t seed, const uint32_t* thr_host, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && thr_host, "plan_synth: null argument");
+    GB_CUDA(cudaSetDevice(p->device));
+    uint4* d_thr = nullptr;
+    GB_CUDA(cudaMalloc(&d_thr, (size_t)p->m_file * 16));
+    cudaError_t e = cudaMemcpy(d_thr, thr_host, (size_t)p->m_file * 16, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        const int64_t total = p->pitch * p->m_file;
+        synth_bed_kernel<<<(unsigned)((total + 255) / 256), 256, 0, p->stream>>>(p->d_bed, p->pitch, p->stride, p->n_file, p->m_file, seed, d_thr);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    }
+    cudaFree(d_thr);
+    GB_CUDA(e);
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && out, "plan_run: null argument");
+    GB_CUDA(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    const int64_t nchunks = (p->m + p->chunk - 1) / p->chunk;
+    // events: [0] start, then per chunk (after decode+diag, after syrk), then after paircount, after finalize
+    const size_t need = (size_t)(2 * nchunks + 4);
+    while (p->events.size() < need) {
+        cudaEvent_t ev;
+        GB_CUDA(cudaEventCreate(&ev));
+        p->events.push_back(ev);
+    }
+    int launches = 0;
+    GB_CUDA(cudaEventRecord(p->events[0], st));
+    GB_CUDA(cudaMemsetAsync(p->d_S, 0, (size_t)p->ntiles * TILE_M * TILE_N * sizeof(float), st));
+    GB_CUDA(cudaMemsetAsync(p->d_diag, 0, (size_t)p->n_file * 8, st));
+    GB_CUDA(cudaMemsetAsync(p->d_nii, 0, (size_t)p->n_file * 4, st));
+    GB_CUDA(cudaMemsetAsync(p->d_total_missing, 0, 8, st));
+    for (int64_t c = 0; c < nchunks; c++) {
+        const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
+        int rc = gcta_b200_bed_decode(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
+                                      p->d_mu_in, p->xchr, p->alg, p->operand, p->d_Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
+                                      p->d_total_missing, st, err, errcap);
+        if (rc) return rc;
+        rc = gcta_b200_diag_accum(p->d_bed, p->pitch, p->n_file, p->d_sexmale, p->d_include, k0, kc, p->d_zlut, p->d_diag, p->d_nii, st, err, errcap);
+        if (rc) return rc;
+        GB_CUDA(cudaEventRecord(p->events[1 + 2 * c], st));
+        rc = gcta_b200_syrk_tiles(p->d_Z, p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+        if (rc) return rc;
+        GB_CUDA(cudaEventRecord(p->events[2 + 2 * c], st));
+        launches += 3;
+    }
+    unsigned long long tm = 0;
+    GB_CUDA(cudaMemcpyAsync(&tm, p->d_total_missing, 8, cudaMemcpyDeviceToHost, st));
+    GB_CUDA(cudaStreamSynchronize(st));
+    p->total_missing = (int64_t)tm;
+    const size_t e_pc = 1 + 2 * nchunks, e_fin = e_pc + 1;
+    if (tm > 0) {
+        const int64_t nwords = (p->m + 31) / 32;
+        if (!p->d_planes) {
+            int rc = dev_alloc(p, &p->d_planes, (size_t)nwords * p->ldz, err, errcap);
+            if (rc) return rc;
+            rc = dev_alloc(p, &p->d_Ntiles, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap);
+            if (rc) return rc;
+            rc = dev_alloc(p, &p->d_N_lower, (size_t)p->band_count, err, errcap);
+            if (rc) return rc;
+        }
+        GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
+        // planes in slabs of at most 65535 words (grid.y limit)
+        for (int64_t w0 = 0; w0 < nwords; w0 += 32768) {
+            const int64_t k0 = w0 * 32, kc = std::min<int64_t>(32768 * 32, p->m - k0);
+            int rc = gcta_b200_nonmiss_planes(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, p->d_planes, p->ldz, st, err, errcap);
+            if (rc) return rc;
+            launches++;
+        }
+        int rc = gcta_b200_paircount_tiles(p->d_planes, p->ldz, nwords, p->d_tiles, p->ntiles, p->d_Ntiles, st, err, errcap);
+        if (rc) return rc;
+        launches++;
+    }
+    GB_CUDA(cudaEventRecord(p->events[e_pc], st));
+    {
+        int rc = gcta_b200_finalize_tiles(p->d_S, tm > 0 ? p->d_Ntiles : nullptr, (int32_t)p->m, p->d_tiles, p->ntiles, p->n, p->d_keep,
+                                          p->d_diag, p->d_nii, p->row_begin, p->row_end, p->d_A_lower, tm > 0 ? p->d_N_lower : nullptr, st, err, errcap);
+        if (rc) return rc;
+        launches++;
+    }
+    GB_CUDA(cudaEventRecord(p->events[e_fin], st));
+    GB_CUDA(cudaStreamSynchronize(st));
+    out->ms_decode = out->ms_syrk = 0.f;
+    for (int64_t c = 0; c < nchunks; c++) {
+        float a = 0.f, b = 0.f;
+        GB_CUDA(cudaEventElapsedTime(&a, p->events[c == 0 ? 0 : 2 * c], p->events[1 + 2 * c]));
+        GB_CUDA(cudaEventElapsedTime(&b, p->events[1 + 2 * c], p->events[2 + 2 * c]));
+        out->ms_decode += a;
+        out->ms_syrk += b;
+    }
+    GB_CUDA(cudaEventElapsedTime(&out->ms_paircount, p->events[2 * nchunks], p->events[e_pc]));
+    GB_CUDA(cudaEventElapsedTime(&out->ms_finalize, p->events[e_pc], p->events[e_fin]));
+    GB_CUDA(cudaEventElapsedTime(&out->ms_total, p->events[0], p->events[e_fin]));
+    out->launches = launches;
+    out->total_missing = p->total_missing;
+    out->row_begin = p->row_begin;
+    out->row_end = p->row_end;
+    p->ran = true;
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_device_results(gcta_b200_plan* p, const float** dA, const int32_t** dN, int64_t* count)
+{
+    if (!p || !p->ran) return GCTA_B200_ERR_ARG;
+    if (dA) *dA = p->d_A_lower;
+    if (dN) *dN = p->total_missing > 0 ? p->d_N_lower : nullptr;
+    if (count) *count = p->band_count;
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_download(gcta_b200_plan* p, gcta_b200_out* out, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && out && out->A_lower, "plan_download: null argument");
+    GB_ARG(p->ran, "plan_download: plan_run has not completed");
+    GB_CUDA(cudaSetDevice(p->device));
+    const int64_t base = p->row_begin * (p->row_begin + 1) / 2;
+    GB_CUDA(cudaMemcpyAsync(out->A_lower + base, p->d_A_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
+    if (out->N_lower && p->total_missing > 0)
+        GB_CUDA(cudaMemcpyAsync(out->N_lower + base, p->d_N_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
+    if (out->mu_out) GB_CUDA(cudaMemcpyAsync(out->mu_out, p->d_mu, (size_t)p->m * 8, cudaMemcpyDeviceToHost, p->stream));
+    if (out->N_lower && p->total_missing == 0) {
+        // nothing missing: N_ij == m for every pair (what grm.cpp:291 yields); fill on the host while the copies run
+        const int nt = (int)std::min<int64_t>(16, std::max<int64_t>(1, p->band_count >> 22));
+        std::vector<std::thread> th;
+        int32_t* dst = out->N_lower + base;
+        const int32_t mval = (int32_t)p->m;
+        for (int t = 0; t < nt; t++)
+            th.emplace_back([=]() {
+                const int64_t lo = p->band_count * t / nt, hi = p->band_count * (t + 1) / nt;
+                std::fill(dst + lo, dst + hi, mval);
+            });
+        for (auto& t : th) t.join();
+    }
+    GB_CUDA(cudaStreamSynchronize(p->stream));
+    out->row_begin = p->row_begin;
+    out->row_end = p->row_end;
+    out->total_missing = p->total_missing;
+    return 0;
+}
+
+extern "C" int gcta_b200_make_grm(const gcta_b200_args* a, gcta_b200_out* out, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(a && out && a->bed && out->A_lower, "make_grm: null argument");
+    gcta_b200_plan* p = nullptr;
+    int rc = gcta_b200_plan_create(a, &p, err, errcap);
+    if (rc) return rc;
+    cudaEvent_t e0, e1, e2, e3;
+    cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2); cudaEventCreate(&e3);
+    cudaEventRecord(e0, p->stream);
+    rc = gcta_b200_plan_upload(p, a->bed, err, errcap);
+    cudaEventRecord(e1, p->stream);
+    if (!rc) rc = gcta_b200_plan_run(p, out, err, errcap);
+    cudaEventRecord(e2, p->stream);
+    if (!rc) rc = gcta_b200_plan_download(p, out, err, errcap);
+    cudaEventRecord(e3, p->stream);
+    cudaEventSynchronize(e3);
+    if (!rc) {
+        cudaEventElapsedTime(&out->ms_h2d, e0, e1);
+        cudaEventElapsedTime(&out->ms_d2h, e2, e3);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
+    gcta_b200_plan_destroy(p);
+    return rc;
+}

@@ -1,0 +1,239 @@
+// syrk.cu - K2: lower-triangle SYRK  S += Z^T Z  on the 5th-generation tensor cores.
+//
+// Replaces the numerator of the reference's triple loop (grm.cpp:276-296):
+//     S_ij = sum_k z_ik * z_jk
+// Z is the 16-bit standardised genotype chunk written by K1, SNP-major [kc_pad][ldz]
+// (rows = SNPs = the contraction axis, columns = individuals), so both MMA operands are
+// "MN-major" tiles of the same matrix and no transpose is ever materialised.
+//
+// One persistent CTA per SM walks a static list of 128x256 output tiles:
+//   warp 0 (one lane) : TMA producer - 6 boxes of [64 SNPs][64 individuals] per stage into a
+//                       4-stage ring of 128B-swizzled shared memory
+//   warp 1 (one lane) : tcgen05.mma issuer - UMMA 128x256x16, kind::f16, FP32 accumulators in
+//                       TMEM, double buffered (2 x 256 columns) so the epilogue of tile t
+//                       overlaps the main loop of tile t+1
+//   warps 2-5         : epilogue - tcgen05.ld the accumulator, add it into the FP32 S tile in
+//                       HBM (S carries the sum over SNP chunks)
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace gb {
+
+constexpr int NUM_STAGES = 4;
+constexpr int GROUP_MN = 64;                                  // individuals per swizzle atom row (128 B)
+constexpr int A_GROUPS = TILE_M / GROUP_MN;                   // 2
+constexpr int B_GROUPS = TILE_N / GROUP_MN;                   // 4
+constexpr int GROUP_BYTES = BLOCK_K * GROUP_MN * 2;           // 8192: [64 k][64 mn] 16-bit
+constexpr int STAGE_BYTES = (A_GROUPS + B_GROUPS) * GROUP_BYTES;  // 49152
+constexpr int SYRK_THREADS = 192;
+constexpr int TMEM_COLS = 512;
+constexpr size_t SYRK_SMEM = (size_t)NUM_STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+// Shared-memory matrix descriptor for an MN-major, 128B-swizzled operand whose 64-individual
+// groups are GROUP_BYTES apart: canonical layout ((8,8,m),(8,k)) : ((1,8,LBO),(64,SBO)) in
+// 16-bit elements, LBO = byte distance between 64-wide MN groups, SBO = byte distance between
+// groups of 8 SNP rows (8 x 128 B).  Bits: [0,14) addr>>4, [16,30) LBO>>4, [32,46) SBO>>4,
+// [46,48) version = 1 (Blackwell), [61,64) layout = 2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t make_mn_desc(uint32_t smem_addr)
+{
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(GROUP_BYTES >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) |
+           (1ull << 46) | (2ull << 61);
+}
+
+__global__ void __launch_bounds__(SYRK_THREADS, 1)
+syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__ tiles, int ntiles, int nkb,
+                  float* __restrict__ S, uint32_t idesc)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = (uint64_t*)(smem + NUM_STAGES * STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + NUM_STAGES;
+    uint64_t* tfull_bar = empty_bar + NUM_STAGES;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_slot = (uint32_t*)(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap);
+        for (int s = 0; s < NUM_STAGES; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int a = 0; a < 2; a++) {
+            mbar_init(&tfull_bar[a], 1);
+            mbar_init(&tempty_bar[a], 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ---------------- TMA producer ----------------
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                const int2 tl = tiles[t];
+                const int row0 = tl.x * TILE_M, col0 = tl.y * TILE_N;
+                for (int kb = 0; kb < nkb; kb++) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* st = smem + stage * STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+#pragma unroll
+                    for (int g = 0; g < A_GROUPS; g++)
+                        tma_load_2d(st + g * GROUP_BYTES, &tmap, &full_bar[stage], row0 + g * GROUP_MN, kb * BLOCK_K);
+#pragma unroll
+                    for (int g = 0; g < B_GROUPS; g++)
+                        tma_load_2d(st + (A_GROUPS + g) * GROUP_BYTES, &tmap, &full_bar[stage], col0 + g * GROUP_MN,
+                                    kb * BLOCK_K);
+                    if (++stage == NUM_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ---------------- MMA issuer ----------------
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+                const int acc = it & 1;
+                const uint32_t acc_phase = (it >> 1) & 1;
+                mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * TILE_N;
+                for (int kb = 0; kb < nkb; kb++) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
+                    const uint64_t a_desc = make_mn_desc(a_addr);
+                    const uint64_t b_desc = make_mn_desc(a_addr + A_GROUPS * GROUP_BYTES);
+#pragma unroll
+                    for (int k4 = 0; k4 < BLOCK_K / 16; k4++) {
+                        // 16 SNPs = two 8-row swizzle atoms = 2048 B further along K
+                        const uint64_t adv = (uint64_t)((k4 * 2048) >> 4);
+                        umma_f16(d_tmem, a_desc + adv, b_desc + adv, idesc, (kb | k4) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
+                    if (++stage == NUM_STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------- epilogue (warps 2..5) ----------------
+        const int q = warp & 3;  // TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;
+        int it = 0;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+            const int acc = it & 1;
+            const uint32_t acc_phase = (it >> 1) & 1;
+            mbar_wait(&tfull_bar[acc], acc_phase);
+            tc_fence_after();
+            float4* Stile = reinterpret_cast<float4*>(S + (size_t)t * (TILE_M * TILE_N));
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TILE_N;
+#pragma unroll 1
+            for (int c0 = 0; c0 < TILE_N; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld_32x32(taddr + c0, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int g = 0; g < 8; g++) {
+                    float4* p = Stile + (size_t)(c0 / 4 + g) * TILE_M + r;
+                    float4 o = *p;
+                    o.x += __uint_as_float(v[4 * g + 0]);
+                    o.y += __uint_as_float(v[4 * g + 1]);
+                    o.z += __uint_as_float(v[4 * g + 2]);
+                    o.w += __uint_as_float(v[4 * g + 3]);
+                    *p = o;
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+}  // namespace gb
+
+extern "C" int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
+                                    int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_Z && d_tiles && d_S, "syrk: null pointer");
+    GB_ARG(ldz > 0 && ldz % TILE_N == 0, "syrk: ldz must be a positive multiple of 256");
+    GB_ARG(kc_pad > 0 && kc_pad % BLOCK_K == 0, "syrk: kc_pad must be a positive multiple of 64");
+    GB_ARG(((uintptr_t)d_Z & 127) == 0, "syrk: Z must be 128-byte aligned");
+    GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "syrk: unknown operand type");
+    if (ntiles == 0) return 0;
+    int dev = 0, sms = 0;
+    GB_CUDA(cudaGetDevice(&dev));
+    GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return set_err(err, errcap, GCTA_B200_ERR_NO_DEVICE, "Error: cuTensorMapEncodeTiled is not available from the driver.");
+
+    CUtensorMap tmap;
+    cuuint64_t gdim[2] = {(cuuint64_t)ldz, (cuuint64_t)kc_pad};
+    cuuint64_t gstride[1] = {(cuuint64_t)ldz * 2};
+    cuuint32_t box[2] = {GROUP_MN, BLOCK_K};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult cr = enc(&tmap, operand == GCTA_B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                      const_cast<void*>(d_Z), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS)
+        return set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: cuTensorMapEncodeTiled failed with code " + std::to_string((int)cr));
+
+    // instruction descriptor (kind::f16): D=F32 [4,6), A fmt [7,10), B fmt [10,13), A MN-major bit 15,
+    // B MN-major bit 16, N>>3 [17,23), M>>4 [24,29)
+    const uint32_t fmt = operand == GCTA_B200_BF16 ? 1u : 0u;
+    const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(TILE_N >> 3) << 17) |
+                           ((uint32_t)(TILE_M >> 4) << 24);
+
+    static bool attr_set[64] = {};
+    if (dev < 64 && !attr_set[dev]) {
+        GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
+        attr_set[dev] = true;
+    }
+    int grid = (int)(ntiles < sms ? ntiles : sms);
+    syrk_tiles_kernel<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, reinterpret_cast<const int2*>(d_tiles),
+                                                                                (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}

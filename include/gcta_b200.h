@@ -1,0 +1,192 @@
+/*
+ * gcta_b200.h - C ABI of the B200-native (sm_100a) replacement for GCTA's `--make-grm` hot path.
+ *
+ * The reference (GCTA 0.93.9, cooljeanius/gcta) has no plugin / FFI interface; the seam this
+ * library fills is the C++ member  void gcta::make_grm(bool grm_xchr_flag, bool output_bin,
+ * int grm_mtd)  (gcta.h:83, defined grm.cpp:219-301, called from option.cpp:620-621).
+ * A maintainer keeps the reference's readers, filters and writers and replaces the body of
+ * make_grm by one call of gcta_b200_make_grm() (see INTEGRATION.md for the stub).
+ *
+ * Conventions
+ *  - plain C types only; no exceptions cross the boundary.  Every function returns 0 on
+ *    success or a non-zero gcta_b200_status and, where an `err` buffer is passed, writes a
+ *    NUL-terminated message into it.  The reference reports errors as throw(std::string)
+ *    caught in main (option.cpp:42-44); the host shim rethrows `err` as std::string.
+ *  - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *    GCTA_B200_ERR_NO_DEVICE.
+ *  - "included SNP k" / "kept individual i" follow the reference's _include / _keep index
+ *    lists (gcta.h:216-238): ascending indices into the .bim / .fam order.
+ *  - the packed lower triangle uses the .grm.gz line order  idx(i,j) = i(i+1)/2 + j, j <= i
+ *    (grm.cpp:328-330).
+ */
+#ifndef GCTA_B200_H
+#define GCTA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    GCTA_B200_OK = 0,
+    GCTA_B200_ERR_ARG = 1,       /* bad argument (message says which) */
+    GCTA_B200_ERR_NO_DEVICE = 2, /* no usable CUDA device / driver */
+    GCTA_B200_ERR_CUDA = 3,      /* a CUDA call or kernel failed */
+    GCTA_B200_ERR_NOMEM = 4      /* device or pinned-host allocation failed */
+} gcta_b200_status;
+
+/* operand type of the standardised genotypes fed to the tensor cores (FP32 accumulate). */
+typedef enum {
+    GCTA_B200_FP16 = 0, /* default: 11-bit significand, |z| <= 65504 (MAF >= 1e-9) */
+    GCTA_B200_BF16 = 1
+} gcta_b200_operand;
+
+/* ------------------------------------------------------------------------------------------
+ * Whole-path entry point: replaces the body of gcta::make_grm (grm.cpp:219-301) up to, but
+ * not including, output_grm_vec (grm.cpp:303-341).  Host pointers in, host pointers out.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct {
+    /* .bed payload after the 3 magic bytes (data.cpp:164 skips them unchecked): m_file rows of
+     * ceil(n_file/4) bytes, SNP-major, 2 bits per individual LSB first (data.cpp:171-185). */
+    const uint8_t* bed;
+    int64_t n_file;         /* individuals in the .fam  (_indi_num) */
+    int64_t m_file;         /* SNPs in the .bim         (_snp_num)  */
+    const int32_t* keep;    /* _keep: ascending file indices of kept individuals, NULL = all */
+    int64_t n;              /* number kept (n_file when keep == NULL) */
+    const int32_t* include; /* _include: ascending file indices of included SNPs, NULL = all */
+    int64_t m;              /* number included (m_file when include == NULL) */
+    const double* mu;       /* per included SNP 2p, as --update-freq leaves _mu (data.cpp:915-916);
+                               NULL = compute like calcu_mu (data.cpp:759-803) */
+    const int32_t* sex;     /* per FILE individual, 1 = male 2 = female (_sex); only read when xchr */
+    int32_t xchr;           /* grm_xchr_flag: sex-weighted mu, male rows * sqrt(0.5) (data.cpp:1045-1055) */
+    int32_t alg;            /* grm_mtd: 0 default, 1 = --grm-alg 1 (grm.cpp:230-237) */
+    int32_t operand;        /* gcta_b200_operand */
+    int32_t device;         /* CUDA device ordinal */
+    int32_t part_rank;      /* this call computes row band part_rank of part_world (0 / 1 = everything) */
+    int32_t part_world;
+    int64_t chunk_snps;     /* SNPs standardised per pass, 0 = choose from free HBM */
+} gcta_b200_args;
+
+typedef struct {
+    /* caller-allocated; the call fills rows [row_begin, row_end) of the packed lower triangle,
+     * i.e. elements [row_begin(row_begin+1)/2, row_end(row_end+1)/2), and leaves the rest alone. */
+    float* A_lower;          /* A_ij, grm.cpp:273-275, 294 */
+    int32_t* N_lower;        /* A_N_ij, grm.cpp:270, 291; may be NULL (--make-grm-bin drops N, grm.cpp:307-318) */
+    double* mu_out;          /* [m] 2p per included SNP, may be NULL */
+    int64_t row_begin, row_end; /* written by the call */
+    int64_t total_missing;   /* number of missing genotypes among kept x included */
+    /* device-side milliseconds (CUDA events on the compute stream) */
+    float ms_h2d, ms_decode, ms_syrk, ms_paircount, ms_finalize, ms_d2h, ms_total;
+    int32_t launches;        /* kernels of this library launched by the call */
+} gcta_b200_out;
+
+int gcta_b200_make_grm(const gcta_b200_args* args, gcta_b200_out* out, char* err, size_t errcap);
+
+/* ------------------------------------------------------------------------------------------
+ * Plan API: the same path split into upload / compute / download so that a caller (bench.py,
+ * a pipelined host) can keep the packed genotypes resident in HBM and time the phases.
+ * gcta_b200_make_grm() is plan_create + upload + run + download + destroy.
+ * All device memory, streams and events are owned by the plan.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct gcta_b200_plan gcta_b200_plan;
+
+int gcta_b200_plan_create(const gcta_b200_args* args, gcta_b200_plan** plan, char* err, size_t errcap);
+/* copy args->bed (pageable or pinned host memory) into the plan's pitched HBM buffer */
+int gcta_b200_plan_upload(gcta_b200_plan* plan, const uint8_t* bed_host, char* err, size_t errcap);
+/* fill the HBM genotype buffer on the device from the counter-based generator of
+ * gcta_b200/synth.py (thr = uint32[m_file][4] thresholds in HOST memory); bench/test use only */
+int gcta_b200_plan_synth(gcta_b200_plan* plan, uint64_t seed, const uint32_t* thr_host, char* err, size_t errcap);
+/* decode + SYRK + pair counts + finalize on the device; results stay in HBM */
+int gcta_b200_plan_run(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size_t errcap);
+/* copy this plan's row band of A (and N when N_lower != NULL) to host memory */
+int gcta_b200_plan_download(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size_t errcap);
+/* device pointers of the finalised band (float A, int32 N; N is NULL when nothing is missing
+ * and N == m everywhere), valid until destroy */
+int gcta_b200_plan_device_results(gcta_b200_plan* plan, const float** dA, const int32_t** dN, int64_t* count);
+void gcta_b200_plan_destroy(gcta_b200_plan* plan);
+
+/* ------------------------------------------------------------------------------------------
+ * Kernel-level entry points (device pointers, caller's stream as void* = cudaStream_t).
+ * Used by the parity tests to check each stage against the oracle.
+ * ---------------------------------------------------------------------------------------- */
+
+/* K1 - fused 2-bit decode + per-SNP allele frequency + standardisation.
+ * Replaces read_bedfile's unpack (data.cpp:171-185), mu_func (data.cpp:781-803), make_XMat
+ * (data.cpp:1001-1007) and std_XMat (data.cpp:1030-1043) for included SNPs [k0, k0+kc).
+ *   d_bed      pitched packed genotypes, row r at d_bed + r*pitch, pitch % 16 == 0
+ *   d_keepmask uint32[pitch/4]: bit 2t of word w set iff file individual 16w+t is kept
+ *   d_keep     int32[n] or NULL when every file individual is kept (then n == n_file)
+ *   d_sexmale  uint32[pitch/4] like d_keepmask, set for kept males; NULL unless xchr
+ *   d_include  int32[>= k0+kc] file row of each included SNP, NULL = identity
+ *   d_mu_in    double[>= k0+kc] override of 2p, or NULL
+ *   d_Z        out: 16-bit standardised genotypes, SNP-major [kc_pad][ldz], kc_pad = kc rounded
+ *              up to 64, ldz % 256 == 0 and ldz >= n; padding rows / columns are written as 0
+ *   d_mu, d_cnt, d_sum, d_zlut   out, indexed by included SNP k (absolute): 2p, non-missing
+ *              count, allele-1 dosage sum, and float[8] = z for codes 0..3 (female/autosome)
+ *              then codes 0..3 (male, xchr only)
+ *   d_total_missing  uint64 accumulator (+= missing genotypes of these SNPs) */
+int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
+                         const uint32_t* d_keepmask, const int32_t* d_keep, int64_t n,
+                         const uint32_t* d_sexmale, const int32_t* d_include, int64_t k0, int64_t kc,
+                         const double* d_mu_in, int32_t xchr, int32_t alg, int32_t operand,
+                         void* d_Z, int64_t ldz,
+                         double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
+                         unsigned long long* d_total_missing, void* stream, char* err, size_t errcap);
+
+/* K1d - exact per-individual diagonal: diag[f] += sum_k z_fk^2 in float64 and nii[f] += number
+ * of non-missing SNPs, over included SNPs [k0, k0+kc), per FILE individual f (grm.cpp:265-275). */
+int gcta_b200_diag_accum(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
+                         const uint32_t* d_sexmale, const int32_t* d_include, int64_t k0, int64_t kc,
+                         const float* d_zlut, double* d_diag, int32_t* d_nii,
+                         void* stream, char* err, size_t errcap);
+
+/* K1m - missingness bit planes for K3: d_miss[w][i] (uint32, i < ldm) has bit b set iff kept
+ * individual i is NON-missing at included SNP 32*w + b; w in [k0/32, (k0+kc)/32) (k0 % 32 == 0). */
+int gcta_b200_nonmiss_planes(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
+                             const int32_t* d_keep, int64_t n, const int32_t* d_include,
+                             int64_t k0, int64_t kc, uint32_t* d_planes, int64_t ldm,
+                             void* stream, char* err, size_t errcap);
+
+/* K2 - lower-triangle SYRK  S += Z^T Z  on tcgen05 tensor cores (grm.cpp:276-296 numerator).
+ * Tiles: 128 rows x 256 columns of S.  d_tiles = int32[ntiles][2] (row block, column block);
+ * tile t of the list is stored at d_S + t*128*256 floats in the layout
+ * [col/4][row][col%4] (see gcta_b200_s_tile_index).  S must be zeroed by the caller before
+ * the first chunk. */
+int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand,
+                         const int32_t* d_tiles, int64_t ntiles, float* d_S,
+                         void* stream, char* err, size_t errcap);
+
+/* K3 - bit-exact pair counts N_ij = sum_k ok_ik ok_jk by AND + popc over the K1m bit planes
+ * (grm.cpp:291), accumulated into int32 tiles laid out like K2's S tiles. */
+int gcta_b200_paircount_tiles(const uint32_t* d_planes, int64_t ldm, int64_t nwords,
+                              const int32_t* d_tiles, int64_t ntiles, int32_t* d_Ntiles,
+                              void* stream, char* err, size_t errcap);
+
+/* K4 - A = S / N with the reference's zero-count rules (grm.cpp:273-275, 294), exact diagonal
+ * from K1d, packed to .grm.gz order.  d_Ntiles NULL means N == m_const for every pair. */
+int gcta_b200_finalize_tiles(const float* d_S, const int32_t* d_Ntiles, int32_t m_const,
+                             const int32_t* d_tiles, int64_t ntiles, int64_t n,
+                             const int32_t* d_keep, const double* d_diag, const int32_t* d_nii,
+                             int64_t row_begin, int64_t row_end,
+                             float* d_A_lower, int32_t* d_N_lower,
+                             void* stream, char* err, size_t errcap);
+
+/* index of element (r, c), r < 128, c < 256, inside one S / N tile */
+static inline int64_t gcta_b200_s_tile_index(int r, int c) { return ((int64_t)(c >> 2) * 128 + r) * 4 + (c & 3); }
+
+/* helpers */
+const char* gcta_b200_version(void);
+int gcta_b200_device_count(void); /* 0 when no driver / device */
+/* row band [row_begin,row_end) owned by part_rank of part_world for n kept individuals
+ * (boundaries are multiples of 128, bands balanced by tile count) */
+int gcta_b200_partition(int64_t n, int32_t part_rank, int32_t part_world, int64_t* row_begin, int64_t* row_end);
+/* number of 128x256 tiles of band [row_begin,row_end) and, when tiles != NULL, the list in
+ * launch order (int32[count][2]) */
+int64_t gcta_b200_tile_list(int64_t n, int64_t row_begin, int64_t row_end, int32_t* tiles);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GCTA_B200_H */

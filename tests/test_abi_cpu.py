@@ -1,0 +1,74 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every symbol the header declares,
+its host-only helpers (row-band partition, tile list) are right, and compute entry points fail
+loudly - with the reference's error-string convention - when there is no CUDA device."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from gcta_b200 import abi, synth
+from tests.helpers import ROOT
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "gcta_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gcta_b200_[a-z0-9_]+)\s*\(", src)) - {"gcta_b200_s_tile_index"})
+
+
+def test_library_exports_every_declared_symbol():
+    L = abi.lib()
+    names = _declared()
+    assert len(names) >= 18
+    for nme in names:
+        assert hasattr(L, nme), f"{nme} declared in include/gcta_b200.h but not exported"
+    assert sorted(abi.EXPORTS) == [x for x in names if x in abi.EXPORTS]
+    assert b"sm_100a" in L.gcta_b200_version()
+
+
+@pytest.mark.parametrize("n", [1, 127, 128, 129, 256, 257, 1000, 5000])
+def test_tile_list_covers_lower_triangle_once(n):
+    t = abi.tile_list(n)
+    assert len({tuple(x) for x in t}) == len(t)
+    n_pad = (n + 255) // 256 * 256
+    cov = np.zeros((n_pad + 128, n_pad), dtype=np.int32)
+    for bi, bj in t:
+        assert bi * 128 < n and bj * 256 < n
+        cov[bi * 128:(bi + 1) * 128, bj * 256:(bj + 1) * 256] += 1
+    ii, jj = np.tril_indices(n)
+    assert (cov[ii, jj] == 1).all()
+    # no tile lies entirely above the diagonal
+    for bi, bj in t:
+        assert min(bi * 128 + 127, n - 1) >= bj * 256
+
+
+@pytest.mark.parametrize("n,world", [(50000, 8), (10000, 4), (2000, 2), (300, 8), (100, 3)])
+def test_partition_bands_are_contiguous_and_balanced(n, world):
+    bands = [abi.partition(n, r, world) for r in range(world)]
+    assert bands[0][0] == 0 and bands[-1][1] == n
+    for (b0, e0), (b1, e1) in zip(bands, bands[1:]):
+        assert e0 == b1 and b0 <= e0
+    counts = [len(abi.tile_list(n, b, e)) for b, e in bands if e > b]
+    assert sum(counts) == len(abi.tile_list(n))
+    if n >= 10000:
+        assert max(counts) <= 1.05 * (sum(counts) / world) + 64
+    # all boundaries except the last are multiples of the tile height
+    assert all(b % 128 == 0 for b, e in bands if e > b)
+
+
+def test_no_cpu_fallback():
+    if abi.lib().gcta_b200_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    bed = synth.make_bed_payload(1, 40, 50)
+    with pytest.raises(abi.GctaB200Error) as e:
+        abi.make_grm(bed, 40, 50)
+    assert e.value.code == 2 and "no CUDA device" in str(e.value)
+
+
+def test_argument_errors_use_reference_messages():
+    bed = synth.make_bed_payload(1, 40, 50)
+    with pytest.raises(abi.GctaB200Error) as e:
+        abi.make_grm(bed, 40, 50, include=np.array([], dtype=np.int32))
+    assert str(e.value) == "Error: No SNP is retained for analysis."  # data.cpp:149

@@ -1,0 +1,132 @@
+"""Whole-path parity (GPU) through gcta_b200_make_grm / the plan API against the reference.
+
+Tolerances are the north-star's: N_ij bit-exact, max|dA| <= 1e-3, |mean diag delta| <= 1e-5.
+Golden fixtures are outputs of the compiled, unmodified reference (tests/golden/).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from gcta_b200 import abi, grmio, synth
+from oracle import oracle
+from tests.helpers import GOLDEN, check_grm, load_plink, pack_lower
+
+pytestmark = pytest.mark.gpu
+
+
+def _names(path):
+    return [ln.split()[0] for ln in open(path) if ln.strip()]
+
+
+@pytest.mark.parametrize("case,txt,binf,kw", [
+    ("g1_basic", "o", "ob", {}),
+    ("g2_edge", "o", "ob", {}),
+    ("g4_xchr", "o", "ob", {"xchr": 1}),
+    ("g5_subset", "o", "ob", {"subset": True}),
+    ("g7_nomiss", "o", "ob", {}),
+])
+@pytest.mark.parametrize("operand", [abi.FP16, abi.BF16])
+def test_golden(case, txt, binf, kw, operand):
+    d = os.path.join(GOLDEN, case)
+    bed, n, m, chrom, sex, snps, ids = load_plink(d + "/t")
+    keep = include = None
+    if kw.get("subset"):
+        kn = set(_names(d + "/keep.txt"))
+        keep = np.array([i for i, (f, _) in enumerate(ids) if f in kn], dtype=np.int32)
+        en = set(_names(d + "/extract.txt"))
+        include = np.array([k for k, s in enumerate(snps) if s in en], dtype=np.int32)
+    A, N, mu, out = abi.make_grm(bed, n, m, keep=keep, include=include, sex=sex, xchr=kw.get("xchr", 0), operand=operand)
+    Aref = pack_lower(grmio.read_grm_bin(f"{d}/{binf}.grm.bin"))
+    _, Nref, _ = grmio.read_grm_gz(f"{d}/{txt}.grm.gz")
+    # BF16 operands carry 8 significand bits: the diagonal is exact anyway (float64 side sum), off-diagonals need the looser bar
+    check_grm(A, N, Aref, Nref, atol=1e-3 if operand == abi.FP16 else 4e-3)
+    assert out.launches > 0
+
+
+def test_update_freq_sub_block():
+    d = os.path.join(GOLDEN, "g5_subset")
+    bed, n, m, chrom, sex, snps, ids = load_plink(d + "/t")
+    kn = set(_names(d + "/keep.txt"))
+    keep = np.array([i for i, (f, _) in enumerate(ids) if f in kn], dtype=np.int32)
+    freq = np.array([float(ln.split()[2]) for ln in open(d + "/full.freq")])
+    A, N, mu, _ = abi.make_grm(bed, n, m, keep=keep, mu=2.0 * freq)
+    Aref = pack_lower(grmio.read_grm_bin(d + "/ob_uf.grm.bin"))
+    assert np.abs(A - Aref).max() <= 1e-3
+    assert np.array_equal(mu, 2.0 * freq)
+
+
+def test_chunked_equals_single_pass_and_bands_tile_the_triangle():
+    n, m = 700, 1500
+    bed = synth.make_bed_payload(42, n, m, miss_rate=0.02)
+    A0, N0, mu0, _ = abi.make_grm(bed, n, m)
+    A1, N1, mu1, _ = abi.make_grm(bed, n, m, chunk_snps=256)  # 6 chunks accumulate into S
+    assert np.array_equal(N0, N1) and np.array_equal(mu0, mu1)
+    assert np.abs(A0 - A1).max() < 1e-5
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n)
+    check_grm(A0, N0, pack_lower(Aref), pack_lower(Nref))
+    # 3 row bands (the multi-GPU partition) written into one buffer reproduce the whole triangle
+    A = np.full(n * (n + 1) // 2, np.nan, dtype=np.float32)
+    N = np.full(n * (n + 1) // 2, -1, dtype=np.int32)
+    covered = 0
+    for r in range(3):
+        with abi.Plan(n, m, part_rank=r, part_world=3) as p:
+            p.upload(bed)
+            o = p.run()
+            p.download(A, N)
+            covered += o.row_end - o.row_begin
+    assert covered == n
+    assert np.array_equal(A, A0) and np.array_equal(N, N0)
+
+
+def test_device_generator_matches_numpy_generator():
+    n, m = 515, 333
+    thr = synth.snp_thresholds(9, m, miss_rate=0.03)
+    bed = synth.make_bed_payload(9, n, m, miss_rate=0.03)
+    A0, N0, mu0, _ = abi.make_grm(bed, n, m)
+    A = np.zeros_like(A0)
+    N = np.zeros_like(N0)
+    mu = np.zeros_like(mu0)
+    with abi.Plan(n, m) as p:
+        p.synth(9, thr)
+        p.run()
+        p.download(A, N, mu)
+    assert np.array_equal(mu, mu0) and np.array_equal(N, N0) and np.array_equal(A, A0)
+
+
+def test_config1_shape_no_missing():
+    """BASELINE config 1 (n=2000, M=50000, no missing): N == M everywhere, A within tolerance."""
+    n, m = 2000, 50000
+    bed = synth.make_bed_payload(1235, n, m)
+    A, N, mu, out = abi.make_grm(bed, n, m)
+    assert out.total_missing == 0 and (N == m).all()
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n)
+    dA, dd = check_grm(A, N, pack_lower(Aref), pack_lower(Nref))
+    print(f"config1: max|dA|={dA:.3e} diag-mean delta={dd:.3e} syrk {out.ms_syrk:.2f} ms decode {out.ms_decode:.2f} ms")
+
+
+def test_larger_with_missing_sub_block_check():
+    """n=6000 x M=20000, 2 % missing, multi-tile persistent schedule (1128 tiles > 148 SMs).
+    Oracle on a sub-block of individuals with the full-sample mu (SURVEY.md 8c identity)."""
+    n, m = 6000, 20000
+    bed = synth.make_bed_payload(77, n, m, miss_rate=0.02)
+    A, N, mu, out = abi.make_grm(bed, n, m)
+    assert out.total_missing > 0
+    rng = np.random.default_rng(1)
+    sub = np.sort(rng.choice(n, 500, replace=False))
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n, keep=sub, mu=mu)
+    ii, jj = np.tril_indices(len(sub))
+    gi, gj = sub[ii], sub[jj]
+    idx = gi.astype(np.int64) * (gi + 1) // 2 + gj
+    check_grm(A[idx], N[idx], Aref[ii, jj], Nref[ii, jj])
+    mu_ref, _, _ = oracle.snp_mu(bed[:200], n)
+    assert np.array_equal(mu[:200], mu_ref)
+
+
+def test_errors_are_reported_not_thrown():
+    bed = synth.make_bed_payload(1, 40, 50)
+    with pytest.raises(abi.GctaB200Error) as e:
+        abi.make_grm(bed, 40, 50, keep=np.array([], dtype=np.int32))
+    assert "No individual is retained" in str(e.value)
+    with pytest.raises(abi.GctaB200Error):
+        abi.make_grm(bed, 40, 50, xchr=1, sex=np.zeros(40, dtype=np.int32))
