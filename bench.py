@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""bench.py - GRM pair.SNP/s of the --make-grm hot path on B200 ("Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n N --m M --miss R]
+
+One step = one pass of the whole device path (decode + SYRK + [pair counts] + finalize) over
+the synthetic workload.  Default workload = BASELINE.json configs[2], the configuration the
+metric is quoted on: n=50,000 x M=1,000,000, MAF U(0.01,0.5), no missing genotypes.  With N>1
+(launched by torchrun, one rank per GPU) the SAME problem is split into N row bands of the
+lower triangle (strong scaling, no data-path collective); value = total pair.SNP / max-over-ranks
+device time.  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "grm_pair_snp_per_s"
+UNIT = "pair*SNP/s"
+SEED = 1236  # 1234 + config index
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops_sustained", 1384.3), d.get("bf16_tflops", 1650.6), d.get("hbm_gbs", 6546.2), "measured"
+    return 1400.0, 1590.0, 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference_sample(n_s, m_s, miss, seed, workdir):
+    """Time the compiled, unmodified reference (oracle/_ref/gcta_ref, single thread) on an
+    n_s x m_s sample of the workload.  -> (pair.SNP/s, seconds, cores)."""
+    from gcta_b200 import synth
+    from oracle import oracle
+    if not oracle.have_ref():
+        raise RuntimeError("oracle/_ref/gcta_ref is not built")
+    bed = synth.make_bed_payload(seed, n_s, m_s, miss_rate=miss)
+    synth.write_plink(os.path.join(workdir, "s"), bed, n_s)
+    t0 = time.perf_counter()
+    r = oracle.run_ref(["--bfile", "s", "--make-grm-bin", "--out", "o"], cwd=workdir)
+    dt = time.perf_counter() - t0
+    if "Analysis finished" not in r.stdout or not os.path.exists(os.path.join(workdir, "o.grm.bin")):
+        raise RuntimeError("reference run failed: " + r.stderr[-300:])
+    return n_s * (n_s + 1) / 2 * m_s / dt, dt, 1
+
+
+def main_reference(a, rank, world):
+    if rank != 0:
+        return
+    n_s, m_s = a.ref_n, a.ref_m
+    vals, secs = [], []
+    with tempfile.TemporaryDirectory() as d:
+        for i in range(a.warmup + a.steps):
+            v, dt, cores = run_reference_sample(n_s, m_s, a.miss, SEED, d)
+            if i >= a.warmup:
+                vals.append(v); secs.append(dt)
+    total = n_s * (n_s + 1) / 2 * m_s * len(vals)
+    value = total / sum(secs)
+    sample = f"n={n_s} x M={m_s} sub-sample of the workload (same generator, seed {SEED}); rate of the O(n^2 M) loop is scale-free"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": 1e3 * sum(secs) / len(secs), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"synthetic .bed n={a.n} x M={a.m}, miss={a.miss}, --make-grm (BASELINE configs[2])", "timed_sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def main_ours(a, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from gcta_b200 import abi, synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - gcta_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    n, m = a.n, a.m
+    pairs_total = n * (n + 1) / 2
+    thr = synth.snp_thresholds(SEED, m, miss_rate=a.miss)
+    plan = abi.Plan(n, m, device=local_rank, part_rank=rank, part_world=world, operand=abi.BF16 if a.operand == "bf16" else abi.FP16)
+    plan.synth(SEED, thr)  # synthetic genotypes generated in HBM (untimed set-up)
+
+    # ---------------- device-resident throughput ("value") ----------------
+    for _ in range(a.warmup):
+        plan.run()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    dev_ms = syrk_ms = dec_ms = pc_ms = fin_ms = 0.0
+    launches = 0
+    for _ in range(a.steps):
+        o = plan.run()
+        dev_ms += o.ms_total; syrk_ms += o.ms_syrk; dec_ms += o.ms_decode; pc_ms += o.ms_paircount; fin_ms += o.ms_finalize
+        launches += o.launches
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+    row_begin, row_end = o.row_begin, o.row_end
+    band_pairs = row_end * (row_end + 1) / 2 - row_begin * (row_begin + 1) / 2
+    dev_ms_max = max_over_ranks(dev_ms)
+    wall_ms_max = max_over_ranks(wall_ms)
+    launches_total = int(sum_over_ranks(launches))
+    value = pairs_total * m * a.steps / (dev_ms_max * 1e-3)
+
+    # roofline of the dominant kernel (K2, tensor bound): algorithmic flops of this rank's band / K2 device time
+    sust, burst, hbm, which = peaks()
+    syrk_tflops = 2.0 * band_pairs * m * a.steps / (syrk_ms * 1e-3) / 1e12 if syrk_ms > 0 else 0.0
+    syrk_tflops_min = -max_over_ranks(-syrk_tflops)
+    nchunks = -(-m // max(1, plan_chunk(plan, n, m)))
+    # K1 (HBM bound) for reference: packed read + 16-bit Z write (+ diag re-read), SURVEY.md 8d
+    ldz = (n + 255) // 256 * 256
+    k1_bytes = m * ((n + 3) // 4 * 2 + 2 * ldz)
+
+    # ---------------- end to end through the C ABI with host buffers ("e2e") ----------------
+    e2e = None
+    if not a.no_e2e:
+        stride = (n + 3) // 4
+        h_bed = torch.empty(stride * m, dtype=torch.uint8, pin_memory=True)
+        plan.download_bed(h_bed.data_ptr())
+        base = row_begin * (row_begin + 1) // 2
+        cnt = int(band_pairs)
+        h_A = torch.empty(max(cnt, 1), dtype=torch.float32, pin_memory=True)
+        h_N = np.empty(max(cnt, 1), dtype=np.int32)
+        A_ptr = h_A.data_ptr() - 4 * base  # the ABI indexes the whole packed triangle; only the band is touched
+        N_ptr = h_N.ctypes.data - 4 * base
+        e2e_steps = max(1, min(a.steps, a.e2e_steps))
+        for _ in range(1):
+            plan.upload(h_bed.data_ptr()); plan.run(); plan.download(A_ptr, N_ptr)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            plan.upload(h_bed.data_ptr())
+            plan.run()
+            plan.download(A_ptr, N_ptr)
+        barrier()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        d2h = sum_over_ranks(cnt * 4 * (2 if o.total_missing > 0 else 1))
+        e2e = {"value": pairs_total * m * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(stride * m * world),
+               "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
+               "api": "gcta_b200_plan_upload + plan_run + plan_download (what gcta_b200_make_grm does), pinned host buffers"}
+        if rank == 0:
+            diag_idx = np.arange(min(1000, row_end - row_begin))
+            di = (diag_idx + row_begin) * (diag_idx + row_begin + 1) // 2 + diag_idx + row_begin - base
+            e2e["diag_mean_check"] = float(h_A.numpy()[di].mean())
+
+    line = None
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dev_ms_max / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": a.operand + " operands, f32 accumulate", "data": "synthetic",
+            "config": {"workload": f"synthetic .bed n={n} x M={m}, MAF U(0.01,0.5), miss={a.miss}, --make-grm (BASELINE configs[2])",
+                       "partition": f"{world} row band(s) of the lower triangle, packed genotypes replicated per GPU",
+                       "l2": "inputs (packed bed + Z chunks) far larger than the 126 MB L2; no flush needed",
+                       "timing": "CUDA events on the plan's stream, max over ranks"},
+            "tflops": 2 * value / 1e12, "wall_ms_per_step": wall_ms_max / a.steps,
+            "phases_ms_per_step_rank0": {"decode+diag": dec_ms / a.steps, "syrk": syrk_ms / a.steps, "paircount": pc_ms / a.steps,
+                                         "finalize": fin_ms / a.steps},
+            "roofline": {"kernel": "syrk_tiles_kernel (K2)", "bound": "tensor", "achieved": syrk_tflops_min, "peak": sust, "unit": "TFLOP/s",
+                         "frac": syrk_tflops_min / sust, "frac_of_burst_peak": syrk_tflops_min / burst, "peak_source": which + " (sustained bf16, kernel timed inside a long step)",
+                         "traffic": None, "launches_per_step": nchunks,
+                         "k1_decode_GBps": k1_bytes / (dec_ms / a.steps * 1e-3) / 1e9 if dec_ms > 0 else None, "hbm_peak_GBps": hbm},
+            "clocks": clocks, "gpu_launches": launches_total,
+        }
+        if e2e:
+            line["e2e"] = e2e
+    # CPU baseline: the compiled reference on a bounded sample, rank 0 at N=1 only
+    if rank == 0 and world == 1 and not a.no_cpu:
+        try:
+            with tempfile.TemporaryDirectory() as d:
+                v, dt, cores = run_reference_sample(a.ref_n, a.ref_m, a.miss, SEED, d)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "seconds": dt,
+                                    "sample": f"oracle/_ref/gcta_ref --make-grm-bin on n={a.ref_n} x M={a.ref_m} of the same generator (single thread: the reference has no threading)"}
+        except Exception as ex:  # noqa: BLE001
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 1, "kind": "reference", "sample": f"failed: {ex}"}
+    if rank == 0:
+        print(json.dumps(line))
+    plan.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def plan_chunk(plan, n, m):
+    """SNPs per chunk the plan chose (mirrors plan.cu: <= 8 GiB of Z)."""
+    ldz = (n + 255) // 256 * 256
+    kc = (8 << 30) // (ldz * 2) // 64 * 64
+    return max(64, min(kc, (m + 63) // 64 * 64))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=50000)
+    ap.add_argument("--m", type=int, default=1000000)
+    ap.add_argument("--miss", type=float, default=0.0)
+    ap.add_argument("--operand", default="fp16", choices=["fp16", "bf16"])
+    ap.add_argument("--ref-n", type=int, default=600, help="individuals in the CPU reference sample")
+    ap.add_argument("--ref-m", type=int, default=20000, help="SNPs in the CPU reference sample")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if a.impl == "reference":
+        main_reference(a, rank, world)
+    else:
+        main_ours(a, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -17,7 +17,7 @@ ERRCAP = 512
 TILE_M, TILE_N = 128, 256
 
 EXPORTS = [
-    "gcta_b200_make_grm", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth",
+    "gcta_b200_make_grm", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth", "gcta_b200_plan_download_bed",
     "gcta_b200_plan_run", "gcta_b200_plan_download", "gcta_b200_plan_device_results", "gcta_b200_plan_destroy",
     "gcta_b200_bed_decode", "gcta_b200_diag_accum", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles",
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
@@ -163,6 +163,10 @@ class Plan:
         thr = np.ascontiguousarray(thr, dtype=np.uint32)
         err = C.create_string_buffer(ERRCAP)
         _check(lib().gcta_b200_plan_synth(self._h, C.c_uint64(seed), C.c_void_p(thr.ctypes.data), err, ERRCAP), err)
+
+    def download_bed(self, bed_host):
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_plan_download_bed(self._h, C.c_void_p(_ptr(bed_host)), err, ERRCAP), err)
 
     def run(self):
         err = C.create_string_buffer(ERRCAP)

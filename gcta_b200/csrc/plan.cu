@@ -265,6 +265,17 @@ extern "C" int gcta_b200_plan_upload(gcta_b200_plan* p, const uint8_t* bed_host,
     return 0;
 }
 
+extern "C" int gcta_b200_plan_download_bed(gcta_b200_plan* p, uint8_t* bed_host, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && bed_host, "plan_download_bed: null argument");
+    GB_CUDA(cudaSetDevice(p->device));
+    GB_CUDA(cudaMemcpy2DAsync(bed_host, (size_t)p->stride, p->d_bed, (size_t)p->pitch, (size_t)p->stride, (size_t)p->m_file,
+                              cudaMemcpyDeviceToHost, p->stream));
+    GB_CUDA(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
 namespace gb {
 __device__ __forceinline__ uint64_t mix64(uint64_t x)
 {

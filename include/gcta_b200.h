@@ -98,6 +98,9 @@ int gcta_b200_plan_upload(gcta_b200_plan* plan, const uint8_t* bed_host, char* e
 /* fill the HBM genotype buffer on the device from the counter-based generator of
  * gcta_b200/synth.py (thr = uint32[m_file][4] thresholds in HOST memory); bench/test use only */
 int gcta_b200_plan_synth(gcta_b200_plan* plan, uint64_t seed, const uint32_t* thr_host, char* err, size_t errcap);
+/* inverse of plan_upload: copy the plan's HBM genotype buffer to host memory in .bed payload layout
+ * (bench/test use: obtain the host copy of a device-generated data set) */
+int gcta_b200_plan_download_bed(gcta_b200_plan* plan, uint8_t* bed_host, char* err, size_t errcap);
 /* decode + SYRK + pair counts + finalize on the device; results stay in HBM */
 int gcta_b200_plan_run(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size_t errcap);
 /* copy this plan's row band of A (and N when N_lower != NULL) to host memory */
