@@ -379,3 +379,107 @@ extern "C" int gcta_b200_nonmiss_planes(const uint8_t* d_bed, int64_t pitch, int
     GB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ================================================================================================
+// Allocation-free variant of K1d (no counterpart in the reference; see include/gcta_b200.h).
+//
+// gcta_b200_diag_accum needs a per-SNP table of standardised values (8 floats per SNP) that
+// some earlier step has to place in device memory; in the plan that table is cudaMalloc'ed.
+// Some hosts cannot do that: an engine that reserved all of HBM for its own pool at start-up,
+// or a service loop that must never enter the CUDA allocator because cudaMalloc/cudaFree
+// synchronise the whole device.  For them the table lives in the fixed array below, which is
+// part of the library image: every GPU that loads libgcta_b200.so carries these 16 MiB until
+// the process exits, whether or not the entry point is ever called.
+// ================================================================================================
+namespace gb {
+
+constexpr int64_t STATIC_LUT_MAX_SNPS = 524288;  // per call; 524288 SNPs x 8 floats = 16 MiB
+static __device__ __align__(256) float g_static_zlut[STATIC_LUT_MAX_SNPS * 8];
+
+// one warp per SNP: allele counts of the kept individuals -> 2p -> the 4 standardised values,
+// written to lut[(k - k0) * 8 ..] in the layout diag_accum_kernel reads (autosomes only, so
+// the "male" half repeats the first).  Same arithmetic as bed_decode_kernel's per-SNP block.
+__global__ void __launch_bounds__(256) snp_lut_kernel(const uint8_t* __restrict__ bed, int64_t pitch,
+                                                       const uint32_t* __restrict__ keepmask,
+                                                       const int32_t* __restrict__ include, int64_t k0, int64_t kc,
+                                                       float* __restrict__ lut)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t kk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (kk >= kc) return;
+    const int64_t k = k0 + kk;
+    const uint4* row16 = reinterpret_cast<const uint4*>(bed + (int64_t)(include ? include[k] : (int32_t)k) * pitch);
+    const uint4* km16 = reinterpret_cast<const uint4*>(keepmask);
+    SnpCounts c = {0, 0, 0, 0};
+    for (int v = lane; v < (int)(pitch / 16); v += 32) {
+        const uint4 w = __ldg(row16 + v), km = __ldg(km16 + v);
+        count_word<false>(w.x, km.x, 0u, c);
+        count_word<false>(w.y, km.y, 0u, c);
+        count_word<false>(w.z, km.z, 0u, c);
+        count_word<false>(w.w, km.w, 0u, c);
+    }
+    c.cnt = warp_sum(c.cnt);
+    c.sum = warp_sum(c.sum);
+    if (lane != 0) return;
+    const double mu = c.cnt > 0 ? __ddiv_rn((double)c.sum, (double)c.cnt) : 0.0;
+    const double var = __dmul_rn(mu, __dsub_rn(1.0, __dmul_rn(0.5, mu)));
+    const double isd = fabs(var) < 1.0e-50 ? 0.0 : __dsqrt_rn(__ddiv_rn(1.0, var));
+#pragma unroll
+    for (int code = 0; code < 4; code++) {
+        const int x = code == 0 ? 2 : (code == 2 ? 1 : 0);
+        float z = __double2float_rn(__dsub_rn((double)x, mu));
+        z = __double2float_rn(__dmul_rn((double)z, isd));
+        if (code == 1) z = 0.0f;
+        lut[kk * 8 + code] = z;
+        lut[kk * 8 + 4 + code] = z;
+    }
+}
+
+// Device address of g_static_zlut for the CURRENT device.  In host code the array's name is
+// only a handle the runtime understands, not something a kernel may dereference, so the real
+// address is asked for once per device (with that device current) and remembered.
+static int static_lut_address(float** out, char* err, size_t errcap)
+{
+    static float* cached[64] = {};
+    int dev = 0;
+    GB_CUDA(cudaGetDevice(&dev));
+    GB_ARG(dev >= 0 && dev < 64, "diag_accum_static: device ordinal above 63");
+    if (!cached[dev]) {
+        float* p = nullptr;
+        GB_CUDA(cudaGetSymbolAddress((void**)&p, g_static_zlut));
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return 0;
+}
+
+}  // namespace gb
+
+extern "C" int gcta_b200_diag_accum_static(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_keepmask,
+                                           const int32_t* d_include, int64_t k0, int64_t kc, double* d_diag, int32_t* d_nii,
+                                           void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_bed && d_keepmask && d_diag && d_nii, "diag_accum_static: null pointer");
+    GB_ARG(pitch > 0 && pitch % 16 == 0 && ((uintptr_t)d_bed & 15) == 0, "diag_accum_static: bed pitch and pointer must be multiples of 16 bytes");
+    GB_ARG(pitch * 4 >= n_file && n_file > 0, "diag_accum_static: pitch too small for n_file");
+    GB_ARG(kc > 0 && k0 >= 0, "diag_accum_static: empty SNP range");
+    if (kc > STATIC_LUT_MAX_SNPS)
+        return set_err(err, errcap, GCTA_B200_ERR_ARG,
+                       "Error: diag_accum_static: " + std::to_string(kc) + " SNPs in one call exceed the built-in table of " +
+                           std::to_string(STATIC_LUT_MAX_SNPS) + " SNPs; split the range over several calls.");
+    float* lut = nullptr;
+    int rc = static_lut_address(&lut, err, errcap);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // every table entry of [0, kc) is rewritten here before the second kernel reads it, so nothing
+    // left behind by an earlier call can leak into this one
+    snp_lut_kernel<<<(unsigned)((kc + 7) / 8), 256, 0, st>>>(d_bed, pitch, d_keepmask, d_include, k0, kc, lut);
+    GB_CUDA(cudaGetLastError());
+    const int64_t cols = (n_file + 15) / 16;
+    dim3 grid((unsigned)((cols + 127) / 128), (unsigned)((kc + DIAG_SPLIT - 1) / DIAG_SPLIT));
+    // diag_accum_kernel indexes its table by absolute SNP number; the table starts at k0
+    diag_accum_kernel<false><<<grid, 128, 0, st>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, lut - k0 * 8, d_diag, d_nii);
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -145,6 +145,25 @@ int gcta_b200_diag_accum(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
                          const float* d_zlut, double* d_diag, int32_t* d_nii,
                          void* stream, char* err, size_t errcap);
 
+/* K1d without any allocation - NO COUNTERPART IN THE REFERENCE.
+ * Same result as gcta_b200_bed_decode (for its per-SNP table) followed by gcta_b200_diag_accum, for
+ * autosomal SNPs [k0, k0+kc): diag[f] += sum_k z_fk^2, nii[f] += non-missing SNPs, per FILE individual.
+ * For callers that cannot allocate device memory - a host that gave all of HBM to its own pool, or a
+ * loop that must stay out of the CUDA allocator because cudaMalloc / cudaFree stall the device.  The
+ * per-SNP table lives in a 16 MiB array built into the library (held by every GPU that loads it,
+ * until the process exits); the caller passes only inputs and outputs.
+ *   - at most 524288 SNPs per call; a larger kc is refused with GCTA_B200_ERR_ARG - split the range.
+ *   - the first call on each device looks the array's device address up (with that device current);
+ *     make that first call outside any stream capture.
+ *   - the call itself calls no cudaMalloc / cudaFree or allocating library routine.
+ *   - all calls share the one array: calls that can overlap on the GPU (different streams, threads or
+ *     processes' streams of the same context) race on it - serialise them.  Each call rewrites the
+ *     part of the table it reads, so a previous call's leftovers are harmless.
+ *   - d_keepmask as for gcta_b200_bed_decode; d_diag / d_nii are accumulated into (zero them first). */
+int gcta_b200_diag_accum_static(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
+                                const uint32_t* d_keepmask, const int32_t* d_include, int64_t k0, int64_t kc,
+                                double* d_diag, int32_t* d_nii, void* stream, char* err, size_t errcap);
+
 /* K1m - missingness bit planes for K3: d_miss[w][i] (uint32, i < ldm) has bit b set iff kept
  * individual i is NON-missing at included SNP 32*w + b; w in [k0/32, (k0+kc)/32) (k0 % 32 == 0). */
 int gcta_b200_nonmiss_planes(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
