@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libgcta_b200.so")
 FP16, BF16 = 0, 1
 ERRCAP = 512
-TILE_M, TILE_N = 128, 256
+TILE_M, TILE_N = 256, 256
 
 EXPORTS = [
     "gcta_b200_make_grm", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth", "gcta_b200_plan_download_bed",

@@ -40,8 +40,9 @@ inline int set_err(char* err, size_t cap, int code, const std::string& msg)
         if (!(cond)) return gb::set_err(err, errcap, GCTA_B200_ERR_ARG, std::string("Error: ") + (msg)); \
     } while (0)
 
-constexpr int TILE_M = 128;  // rows of S per tile (= UMMA M, TMEM lanes)
-constexpr int TILE_N = 256;  // columns of S per tile (= UMMA N, TMEM columns)
+constexpr int TILE_M = 256;  // rows of S per tile (two UMMA M=128 halves, one TMEM accumulator each)
+constexpr int TILE_N = 256;  // columns of S per tile (= UMMA N, TMEM columns per accumulator)
+constexpr int UMMA_M = 128;  // rows per tcgen05.mma (= TMEM lanes)
 constexpr int BLOCK_K = 64;  // SNPs per pipeline stage
 
 // ------------------------------------------------------------------------------------------------

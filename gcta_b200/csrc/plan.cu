@@ -10,6 +10,7 @@
 // the lower triangle, balanced by tile count, so outputs are disjoint contiguous ranges of
 // the packed triangle and no collective is needed on the data path.
 #include <algorithm>
+#include <cstdlib>
 #include <thread>
 #include <vector>
 
@@ -26,7 +27,17 @@ static int64_t tiles_in_row_block(int64_t bi, int64_t n)
     return last_row / TILE_N + 1;
 }
 
-constexpr int RASTER_ROWS = 16;  // row blocks per raster group: tiles in flight share 16 A panels
+// row blocks per raster group (measured on cfg3: 4-8 equivalent, 2 and 12 are 15 % slower; profiles/README.md)
+static int raster_rows()
+{
+    static int v = 0;
+    if (!v) {
+        const char* e = getenv("GCTA_B200_RASTER");
+        v = e ? atoi(e) : 6;
+        if (v < 1) v = 6;
+    }
+    return v;
+}
 
 }  // namespace gb
 
@@ -76,6 +87,7 @@ extern "C" int64_t gcta_b200_tile_list(int64_t n, int64_t row_begin, int64_t row
     if (row_begin % TILE_M != 0) return -1;
     const int64_t b0 = row_begin / TILE_M, b1 = (row_end + TILE_M - 1) / TILE_M;
     int64_t cnt = 0;
+    const int RASTER_ROWS = raster_rows();
     for (int64_t g0 = b0; g0 < b1; g0 += RASTER_ROWS) {
         const int64_t g1 = std::min<int64_t>(g0 + RASTER_ROWS, b1);
         const int64_t maxcb = tiles_in_row_block(g1 - 1, n);

@@ -6,27 +6,30 @@
 // (rows = SNPs = the contraction axis, columns = individuals), so both MMA operands are
 // "MN-major" tiles of the same matrix and no transpose is ever materialised.
 //
-// One persistent CTA per SM walks a static list of 128x256 output tiles:
-//   warp 0 (one lane) : TMA producer - 6 boxes of [64 SNPs][64 individuals] per stage into a
-//                       4-stage ring of 128B-swizzled shared memory
-//   warp 1 (one lane) : tcgen05.mma issuer - UMMA 128x256x16, kind::f16, FP32 accumulators in
-//                       TMEM, double buffered (2 x 256 columns) so the epilogue of tile t
-//                       overlaps the main loop of tile t+1
-//   warps 2-5         : epilogue - tcgen05.ld the accumulator, add it into the FP32 S tile in
-//                       HBM (S carries the sum over SNP chunks)
+// One persistent CTA per SM walks a static list of 256x256 output tiles.  A tile is two
+// UMMA M=128 halves sharing one B operand, each with its own 256-column TMEM accumulator
+// (all 512 columns in use), so every 64-SNP stage moves 64 KB for 2 x (128x256x64) MACs -
+// a third less L2->SM traffic per flop than a 128x256 tile, and a 2x larger wave footprint
+// for L2 reuse:
+//   warp 0 (one lane) : TMA producer - 8 boxes of [64 SNPs][64 individuals] per stage into a
+//                       3-stage ring of 128B-swizzled shared memory
+//   warp 1 (one lane) : tcgen05.mma issuer - UMMA 128x256x16, kind::f16, FP32 accumulate
+//   warps 2-9         : epilogue - tcgen05.ld the accumulators, add them into the FP32 S tile
+//                       in HBM (S carries the sum over SNP chunks)
 #include <cuda.h>
 
 #include "common.cuh"
 
 namespace gb {
 
-constexpr int NUM_STAGES = 4;
+constexpr int NUM_STAGES = 3;
 constexpr int GROUP_MN = 64;                                  // individuals per swizzle atom row (128 B)
-constexpr int A_GROUPS = TILE_M / GROUP_MN;                   // 2
+constexpr int A_GROUPS = TILE_M / GROUP_MN;                   // 4
 constexpr int B_GROUPS = TILE_N / GROUP_MN;                   // 4
 constexpr int GROUP_BYTES = BLOCK_K * GROUP_MN * 2;           // 8192: [64 k][64 mn] 16-bit
-constexpr int STAGE_BYTES = (A_GROUPS + B_GROUPS) * GROUP_BYTES;  // 49152
-constexpr int SYRK_THREADS = 192;
+constexpr int STAGE_BYTES = (A_GROUPS + B_GROUPS) * GROUP_BYTES;  // 65536
+constexpr int EPI_WARPS = 8;
+constexpr int SYRK_THREADS = 64 + 32 * EPI_WARPS;             // 320
 constexpr int TMEM_COLS = 512;
 constexpr size_t SYRK_SMEM = (size_t)NUM_STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 
@@ -50,8 +53,8 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restri
     uint64_t* full_bar = (uint64_t*)(smem + NUM_STAGES * STAGE_BYTES);
     uint64_t* empty_bar = full_bar + NUM_STAGES;
     uint64_t* tfull_bar = empty_bar + NUM_STAGES;
-    uint64_t* tempty_bar = tfull_bar + 2;
-    uint32_t* tmem_slot = (uint32_t*)(tempty_bar + 2);
+    uint64_t* tempty_bar = tfull_bar + 1;
+    uint32_t* tmem_slot = (uint32_t*)(tempty_bar + 1);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -62,10 +65,8 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restri
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        for (int a = 0; a < 2; a++) {
-            mbar_init(&tfull_bar[a], 1);
-            mbar_init(&tempty_bar[a], 4);
-        }
+        mbar_init(tfull_bar, 1);
+        mbar_init(tempty_bar, EPI_WARPS);
         mbar_fence_init();
     }
     if (warp == 1) {
@@ -108,42 +109,41 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restri
             uint32_t phase = 0;
             int it = 0;
             for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
-                const int acc = it & 1;
-                const uint32_t acc_phase = (it >> 1) & 1;
-                mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+                mbar_wait(tempty_bar, (it & 1) ^ 1);  // epilogue has drained the previous tile
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * TILE_N;
                 for (int kb = 0; kb < nkb; kb++) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
-                    const uint64_t a_desc = make_mn_desc(a_addr);
+                    const uint64_t a0_desc = make_mn_desc(a_addr);                                        // rows   0..127
+                    const uint64_t a1_desc = make_mn_desc(a_addr + (UMMA_M / GROUP_MN) * GROUP_BYTES);    // rows 128..255
                     const uint64_t b_desc = make_mn_desc(a_addr + A_GROUPS * GROUP_BYTES);
 #pragma unroll
                     for (int k4 = 0; k4 < BLOCK_K / 16; k4++) {
                         // 16 SNPs = two 8-row swizzle atoms = 2048 B further along K
                         const uint64_t adv = (uint64_t)((k4 * 2048) >> 4);
-                        umma_f16(d_tmem, a_desc + adv, b_desc + adv, idesc, (kb | k4) != 0 ? 1u : 0u);
+                        const uint32_t acc = (kb | k4) != 0 ? 1u : 0u;
+                        umma_f16(tmem_base, a0_desc + adv, b_desc + adv, idesc, acc);
+                        umma_f16(tmem_base + TILE_N, a1_desc + adv, b_desc + adv, idesc, acc);
                     }
                     umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
                     if (++stage == NUM_STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+                umma_commit(tfull_bar);  // both accumulators complete -> epilogue
             }
         }
         __syncwarp();
     } else {
-        // ---------------- epilogue (warps 2..5) ----------------
-        const int q = warp & 3;  // TMEM lane quarter this warp may read
-        const int r = q * 32 + lane;
+        // ---------------- epilogue (warps 2..9) ----------------
+        const int q = warp & 3;              // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;    // which accumulator / 128-row half of the tile
+        const int r = half * UMMA_M + q * 32 + lane;
         int it = 0;
         for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
-            const int acc = it & 1;
-            const uint32_t acc_phase = (it >> 1) & 1;
-            mbar_wait(&tfull_bar[acc], acc_phase);
+            mbar_wait(tfull_bar, it & 1);
             tc_fence_after();
             float4* Stile = reinterpret_cast<float4*>(S + (size_t)t * (TILE_M * TILE_N));
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TILE_N;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * TILE_N;
 #pragma unroll 1
             for (int c0 = 0; c0 < TILE_N; c0 += 32) {
                 uint32_t v[32];
@@ -162,7 +162,7 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restri
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+            if (lane == 0) mbar_arrive(tempty_bar);
         }
     }
 
@@ -224,7 +224,7 @@ extern "C" int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad
     // B MN-major bit 16, N>>3 [17,23), M>>4 [24,29)
     const uint32_t fmt = operand == GCTA_B200_BF16 ? 1u : 0u;
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(TILE_N >> 3) << 17) |
-                           ((uint32_t)(TILE_M >> 4) << 24);
+                           ((uint32_t)(UMMA_M >> 4) << 24);
 
     static bool attr_set[64] = {};
     if (dev < 64 && !attr_set[dev]) {

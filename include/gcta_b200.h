@@ -172,8 +172,8 @@ int gcta_b200_nonmiss_planes(const uint8_t* d_bed, int64_t pitch, int64_t n_file
                              void* stream, char* err, size_t errcap);
 
 /* K2 - lower-triangle SYRK  S += Z^T Z  on tcgen05 tensor cores (grm.cpp:276-296 numerator).
- * Tiles: 128 rows x 256 columns of S.  d_tiles = int32[ntiles][2] (row block, column block);
- * tile t of the list is stored at d_S + t*128*256 floats in the layout
+ * Tiles: 256 rows x 256 columns of S.  d_tiles = int32[ntiles][2] (row block, column block);
+ * tile t of the list is stored at d_S + t*256*256 floats in the layout
  * [col/4][row][col%4] (see gcta_b200_s_tile_index).  S must be zeroed by the caller before
  * the first chunk. */
 int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand,
@@ -195,16 +195,16 @@ int gcta_b200_finalize_tiles(const float* d_S, const int32_t* d_Ntiles, int32_t 
                              float* d_A_lower, int32_t* d_N_lower,
                              void* stream, char* err, size_t errcap);
 
-/* index of element (r, c), r < 128, c < 256, inside one S / N tile */
-static inline int64_t gcta_b200_s_tile_index(int r, int c) { return ((int64_t)(c >> 2) * 128 + r) * 4 + (c & 3); }
+/* index of element (r, c), r < 256, c < 256, inside one S / N tile */
+static inline int64_t gcta_b200_s_tile_index(int r, int c) { return ((int64_t)(c >> 2) * 256 + r) * 4 + (c & 3); }
 
 /* helpers */
 const char* gcta_b200_version(void);
 int gcta_b200_device_count(void); /* 0 when no driver / device */
 /* row band [row_begin,row_end) owned by part_rank of part_world for n kept individuals
- * (boundaries are multiples of 128, bands balanced by tile count) */
+ * (boundaries are multiples of 256, bands balanced by tile count) */
 int gcta_b200_partition(int64_t n, int32_t part_rank, int32_t part_world, int64_t* row_begin, int64_t* row_end);
-/* number of 128x256 tiles of band [row_begin,row_end) and, when tiles != NULL, the list in
+/* number of 256x256 tiles of band [row_begin,row_end) and, when tiles != NULL, the list in
  * launch order (int32[count][2]) */
 int64_t gcta_b200_tile_list(int64_t n, int64_t row_begin, int64_t row_end, int32_t* tiles);
 

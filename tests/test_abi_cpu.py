@@ -33,15 +33,15 @@ def test_tile_list_covers_lower_triangle_once(n):
     t = abi.tile_list(n)
     assert len({tuple(x) for x in t}) == len(t)
     n_pad = (n + 255) // 256 * 256
-    cov = np.zeros((n_pad + 128, n_pad), dtype=np.int32)
+    cov = np.zeros((n_pad, n_pad), dtype=np.int32)
     for bi, bj in t:
-        assert bi * 128 < n and bj * 256 < n
-        cov[bi * 128:(bi + 1) * 128, bj * 256:(bj + 1) * 256] += 1
+        assert bi * 256 < n and bj * 256 < n
+        cov[bi * 256:(bi + 1) * 256, bj * 256:(bj + 1) * 256] += 1
     ii, jj = np.tril_indices(n)
     assert (cov[ii, jj] == 1).all()
     # no tile lies entirely above the diagonal
     for bi, bj in t:
-        assert min(bi * 128 + 127, n - 1) >= bj * 256
+        assert min(bi * 256 + 255, n - 1) >= bj * 256
 
 
 @pytest.mark.parametrize("n,world", [(50000, 8), (10000, 4), (2000, 2), (300, 8), (100, 3)])
@@ -55,7 +55,7 @@ def test_partition_bands_are_contiguous_and_balanced(n, world):
     if n >= 10000:
         assert max(counts) <= 1.05 * (sum(counts) / world) + 64
     # all boundaries except the last are multiples of the tile height
-    assert all(b % 128 == 0 for b, e in bands if e > b)
+    assert all(b % 256 == 0 for b, e in bands if e > b)
 
 
 def test_no_cpu_fallback():

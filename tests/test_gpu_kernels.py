@@ -139,12 +139,12 @@ def test_bed_decode_keep_include_mu_override_xchr():
 
 
 def s_tiles_to_dense(S, tiles, n_pad):
-    """[ntiles][64][128][4] tile storage -> dense [n_pad, n_pad] (only listed tiles filled)"""
+    """[ntiles][64][256][4] tile storage -> dense [n_pad, n_pad] (only listed tiles filled)"""
     out = np.zeros((n_pad, n_pad), dtype=S.dtype)
-    T = S.reshape(len(tiles), 64, 128, 4)
+    T = S.reshape(len(tiles), 64, 256, 4)
     for t, (bi, bj) in enumerate(tiles):
-        blk = T[t].transpose(1, 0, 2).reshape(128, 256)  # [r][c4][4] -> [r][c]
-        out[bi * 128:(bi + 1) * 128, bj * 256:(bj + 1) * 256] = blk
+        blk = T[t].transpose(1, 0, 2).reshape(256, 256)  # [r][c4][4] -> [r][c]
+        out[bi * 256:(bi + 1) * 256, bj * 256:(bj + 1) * 256] = blk
     return out
 
 
@@ -153,7 +153,7 @@ def run_syrk(Zt, n, operand, S=None):
     tiles = abi.tile_list(n)
     d_tiles = dev(tiles)
     if S is None:
-        S = torch.zeros(len(tiles) * 128 * 256, dtype=torch.float32, device="cuda")
+        S = torch.zeros(len(tiles) * 256 * 256, dtype=torch.float32, device="cuda")
     abi.call("gcta_b200_syrk_tiles", P(Zt.data_ptr()), I64(ldz), I64(kc_pad), I32(operand), P(d_tiles.data_ptr()),
              I64(len(tiles)), P(S.data_ptr()), stream())
     torch.cuda.synchronize()
@@ -172,13 +172,13 @@ def test_syrk_exact_on_integer_operands(n, kc, operand):
     ref = (Zi.double().T @ Zi.double()).cpu().numpy()  # exact integers, |S| <= 9*kc < 2^24
     got = s_tiles_to_dense(S.cpu().numpy(), tiles, ldz)
     for (bi, bj) in tiles:
-        r = slice(bi * 128, (bi + 1) * 128)
+        r = slice(bi * 256, (bi + 1) * 256)
         c = slice(bj * 256, (bj + 1) * 256)
         assert np.array_equal(got[r, c], ref[r, c]), f"tile {(bi, bj)} wrong, max diff {np.abs(got[r, c] - ref[r, c]).max()}"
     # every element of the lower triangle is covered by some tile
     cov = np.zeros((ldz, ldz), dtype=bool)
     for (bi, bj) in tiles:
-        cov[bi * 128:(bi + 1) * 128, bj * 256:(bj + 1) * 256] = True
+        cov[bi * 256:(bi + 1) * 256, bj * 256:(bj + 1) * 256] = True
     ii, jj = np.tril_indices(n)
     assert cov[ii, jj].all()
 
@@ -230,7 +230,7 @@ def test_diag_planes_paircount_finalize():
     # K3
     tiles = abi.tile_list(n)
     d_tiles = dev(tiles)
-    Nt = torch.zeros(len(tiles) * 128 * 256, dtype=torch.int32, device="cuda")
+    Nt = torch.zeros(len(tiles) * 256 * 256, dtype=torch.int32, device="cuda")
     abi.call("gcta_b200_paircount_tiles", ptr(planes), I64(ldm), I64(nwords), ptr(d_tiles), I64(len(tiles)), ptr(Nt), stream())
     Nref = (ok.astype(np.int64).T @ ok.astype(np.int64))
     Nd = s_tiles_to_dense(Nt.cpu().numpy(), tiles, ldm)
