@@ -12,6 +12,9 @@
 //
 // All three are HBM-bound byte/bit kernels: 128-bit loads of packed genotypes, 128-bit
 // coalesced stores of Z.  Algorithmic bytes per SNP: ceil(n/4) read + 2*ldz written (K1).
+#include <algorithm>
+#include <vector>
+
 #include "common.cuh"
 
 namespace gb {
@@ -482,4 +485,130 @@ extern "C" int gcta_b200_diag_accum_static(const uint8_t* d_bed, int64_t pitch, 
     diag_accum_kernel<false><<<grid, 128, 0, st>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, lut - k0 * 8, d_diag, d_nii);
     GB_CUDA(cudaGetLastError());
     return 0;
+}
+
+// ================================================================================================
+// Allele counts only (no Z): the counting half of calcu_mu / mu_func (data.cpp:759-803) for the
+// host's --freq, --maf and --max-maf, which run before / without make_grm (option.cpp:601-615).
+// One warp per included SNP; optional male / female masks give the X-chromosome split.
+// ================================================================================================
+namespace gb {
+
+__global__ void __launch_bounds__(256) allele_counts_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t row_base,
+                                                             const uint32_t* __restrict__ keepmask,
+                                                             const uint32_t* __restrict__ malemask,
+                                                             const uint32_t* __restrict__ femalemask,
+                                                             const int32_t* __restrict__ include, int64_t k0, int64_t kc,
+                                                             int32_t* __restrict__ out /* [6][kc]: cnt,sum,cntM,sumM,cntF,sumF */)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t kk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (kk >= kc) return;
+    const int64_t k = k0 + kk;
+    const int64_t frow = (include ? (int64_t)include[k] : k) - row_base;
+    const uint4* row16 = reinterpret_cast<const uint4*>(bed + frow * pitch);
+    const uint4* km16 = reinterpret_cast<const uint4*>(keepmask);
+    const uint4* mm16 = reinterpret_cast<const uint4*>(malemask);
+    const uint4* fm16 = reinterpret_cast<const uint4*>(femalemask);
+    SnpCounts a = {0, 0, 0, 0}, f = {0, 0, 0, 0};
+    for (int v = lane; v < (int)(pitch / 16); v += 32) {
+        const uint4 w = __ldg(row16 + v), km = __ldg(km16 + v);
+        if (malemask) {
+            const uint4 mm = __ldg(mm16 + v), fm = __ldg(fm16 + v);
+            count_word<true>(w.x, km.x, mm.x, a); count_word<true>(w.y, km.y, mm.y, a);
+            count_word<true>(w.z, km.z, mm.z, a); count_word<true>(w.w, km.w, mm.w, a);
+            count_word<true>(w.x, km.x, fm.x, f); count_word<true>(w.y, km.y, fm.y, f);
+            count_word<true>(w.z, km.z, fm.z, f); count_word<true>(w.w, km.w, fm.w, f);
+        } else {
+            count_word<false>(w.x, km.x, 0u, a); count_word<false>(w.y, km.y, 0u, a);
+            count_word<false>(w.z, km.z, 0u, a); count_word<false>(w.w, km.w, 0u, a);
+        }
+    }
+    const int v0 = warp_sum(a.cnt), v1 = warp_sum(a.sum), v2 = warp_sum(a.cntM), v3 = warp_sum(a.sumM);
+    const int v4 = warp_sum(f.cntM), v5 = warp_sum(f.sumM);
+    if (lane == 0) {
+        out[0 * kc + kk] = v0; out[1 * kc + kk] = v1; out[2 * kc + kk] = v2;
+        out[3 * kc + kk] = v3; out[4 * kc + kk] = v4; out[5 * kc + kk] = v5;
+    }
+}
+
+}  // namespace gb
+
+extern "C" int gcta_b200_allele_counts(const gcta_b200_args* a, int32_t* cnt, int32_t* sum, int32_t* cntM, int32_t* sumM,
+                                       int32_t* cntF, int32_t* sumF, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(a && a->bed && cnt && sum, "allele_counts: null argument");
+    GB_ARG(a->n_file > 0 && a->m_file > 0, "allele_counts: empty genotype file");
+    const int64_t n = a->keep ? a->n : a->n_file, m = a->include ? a->m : a->m_file;
+    if (m <= 0) return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: No SNP is retained for analysis.");
+    if (n <= 0) return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: No individual is retained for analysis.");
+    if (gcta_b200_device_count() <= 0)
+        return set_err(err, errcap, GCTA_B200_ERR_NO_DEVICE, "Error: no CUDA device is available (gcta_b200 has no CPU fallback).");
+    const bool split = a->sex != nullptr && cntM && sumM && cntF && sumF;
+    GB_CUDA(cudaSetDevice(a->device));
+    const int64_t stride = (a->n_file + 3) / 4, pitch = (stride + 15) / 16 * 16;
+    std::string km((size_t)pitch, '\0'), mm, fm;
+    if (split) { mm.assign((size_t)pitch, '\0'); fm.assign((size_t)pitch, '\0'); }
+    auto setbit = [](std::string& s, int64_t f) { s[(size_t)(f >> 2)] |= (char)(1 << ((f & 3) * 2)); };
+    for (int64_t i = 0; i < n; i++) {
+        const int64_t f = a->keep ? a->keep[i] : i;
+        GB_ARG(f >= 0 && f < a->n_file, "allele_counts: keep index out of range");
+        setbit(km, f);
+        if (split && a->sex[f] == 1) setbit(mm, f);
+        if (split && a->sex[f] == 2) setbit(fm, f);
+    }
+    // slabs of included SNPs whose file rows span at most ~1 GiB
+    const int64_t slab_rows = std::max<int64_t>(1, (1ll << 30) / pitch);
+    uint8_t* d_bed = nullptr; uint32_t *d_km = nullptr, *d_mm = nullptr, *d_fm = nullptr; int32_t *d_inc = nullptr, *d_out = nullptr;
+    int rc = 0;
+    cudaError_t e = cudaSuccess;
+    auto fail = [&](cudaError_t ce, const char* what) {
+        rc = set_err(err, errcap, ce == cudaErrorMemoryAllocation ? GCTA_B200_ERR_NOMEM : GCTA_B200_ERR_CUDA,
+                     std::string("Error: CUDA call failed: ") + what + ": " + cudaGetErrorString(ce));
+    };
+#define AC_TRY(x) do { if (!rc && (e = (x)) != cudaSuccess) fail(e, #x); } while (0)
+    AC_TRY(cudaMalloc(&d_bed, (size_t)pitch * std::min<int64_t>(slab_rows, a->m_file)));
+    AC_TRY(cudaMalloc(&d_km, (size_t)pitch));
+    AC_TRY(cudaMemcpy(d_km, km.data(), (size_t)pitch, cudaMemcpyHostToDevice));
+    if (split) {
+        AC_TRY(cudaMalloc(&d_mm, (size_t)pitch)); AC_TRY(cudaMalloc(&d_fm, (size_t)pitch));
+        AC_TRY(cudaMemcpy(d_mm, mm.data(), (size_t)pitch, cudaMemcpyHostToDevice));
+        AC_TRY(cudaMemcpy(d_fm, fm.data(), (size_t)pitch, cudaMemcpyHostToDevice));
+    }
+    if (a->include) {
+        AC_TRY(cudaMalloc(&d_inc, (size_t)m * 4));
+        AC_TRY(cudaMemcpy(d_inc, a->include, (size_t)m * 4, cudaMemcpyHostToDevice));
+    }
+    AC_TRY(cudaMalloc(&d_out, (size_t)6 * std::min<int64_t>(slab_rows, m) * 4));
+    std::vector<int32_t> h;
+    for (int64_t k0 = 0; !rc && k0 < m;) {
+        const int64_t r0 = a->include ? a->include[k0] : k0;
+        int64_t k1 = k0;
+        while (k1 < m && k1 - k0 < slab_rows && (a->include ? a->include[k1] : k1) - r0 < slab_rows &&
+               (a->include ? a->include[k1] : k1) >= r0)
+            k1++;
+        if (k1 == k0) { rc = set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: allele_counts: include must be ascending"); break; }
+        const int64_t r1 = (a->include ? a->include[k1 - 1] : k1 - 1) + 1, kc = k1 - k0;
+        if (pitch != stride) AC_TRY(cudaMemset(d_bed, 0, (size_t)pitch * (r1 - r0)));
+        AC_TRY(cudaMemcpy2D(d_bed, (size_t)pitch, a->bed + r0 * stride, (size_t)stride, (size_t)stride, (size_t)(r1 - r0), cudaMemcpyHostToDevice));
+        if (!rc) {
+            allele_counts_kernel<<<(unsigned)((kc + 7) / 8), 256>>>(d_bed, pitch, r0, d_km, split ? d_mm : nullptr, split ? d_fm : nullptr, d_inc, k0, kc, d_out);
+            AC_TRY(cudaGetLastError());
+        }
+        h.resize((size_t)6 * kc);
+        AC_TRY(cudaMemcpy(h.data(), d_out, (size_t)6 * kc * 4, cudaMemcpyDeviceToHost));
+        if (!rc) {
+            memcpy(cnt + k0, h.data(), (size_t)kc * 4);
+            memcpy(sum + k0, h.data() + kc, (size_t)kc * 4);
+            if (split) {
+                memcpy(cntM + k0, h.data() + 2 * kc, (size_t)kc * 4); memcpy(sumM + k0, h.data() + 3 * kc, (size_t)kc * 4);
+                memcpy(cntF + k0, h.data() + 4 * kc, (size_t)kc * 4); memcpy(sumF + k0, h.data() + 5 * kc, (size_t)kc * 4);
+            }
+        }
+        k0 = k1;
+    }
+#undef AC_TRY
+    cudaFree(d_bed); cudaFree(d_km); cudaFree(d_mm); cudaFree(d_fm); cudaFree(d_inc); cudaFree(d_out);
+    return rc;
 }

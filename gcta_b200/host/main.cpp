@@ -1,0 +1,153 @@
+// main.cpp - gcta64_b200: command-line front end for the accelerated `--bfile ... --make-grm` path.
+//
+// Drop-in for the flag subset of SURVEY.md 8a-1 (option.cpp:114-543): same flag names, value
+// parsing (atoi / atof), range errors, option echo, banner, ordering of the calls
+// (option.cpp:580-621) and error convention (message on stderr, "Analysis finished", exit code 0;
+// option.cpp:42-50).  Flags of GCTA analyses outside the path are rejected like unknown flags.
+// Extra flags (not in the reference): --gpus N, --operand fp16|bf16, --chunk-snps K.
+#include <cstdlib>
+#include <cstring>
+#include <ctime>
+#include <iostream>
+#include <sstream>
+#include <string>
+
+#include "../../include/gcta_b200.h"
+#include "gcta_host.h"
+
+using std::cerr;
+using std::cout;
+using std::endl;
+using std::string;
+
+static void option(int argc, char* argv_in[])
+{
+    string bfile, update_sex_file, update_freq_file, update_refA_file, kp_indi_file, rm_indi_file, extract_snp_file,
+        exclude_snp_file, extract_snp_name, exclude_snp_name, out = "gcta";
+    bool bfile_flag = false, out_freq_flag = false, autosome_flag = false, make_grm_flag = false, make_grm_xchr_flag = false,
+         grm_out_bin_flag = false;
+    int autosome_num = 22, extract_chr_start = 0, extract_chr_end = 0, grm_mtd = 0, n_gpus = 1, operand = GCTA_B200_FP16;
+    long long chunk_snps = 0;
+    double maf = 0.0, max_maf = 0.0, rm_high_ld_cutoff = -1.0;
+
+    // like the reference, a sentinel after the last argument keeps `argv[++i]` in range (option.cpp:111-113)
+    std::vector<const char*> argv(argv_in, argv_in + argc);
+    argv.push_back("gcta");
+    argv.push_back("gcta");
+    for (int i = 1; i < argc; i++) {
+        const char* o = argv[i];
+        auto is = [&](const char* name) { return strcmp(o, name) == 0; };
+        if (is("--bfile")) { bfile_flag = true; bfile = argv[++i]; cout << "--bfile " << argv[i] << endl; }
+        else if (is("--update-freq")) { update_freq_file = argv[++i]; cout << "--update-freq " << update_freq_file << endl; }
+        else if (is("--update-ref-allele")) { update_refA_file = argv[++i]; cout << "--update-ref-allele " << update_refA_file << endl; }
+        else if (is("--keep")) { kp_indi_file = argv[++i]; cout << "--keep " << kp_indi_file << endl; }
+        else if (is("--remove")) { rm_indi_file = argv[++i]; cout << "--remove " << rm_indi_file << endl; }
+        else if (is("--update-sex")) { update_sex_file = argv[++i]; cout << "--update-sex " << update_sex_file << endl; }
+        else if (is("--chr")) {
+            extract_chr_start = extract_chr_end = atoi(argv[++i]);
+            cout << "--chr " << extract_chr_start << endl;
+            if (extract_chr_start < 1 || extract_chr_start > 100) throw("\nError: --chr should be within the range from 1 to 100.\n");
+        }
+        else if (is("--autosome-num")) {
+            autosome_num = atoi(argv[++i]);
+            cout << "--autosome-num " << autosome_num << endl;
+            if (autosome_num < 1 || autosome_num > 100) throw("\nError: invalid number specified after the option --autosome-num.\n");
+        }
+        else if (is("--autosome")) { autosome_flag = true; cout << "--autosome" << endl; }
+        else if (is("--extract")) { extract_snp_file = argv[++i]; cout << "--extract " << extract_snp_file << endl; }
+        else if (is("--exclude")) { exclude_snp_file = argv[++i]; cout << "--exclude " << exclude_snp_file << endl; }
+        else if (is("--extract-snp")) { extract_snp_name = argv[++i]; cout << "--extract-snp " << extract_snp_name << endl; }
+        else if (is("--exclude-snp")) { exclude_snp_name = argv[++i]; cout << "--exclude-snp " << exclude_snp_name << endl; }
+        else if (is("--maf")) {
+            maf = atof(argv[++i]);
+            cout << "--maf " << maf << endl;
+            if (maf < 0 || maf > 0.5) throw("\nError: --maf should be within the range from 0 to 0.5.\n");
+        }
+        else if (is("--max-maf")) {
+            max_maf = atof(argv[++i]);
+            cout << "--max-maf " << max_maf << endl;
+            if (max_maf < 0 || max_maf > 0.5) throw("\nError: --max-maf should be within the range from 0 to 0.5.\n");
+        }
+        else if (is("--out")) { out = argv[++i]; cout << "--out " << out << endl; }
+        else if (is("--freq")) { out_freq_flag = true; cout << "--freq" << endl; }
+        else if (is("--save-ram")) { cout << "--save-ram" << endl; }   // only read by the LD analysis in the reference
+        else if (is("--grm-alg")) {
+            grm_mtd = atoi(argv[++i]);
+            cout << "--grm-alg " << grm_mtd << endl;
+            if (grm_mtd < 0 || grm_mtd > 1) throw("\nError: --grm-alg should be 0 or 1.\n");
+        }
+        else if (is("--rm-high-ld")) {
+            rm_high_ld_cutoff = atof(argv[++i]);
+            cout << "--rm-high-ld " << rm_high_ld_cutoff << endl;
+            if (rm_high_ld_cutoff <= 0 || rm_high_ld_cutoff >= 1) throw("\nError: the value to be specified after --rm-high-ld should be within the range from 0 to 1.\n");
+        }
+        else if (is("--make-grm")) { make_grm_flag = true; cout << "--make-grm" << endl; }
+        else if (is("--make-grm-xchr")) { make_grm_xchr_flag = true; cout << "--make-grm-xchr" << endl; }
+        else if (is("--make-grm-bin")) { make_grm_flag = true; grm_out_bin_flag = true; cout << "--make-grm-bin" << endl; }
+        else if (is("--make-grm-xchr-bin")) { make_grm_xchr_flag = true; grm_out_bin_flag = true; cout << "--make-grm-xchr-bin" << endl; }
+        // ---- device options, not in the reference ----
+        else if (is("--gpus")) { n_gpus = atoi(argv[++i]); cout << "--gpus " << n_gpus << endl; if (n_gpus < 1 || n_gpus > 64) throw("\nError: --gpus should be within the range from 1 to 64.\n"); }
+        else if (is("--operand")) {
+            const string v = argv[++i];
+            cout << "--operand " << v << endl;
+            if (v == "fp16") operand = GCTA_B200_FP16;
+            else if (v == "bf16") operand = GCTA_B200_BF16;
+            else throw("\nError: --operand should be fp16 or bf16.\n");
+        }
+        else if (is("--chunk-snps")) { chunk_snps = atoll(argv[++i]); cout << "--chunk-snps " << chunk_snps << endl; }
+        else if (is("gcta")) break;
+        else { std::stringstream e; e << "\nError: invalid option \"" << o << "\".\n"; throw(e.str()); }
+    }
+    cout << endl;
+    // set autosome (option.cpp:566-571)
+    if (autosome_flag) { extract_chr_start = 1; extract_chr_end = autosome_num; }
+    if (make_grm_xchr_flag) extract_chr_start = extract_chr_end = autosome_num + 1;
+
+    cout << endl;
+    gcta_host g(autosome_num, rm_high_ld_cutoff, out);
+    g.n_gpus = n_gpus; g.operand = operand; g.chunk_snps = chunk_snps;
+    if (bfile_flag) {   // option.cpp:580-621
+        g.read_famfile(bfile + ".fam");
+        if (!kp_indi_file.empty()) g.keep_indi(kp_indi_file);
+        if (!rm_indi_file.empty()) g.remove_indi(rm_indi_file);
+        if (!update_sex_file.empty()) g.update_sex(update_sex_file);
+        g.read_bimfile(bfile + ".bim");
+        if (!extract_snp_file.empty()) g.extract_snp(extract_snp_file);
+        if (!exclude_snp_file.empty()) g.exclude_snp(exclude_snp_file);
+        if (extract_chr_start > 0) g.extract_chr(extract_chr_start, extract_chr_end);
+        if (!extract_snp_name.empty()) g.extract_single_snp(extract_snp_name);
+        if (!exclude_snp_name.empty()) g.exclude_single_snp(exclude_snp_name);
+        if (!update_refA_file.empty()) g.update_ref_A(update_refA_file);
+        g.read_bedfile(bfile + ".bed");
+        if (!update_freq_file.empty()) g.update_freq(update_freq_file);
+        if (maf > 0) g.filter_snp_maf(maf);
+        if (max_maf > 0.0) g.filter_snp_max_maf(max_maf);
+        if (out_freq_flag) g.save_freq();
+        else if (make_grm_flag) g.make_grm(false, grm_out_bin_flag, grm_mtd);
+        else if (make_grm_xchr_flag) g.make_grm(true, grm_out_bin_flag, grm_mtd);
+    }
+    else throw("Error: no analysis has been launched by the option(s).\n");
+}
+
+int main(int argc, char* argv[])
+{
+    cout << "*******************************************************************" << endl;
+    cout << "* Genome-wide Complex Trait Analysis (GCTA)" << endl;
+    cout << "* version 0.93.9 - B200 build of the --make-grm path (" << gcta_b200_version() << ")" << endl;
+    cout << "* (C) 2010 Jian Yang, Hong Lee, Michael Goddard and Peter Visscher" << endl;
+    cout << "* GNU General Public License, v2" << endl;
+    cout << "* Queensland Institute of Medical Research" << endl;
+    cout << "*******************************************************************" << endl;
+    const time_t start = time(NULL);
+    time_t curr = time(0);
+    cout << "Analysis started: " << ctime(&curr) << endl;
+    cout << "Options:" << endl;
+    try { option(argc, argv); }
+    catch (const string& err_msg) { cerr << err_msg << endl; }
+    catch (const char* err_msg) { cerr << err_msg << endl; }
+    curr = time(0);
+    cout << "\nAnalysis finished: " << ctime(&curr);
+    const long t = (long)(time(NULL) - start);
+    cout << "Computational time: " << t / 3600 << ":" << (t % 3600) / 60 << ":" << t % 60 << endl;
+    return 0;   // the reference exits 0 even after an error (option.cpp:50)
+}

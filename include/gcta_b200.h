@@ -84,6 +84,14 @@ typedef struct {
 
 int gcta_b200_make_grm(const gcta_b200_args* args, gcta_b200_out* out, char* err, size_t errcap);
 
+/* Allele counts without building a GRM: the counting half of calcu_mu / mu_func (data.cpp:759-803)
+ * that --freq, --maf and --max-maf need (option.cpp:604-615).  Host pointers; per included SNP the
+ * non-missing count and the allele-1 dosage sum among kept individuals.  When args->sex and all four
+ * split outputs are given, the same counts restricted to kept males (sex == 1) and kept females
+ * (sex == 2) are returned too, so the host can apply the X-chromosome weights of data.cpp:765-777. */
+int gcta_b200_allele_counts(const gcta_b200_args* args, int32_t* cnt, int32_t* sum, int32_t* cntM, int32_t* sumM,
+                            int32_t* cntF, int32_t* sumF, char* err, size_t errcap);
+
 /* ------------------------------------------------------------------------------------------
  * Plan API: the same path split into upload / compute / download so that a caller (bench.py,
  * a pipelined host) can keep the packed genotypes resident in HBM and time the phases.
