@@ -125,32 +125,20 @@ def main_reference(a, rank, world):
 
 def main_ours(a, rank, world, local_rank):
     import torch
-    import torch.distributed as dist
     from gcta_b200 import abi, synth
+    from gcta_b200 import dist as gdist
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device - gcta_b200 has no CPU fallback")
     torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ranks = gdist.Ranks(backend="nccl", device=torch.device("cuda", local_rank))   # same class the gloo CPU test drives
 
     def barrier():
         torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        ranks.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(x):
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    max_over_ranks, sum_over_ranks = ranks.max, ranks.sum
 
     n, m = a.n, a.m
     pairs_total = n * (n + 1) / 2
@@ -255,8 +243,7 @@ def main_ours(a, rank, world, local_rank):
     if rank == 0:
         print(json.dumps(line))
     plan.close()
-    if world > 1:
-        dist.destroy_process_group()
+    ranks.close()
 
 
 def plan_chunk(plan, n, m):
