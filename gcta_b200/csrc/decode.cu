@@ -199,52 +199,100 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
 }
 
 // ------------------------------------------------------------------------------------------------
-// K1d: thread = one 32-bit column (16 file individuals), loops over a slice of SNPs.
+// K1d: thread = one 32-bit column (16 file individuals) x a slice of SNPs.
+// The squares z^2 of the (at most) three values a SNP takes are staged per tile of 192 SNPs as a
+// [SNP][code] float table in shared memory; per genotype the inner loop is shift, mask, one LDS
+// (code -> z^2; a warp touches at most 4 banks) and one FADD.  FP32 partial sums over a tile are
+// folded into FP64 per tile; missing genotypes are counted bit-sliced (2-bit lanes -> 8-bit
+// lanes every 3 SNPs -> 32-bit per tile), so counting costs ~0.3 instructions per genotype.
 // ------------------------------------------------------------------------------------------------
-constexpr int DIAG_SPLIT = 1024;  // SNPs per thread slice
+constexpr int DIAG_TILE = 192;              // SNPs per shared-memory tile (multiple of 3, <= 255)
+constexpr int DIAG_SPLIT = 4 * DIAG_TILE;   // SNPs per block slice
+constexpr int DIAG_THREADS = 256;
 
 template <bool XCHR>
-__global__ void __launch_bounds__(128) diag_accum_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n_file,
-                                                          const uint32_t* __restrict__ sexmale,
-                                                          const int32_t* __restrict__ include, int64_t k0, int64_t kc,
-                                                          const float* __restrict__ zlut, double* __restrict__ diag,
-                                                          int32_t* __restrict__ nii)
+__global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n_file,
+                                                                   const uint32_t* __restrict__ sexmale,
+                                                                   const int32_t* __restrict__ include, int64_t k0, int64_t kc,
+                                                                   const float* __restrict__ zlut, double* __restrict__ diag,
+                                                                   int32_t* __restrict__ nii)
 {
-    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (col * 16 >= n_file) return;
-    const int64_t kbeg = (int64_t)blockIdx.y * DIAG_SPLIT, kend = min(kbeg + DIAG_SPLIT, kc);
-    const uint32_t mm = XCHR ? sexmale[col] : 0u;
-    double acc[16];
-    int cn[16];
+    __shared__ __align__(16) float q_s[(XCHR ? 2 : 1) * DIAG_TILE * 4];   // [sex][SNP][code] squares
+    __shared__ int64_t row_s[DIAG_TILE];                                   // byte offset of each SNP row
+    const int64_t col = (int64_t)blockIdx.x * DIAG_THREADS + threadIdx.x;
+    const bool active = col * 16 < n_file;
+    const int64_t kbeg = (int64_t)blockIdx.y * DIAG_SPLIT, kend = min(kbeg + (int64_t)DIAG_SPLIT, kc);
+    // byte offsets into q_s of the male table, per individual slot (0 for females / autosomes)
+    uint32_t moff[16];
 #pragma unroll
-    for (int e = 0; e < 16; e++) { acc[e] = 0.0; cn[e] = 0; }
-    for (int64_t kk = kbeg; kk < kend; kk++) {
-        const int64_t k = k0 + kk;
-        const int64_t frow = include ? include[k] : k;
-        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(bed + frow * pitch) + col);
-        const float4 lf = __ldg(reinterpret_cast<const float4*>(zlut + k * 8));
-        // exact products of two floats in double (grm.cpp:267: static_cast<double>(X) * X)
-        const double q0 = (double)lf.x * (double)lf.x, q2 = (double)lf.z * (double)lf.z, q3 = (double)lf.w * (double)lf.w;
-        double m0 = q0, m2 = q2, m3 = q3;
-        if (XCHR) {
-            const float4 lm = __ldg(reinterpret_cast<const float4*>(zlut + k * 8 + 4));
-            m0 = (double)lm.x * (double)lm.x; m2 = (double)lm.z * (double)lm.z; m3 = (double)lm.w * (double)lm.w;
+    for (int e = 0; e < 16; e++) moff[e] = 0;
+    if (XCHR && active) {
+        const uint32_t mm = sexmale[col];
+#pragma unroll
+        for (int e = 0; e < 16; e++) moff[e] = ((mm >> (2 * e)) & 1u) ? DIAG_TILE * 16 : 0;
+    }
+    double dacc[16];
+    int miss[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) { dacc[e] = 0.0; miss[e] = 0; }
+    const char* q_bytes = reinterpret_cast<const char*>(q_s);
+
+    for (int64_t t0 = kbeg; t0 < kend; t0 += DIAG_TILE) {
+        const int tn = (int)min((int64_t)DIAG_TILE, kend - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < tn; i += DIAG_THREADS) {
+            const int64_t k = k0 + t0 + i;
+            row_s[i] = (include ? (int64_t)include[k] : k) * pitch;
+            const float4 lf = __ldg(reinterpret_cast<const float4*>(zlut + k * 8));
+            // exact squares of floats rounded once to float (relative 6e-8, unbiased)
+            reinterpret_cast<float4*>(q_s)[i] = make_float4(lf.x * lf.x, 0.0f, lf.z * lf.z, lf.w * lf.w);
+            if (XCHR) {
+                const float4 lm = __ldg(reinterpret_cast<const float4*>(zlut + k * 8 + 4));
+                reinterpret_cast<float4*>(q_s)[DIAG_TILE + i] = make_float4(lm.x * lm.x, 0.0f, lm.z * lm.z, lm.w * lm.w);
+            }
         }
+        __syncthreads();
+        if (!active) continue;
+        float acc[16];
+#pragma unroll
+        for (int e = 0; e < 16; e++) acc[e] = 0.0f;
+        uint32_t c8[4] = {0, 0, 0, 0};
+        uint32_t c2 = 0;
+        int in3 = 0;
+#pragma unroll 4
+        for (int i = 0; i < tn; i++) {
+            const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(bed + row_s[i]) + col);
+            const char* qrow = q_bytes + i * 16;
+#pragma unroll
+            for (int e = 0; e < 16; e++) {
+                // byte offset of the code inside the 16-byte row: ((w >> 2e) & 3) * 4
+                const uint32_t off = e == 0 ? (w << 2) & 0xCu : (w >> (2 * e - 2)) & 0xCu;
+                acc[e] += *reinterpret_cast<const float*>(qrow + off + (XCHR ? moff[e] : 0u));
+            }
+            c2 += (w & 0x55555555u) & ~(w >> 1);   // missing = code 01b, one count per 2-bit lane
+            if (++in3 == 3) {
+                in3 = 0;
+#pragma unroll
+                for (int g = 0; g < 4; g++) c8[g] += (c2 >> (2 * g)) & 0x03030303u;
+                c2 = 0;
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < 4; g++) c8[g] += (c2 >> (2 * g)) & 0x03030303u;
 #pragma unroll
         for (int e = 0; e < 16; e++) {
-            const uint32_t code = (w >> (2 * e)) & 3u;
-            const bool male = XCHR && ((mm >> (2 * e)) & 1u);
-            const double a0 = male ? m0 : q0, a2 = male ? m2 : q2, a3 = male ? m3 : q3;
-            acc[e] += code == 0 ? a0 : (code == 2 ? a2 : (code == 3 ? a3 : 0.0));
-            cn[e] += code != 1u;
+            dacc[e] += (double)acc[e];
+            miss[e] += (int)((c8[e & 3] >> (8 * (e >> 2))) & 0xFFu);   // byte b of c8[g] = individual 4b + g
         }
     }
+    if (!active) return;
+    const int span = (int)(kend - kbeg);
 #pragma unroll
     for (int e = 0; e < 16; e++) {
         const int64_t f = col * 16 + e;
         if (f < n_file) {
-            atomicAdd(diag + f, acc[e]);
-            atomicAdd(nii + f, cn[e]);
+            atomicAdd(diag + f, dacc[e]);
+            atomicAdd(nii + f, span - miss[e]);
         }
     }
 }
@@ -354,9 +402,9 @@ extern "C" int gcta_b200_diag_accum(const uint8_t* d_bed, int64_t pitch, int64_t
     GB_ARG(pitch > 0 && pitch % 16 == 0, "diag_accum: pitch must be a multiple of 16");
     GB_ARG(kc > 0, "diag_accum: empty SNP range");
     const int64_t cols = (n_file + 15) / 16;
-    dim3 grid((unsigned)((cols + 127) / 128), (unsigned)((kc + DIAG_SPLIT - 1) / DIAG_SPLIT));
-    if (d_sexmale) diag_accum_kernel<true><<<grid, 128, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, d_sexmale, d_include, k0, kc, d_zlut, d_diag, d_nii);
-    else diag_accum_kernel<false><<<grid, 128, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, d_zlut, d_diag, d_nii);
+    dim3 grid((unsigned)((cols + DIAG_THREADS - 1) / DIAG_THREADS), (unsigned)((kc + DIAG_SPLIT - 1) / DIAG_SPLIT));
+    if (d_sexmale) diag_accum_kernel<true><<<grid, DIAG_THREADS, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, d_sexmale, d_include, k0, kc, d_zlut, d_diag, d_nii);
+    else diag_accum_kernel<false><<<grid, DIAG_THREADS, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, d_zlut, d_diag, d_nii);
     GB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -480,9 +528,9 @@ extern "C" int gcta_b200_diag_accum_static(const uint8_t* d_bed, int64_t pitch, 
     snp_lut_kernel<<<(unsigned)((kc + 7) / 8), 256, 0, st>>>(d_bed, pitch, d_keepmask, d_include, k0, kc, lut);
     GB_CUDA(cudaGetLastError());
     const int64_t cols = (n_file + 15) / 16;
-    dim3 grid((unsigned)((cols + 127) / 128), (unsigned)((kc + DIAG_SPLIT - 1) / DIAG_SPLIT));
+    dim3 grid((unsigned)((cols + DIAG_THREADS - 1) / DIAG_THREADS), (unsigned)((kc + DIAG_SPLIT - 1) / DIAG_SPLIT));
     // diag_accum_kernel indexes its table by absolute SNP number; the table starts at k0
-    diag_accum_kernel<false><<<grid, 128, 0, st>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, lut - k0 * 8, d_diag, d_nii);
+    diag_accum_kernel<false><<<grid, DIAG_THREADS, 0, st>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, lut - k0 * 8, d_diag, d_nii);
     GB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -108,17 +108,17 @@ struct gcta_b200_plan {
     bool has_keep = false, has_include = false, has_mu = false;
     int64_t row_begin = 0, row_end = 0, ntiles = 0, chunk = 0, band_count = 0;
     // device
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;
     uint8_t* d_bed = nullptr;
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
     int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr;
     double *d_mu_in = nullptr, *d_mu = nullptr, *d_diag = nullptr;
     float *d_zlut = nullptr, *d_S = nullptr, *d_A_lower = nullptr;
-    void* d_Z = nullptr;
+    void* d_Zbuf[2] = {nullptr, nullptr};
     unsigned long long* d_total_missing = nullptr;
     std::vector<cudaEvent_t> events;
-    bool ran = false;
+    bool ran = false, overlap = false;
     int64_t total_missing = 0;
     std::vector<void*> allocs;
 };
@@ -147,9 +147,11 @@ extern "C" void gcta_b200_plan_destroy(gcta_b200_plan* p)
     if (!p) return;
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
+    if (p->stream2) cudaStreamSynchronize(p->stream2);
     for (cudaEvent_t e : p->events) cudaEventDestroy(e);
     for (void* q : p->allocs) cudaFree(q);
     if (p->stream) cudaStreamDestroy(p->stream);
+    if (p->stream2) cudaStreamDestroy(p->stream2);
     delete p;
 }
 
@@ -204,6 +206,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     p->ntiles = gcta_b200_tile_list(n, p->row_begin, p->row_end, nullptr);
     p->band_count = p->row_end * (p->row_end + 1) / 2 - p->row_begin * (p->row_begin + 1) / 2;
     PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream2, cudaStreamNonBlocking));
 
     // fixed-size buffers
     PLAN_TRY(dev_alloc(p, &p->d_bed, (size_t)p->pitch * a->m_file, err, errcap));
@@ -253,12 +256,14 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     {
         size_t free_b = 0, total_b = 0;
         PLAN_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        int64_t budget = std::min<int64_t>((int64_t)(free_b / 3), 8ll << 30);
+        int64_t budget = std::min<int64_t>((int64_t)(free_b / 4), 8ll << 30);   // per Z buffer (two when overlapping)
         int64_t kc = a->chunk_snps > 0 ? a->chunk_snps : budget / (p->ldz * 2);
         kc = std::max<int64_t>(64, kc / 64 * 64);
         kc = std::min<int64_t>(kc, round_up(m, 64));
         p->chunk = kc;
-        PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Z, (size_t)kc * p->ldz, err, errcap));
+        PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz, err, errcap));
+        p->overlap = getenv("GCTA_B200_OVERLAP") && atoi(getenv("GCTA_B200_OVERLAP")) > 0;
+        if (p->overlap && kc < round_up(m, 64)) PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[1], (size_t)kc * p->ldz, err, errcap));
     }
     *out_plan = p;
     return 0;
@@ -345,40 +350,52 @@ extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* e
     using namespace gb;
     GB_ARG(p && out, "plan_run: null argument");
     GB_CUDA(cudaSetDevice(p->device));
-    cudaStream_t st = p->stream;
+    // Two streams: `sd` standardises chunk c+1 (K1, K1d - HBM / ALU work) while `st` runs the SYRK of
+    // chunk c on the tensor cores; two Z buffers alternate.  Ordering is by events only.
+    // Measured on cfg3 (profiles/README.md): co-running the decode with the SYRK steals issue slots and power
+    // from the tensor loop (K2 +30 %), so by default both run on one stream; GCTA_B200_OVERLAP=1 enables it.
+    cudaStream_t st = p->stream, sd = p->overlap ? p->stream2 : p->stream;
     const int64_t nchunks = (p->m + p->chunk - 1) / p->chunk;
-    // events: [0] start, then per chunk (after decode+diag, after syrk), then after paircount, after finalize
-    const size_t need = (size_t)(2 * nchunks + 4);
+    // events: [0] start, [1] buffers cleared, then 4 per chunk (decode start/end, syrk start/end), then 2
+    const size_t need = (size_t)(4 * nchunks + 4);
     while (p->events.size() < need) {
         cudaEvent_t ev;
         GB_CUDA(cudaEventCreate(&ev));
         p->events.push_back(ev);
     }
+    auto EV = [&](int64_t c, int which) { return p->events[(size_t)(2 + 4 * c + which)]; };
     int launches = 0;
     GB_CUDA(cudaEventRecord(p->events[0], st));
     GB_CUDA(cudaMemsetAsync(p->d_S, 0, (size_t)p->ntiles * TILE_M * TILE_N * sizeof(float), st));
     GB_CUDA(cudaMemsetAsync(p->d_diag, 0, (size_t)p->n_file * 8, st));
     GB_CUDA(cudaMemsetAsync(p->d_nii, 0, (size_t)p->n_file * 4, st));
     GB_CUDA(cudaMemsetAsync(p->d_total_missing, 0, 8, st));
+    GB_CUDA(cudaEventRecord(p->events[1], st));
+    GB_CUDA(cudaStreamWaitEvent(sd, p->events[1], 0));
     for (int64_t c = 0; c < nchunks; c++) {
         const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
+        void* Z = (p->overlap && p->d_Zbuf[1]) ? p->d_Zbuf[c & 1] : p->d_Zbuf[0];
+        if (c >= 2) GB_CUDA(cudaStreamWaitEvent(sd, EV(c - 2, 3), 0));   // the SYRK that last read this Z buffer
+        GB_CUDA(cudaEventRecord(EV(c, 0), sd));
         int rc = gcta_b200_bed_decode(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
-                                      p->d_mu_in, p->xchr, p->alg, p->operand, p->d_Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
-                                      p->d_total_missing, st, err, errcap);
+                                      p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
+                                      p->d_total_missing, sd, err, errcap);
         if (rc) return rc;
-        rc = gcta_b200_diag_accum(p->d_bed, p->pitch, p->n_file, p->d_sexmale, p->d_include, k0, kc, p->d_zlut, p->d_diag, p->d_nii, st, err, errcap);
+        rc = gcta_b200_diag_accum(p->d_bed, p->pitch, p->n_file, p->d_sexmale, p->d_include, k0, kc, p->d_zlut, p->d_diag, p->d_nii, sd, err, errcap);
         if (rc) return rc;
-        GB_CUDA(cudaEventRecord(p->events[1 + 2 * c], st));
-        rc = gcta_b200_syrk_tiles(p->d_Z, p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+        GB_CUDA(cudaEventRecord(EV(c, 1), sd));
+        GB_CUDA(cudaStreamWaitEvent(st, EV(c, 1), 0));
+        GB_CUDA(cudaEventRecord(EV(c, 2), st));
+        rc = gcta_b200_syrk_tiles(Z, p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
         if (rc) return rc;
-        GB_CUDA(cudaEventRecord(p->events[2 + 2 * c], st));
+        GB_CUDA(cudaEventRecord(EV(c, 3), st));
         launches += 3;
     }
     unsigned long long tm = 0;
     GB_CUDA(cudaMemcpyAsync(&tm, p->d_total_missing, 8, cudaMemcpyDeviceToHost, st));
     GB_CUDA(cudaStreamSynchronize(st));
     p->total_missing = (int64_t)tm;
-    const size_t e_pc = 1 + 2 * nchunks, e_fin = e_pc + 1;
+    const size_t e_pc = 2 + 4 * nchunks, e_fin = e_pc + 1;
     if (tm > 0) {
         const int64_t nwords = (p->m + 31) / 32;
         if (!p->d_planes) {
@@ -390,7 +407,7 @@ extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* e
             if (rc) return rc;
         }
         GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
-        // planes in slabs of at most 65535 words (grid.y limit)
+        // planes in slabs of at most 32768 words (grid.y limit)
         for (int64_t w0 = 0; w0 < nwords; w0 += 32768) {
             const int64_t k0 = w0 * 32, kc = std::min<int64_t>(32768 * 32, p->m - k0);
             int rc = gcta_b200_nonmiss_planes(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, p->d_planes, p->ldz, st, err, errcap);
@@ -410,15 +427,16 @@ extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* e
     }
     GB_CUDA(cudaEventRecord(p->events[e_fin], st));
     GB_CUDA(cudaStreamSynchronize(st));
+    // decode and SYRK overlap, so the phase times are per-stream busy times and do not add up to ms_total
     out->ms_decode = out->ms_syrk = 0.f;
     for (int64_t c = 0; c < nchunks; c++) {
         float a = 0.f, b = 0.f;
-        GB_CUDA(cudaEventElapsedTime(&a, p->events[c == 0 ? 0 : 2 * c], p->events[1 + 2 * c]));
-        GB_CUDA(cudaEventElapsedTime(&b, p->events[1 + 2 * c], p->events[2 + 2 * c]));
+        GB_CUDA(cudaEventElapsedTime(&a, EV(c, 0), EV(c, 1)));
+        GB_CUDA(cudaEventElapsedTime(&b, EV(c, 2), EV(c, 3)));
         out->ms_decode += a;
         out->ms_syrk += b;
     }
-    GB_CUDA(cudaEventElapsedTime(&out->ms_paircount, p->events[2 * nchunks], p->events[e_pc]));
+    GB_CUDA(cudaEventElapsedTime(&out->ms_paircount, EV(nchunks - 1, 3), p->events[e_pc]));
     GB_CUDA(cudaEventElapsedTime(&out->ms_finalize, p->events[e_pc], p->events[e_fin]));
     GB_CUDA(cudaEventElapsedTime(&out->ms_total, p->events[0], p->events[e_fin]));
     out->launches = launches;

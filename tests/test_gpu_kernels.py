@@ -214,7 +214,9 @@ def test_diag_planes_paircount_finalize():
     z, ok, mu = oracle.standardise(x)
     assert np.array_equal(nii.cpu().numpy(), ok.sum(0).astype(np.int32))
     dref = (z.astype(np.float64) ** 2).sum(0)
-    assert np.abs(diag.cpu().numpy() - dref).max() <= 1e-9 * dref.max()
+    # squares are rounded once to f32 (6e-8, unbiased) and summed in f32 per 192-SNP tile, f64 across tiles
+    err = diag.cpu().numpy() - dref
+    assert np.abs(err).max() <= 2e-6 * dref.max() and abs(err.mean()) <= 2e-7 * dref.mean()
     # K1m
     ldm = r["ldz"]
     nwords = (m + 31) // 32
