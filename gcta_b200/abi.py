@@ -18,7 +18,7 @@ TILE_M, TILE_N = 256, 256
 
 EXPORTS = [
     "gcta_b200_make_grm", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth", "gcta_b200_plan_download_bed",
-    "gcta_b200_plan_run", "gcta_b200_plan_download", "gcta_b200_plan_device_results", "gcta_b200_plan_destroy",
+    "gcta_b200_plan_run", "gcta_b200_plan_run_streamed", "gcta_b200_plan_download", "gcta_b200_plan_device_results", "gcta_b200_plan_destroy",
     "gcta_b200_bed_decode", "gcta_b200_diag_accum", "gcta_b200_diag_accum_static", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles",
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
     "gcta_b200_partition", "gcta_b200_tile_list", "gcta_b200_allele_counts",
@@ -171,6 +171,12 @@ class Plan:
     def run(self):
         err = C.create_string_buffer(ERRCAP)
         _check(lib().gcta_b200_plan_run(self._h, C.byref(self.out), err, ERRCAP), err)
+        return self.out
+
+    def run_streamed(self, bed_host):
+        """upload + run with the host->HBM copy of chunk c+1 hidden behind the compute of chunk c"""
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_plan_run_streamed(self._h, C.c_void_p(_ptr(bed_host)), C.byref(self.out), err, ERRCAP), err)
         return self.out
 
     def download(self, A_lower, N_lower=None, mu=None):

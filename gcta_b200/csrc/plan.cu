@@ -108,7 +108,9 @@ struct gcta_b200_plan {
     bool has_keep = false, has_include = false, has_mu = false;
     int64_t row_begin = 0, row_end = 0, ntiles = 0, chunk = 0, band_count = 0;
     // device
-    cudaStream_t stream = nullptr, stream2 = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr, stream_copy = nullptr;
+    std::vector<cudaEvent_t> upload_events;
+    std::vector<int32_t> h_include;
     uint8_t* d_bed = nullptr;
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
@@ -152,6 +154,8 @@ extern "C" void gcta_b200_plan_destroy(gcta_b200_plan* p)
     for (void* q : p->allocs) cudaFree(q);
     if (p->stream) cudaStreamDestroy(p->stream);
     if (p->stream2) cudaStreamDestroy(p->stream2);
+    if (p->stream_copy) cudaStreamDestroy(p->stream_copy);
+    for (cudaEvent_t e : p->upload_events) cudaEventDestroy(e);
     delete p;
 }
 
@@ -210,6 +214,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
 
     // fixed-size buffers
     PLAN_TRY(dev_alloc(p, &p->d_bed, (size_t)p->pitch * a->m_file, err, errcap));
+    if (p->pitch != p->stride) PLAN_CUDA(cudaMemset(p->d_bed, 0, (size_t)p->pitch * a->m_file));
     PLAN_TRY(dev_alloc(p, &p->d_keepmask, (size_t)p->pitch / 4, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_mu, (size_t)m, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_cnt, (size_t)m, err, errcap));
@@ -242,6 +247,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     if (p->has_include) {
         PLAN_TRY(dev_alloc(p, &p->d_include, (size_t)m, err, errcap));
         PLAN_CUDA(cudaMemcpy(p->d_include, a->include, (size_t)m * 4, cudaMemcpyHostToDevice));
+        p->h_include.assign(a->include, a->include + m);
     }
     if (p->has_mu) {
         PLAN_TRY(dev_alloc(p, &p->d_mu_in, (size_t)m, err, errcap));
@@ -345,11 +351,39 @@ extern "C" int gcta_b200_plan_synth(gcta_b200_plan* p, uint64_t seed, const uint
     return 0;
 }
 
-extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* err, size_t errcap)
+// plan_run and plan_run_streamed.  With bed_host != NULL the packed rows of chunk c+1 travel host -> HBM on the
+// copy stream while chunk c is standardised and contracted, so the upload hides behind the tensor work.
+static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap)
 {
     using namespace gb;
     GB_ARG(p && out, "plan_run: null argument");
     GB_CUDA(cudaSetDevice(p->device));
+    std::vector<cudaEvent_t>& up = p->upload_events;
+    const int64_t nch_up = (p->m + p->chunk - 1) / p->chunk;
+    if (bed_host) {
+        if (!p->stream_copy) GB_CUDA(cudaStreamCreateWithFlags(&p->stream_copy, cudaStreamNonBlocking));
+        while ((int64_t)up.size() < nch_up) {
+            cudaEvent_t ev;
+            GB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            up.push_back(ev);
+        }
+    }
+    // host -> HBM copy of the file rows chunk c needs; issued one chunk ahead of the compute so that it overlaps
+    // even when the host buffer is pageable (then the call blocks the host, but the GPU is already busy)
+    auto issue_upload = [&](int64_t c) -> cudaError_t {
+        if (!bed_host || c >= nch_up) return cudaSuccess;
+        const int64_t k0 = c * p->chunk, k1 = std::min<int64_t>(p->m, k0 + p->chunk);
+        int64_t r0 = k0, r1 = k1;
+        if (p->has_include) {
+            r0 = *std::min_element(p->h_include.begin() + k0, p->h_include.begin() + k1);
+            r1 = *std::max_element(p->h_include.begin() + k0, p->h_include.begin() + k1) + 1;
+        }
+        cudaError_t e = cudaMemcpy2DAsync(p->d_bed + r0 * p->pitch, (size_t)p->pitch, bed_host + r0 * p->stride, (size_t)p->stride,
+                                          (size_t)p->stride, (size_t)(r1 - r0), cudaMemcpyHostToDevice, p->stream_copy);
+        if (e != cudaSuccess) return e;
+        return cudaEventRecord(up[c], p->stream_copy);
+    };
+    GB_CUDA(issue_upload(0));
     // Two streams: `sd` standardises chunk c+1 (K1, K1d - HBM / ALU work) while `st` runs the SYRK of
     // chunk c on the tensor cores; two Z buffers alternate.  Ordering is by events only.
     // Measured on cfg3 (profiles/README.md): co-running the decode with the SYRK steals issue slots and power
@@ -376,6 +410,7 @@ extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* e
         const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
         void* Z = (p->overlap && p->d_Zbuf[1]) ? p->d_Zbuf[c & 1] : p->d_Zbuf[0];
         if (c >= 2) GB_CUDA(cudaStreamWaitEvent(sd, EV(c - 2, 3), 0));   // the SYRK that last read this Z buffer
+        if (bed_host) GB_CUDA(cudaStreamWaitEvent(sd, up[c], 0));        // this chunk's packed rows have landed
         GB_CUDA(cudaEventRecord(EV(c, 0), sd));
         int rc = gcta_b200_bed_decode(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
                                       p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
@@ -390,6 +425,7 @@ extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* e
         if (rc) return rc;
         GB_CUDA(cudaEventRecord(EV(c, 3), st));
         launches += 3;
+        GB_CUDA(issue_upload(c + 1));
     }
     unsigned long long tm = 0;
     GB_CUDA(cudaMemcpyAsync(&tm, p->d_total_missing, 8, cudaMemcpyDeviceToHost, st));
@@ -447,6 +483,18 @@ extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* e
     return 0;
 }
 
+extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* err, size_t errcap)
+{
+    return plan_run_impl(p, nullptr, out, err, errcap);
+}
+
+extern "C" int gcta_b200_plan_run_streamed(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(bed_host, "plan_run_streamed: null bed");
+    return plan_run_impl(p, bed_host, out, err, errcap);
+}
+
 extern "C" int gcta_b200_plan_device_results(gcta_b200_plan* p, const float** dA, const int32_t** dN, int64_t* count)
 {
     if (!p || !p->ran) return GCTA_B200_ERR_ARG;
@@ -497,9 +545,8 @@ extern "C" int gcta_b200_make_grm(const gcta_b200_args* a, gcta_b200_out* out, c
     cudaEvent_t e0, e1, e2, e3;
     cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2); cudaEventCreate(&e3);
     cudaEventRecord(e0, p->stream);
-    rc = gcta_b200_plan_upload(p, a->bed, err, errcap);
-    cudaEventRecord(e1, p->stream);
-    if (!rc) rc = gcta_b200_plan_run(p, out, err, errcap);
+    cudaEventRecord(e1, p->stream);   // the upload is streamed chunk by chunk inside the run (ms_h2d ~ 0)
+    if (!rc) rc = gcta_b200_plan_run_streamed(p, a->bed, out, err, errcap);
     cudaEventRecord(e2, p->stream);
     if (!rc) rc = gcta_b200_plan_download(p, out, err, errcap);
     cudaEventRecord(e3, p->stream);

@@ -111,6 +111,10 @@ int gcta_b200_plan_synth(gcta_b200_plan* plan, uint64_t seed, const uint32_t* th
 int gcta_b200_plan_download_bed(gcta_b200_plan* plan, uint8_t* bed_host, char* err, size_t errcap);
 /* decode + SYRK + pair counts + finalize on the device; results stay in HBM */
 int gcta_b200_plan_run(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size_t errcap);
+/* plan_upload + plan_run in one call, pipelined: the packed rows of SNP chunk c+1 are copied host -> HBM on a
+ * copy stream while chunk c is standardised and contracted (use pinned host memory for full overlap).  This is what
+ * gcta_b200_make_grm runs. */
+int gcta_b200_plan_run_streamed(gcta_b200_plan* plan, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap);
 /* copy this plan's row band of A (and N when N_lower != NULL) to host memory */
 int gcta_b200_plan_download(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size_t errcap);
 /* device pointers of the finalised band (float A, int32 N; N is NULL when nothing is missing
