@@ -21,7 +21,7 @@ EXPORTS = [
     "gcta_b200_plan_run", "gcta_b200_plan_run_streamed", "gcta_b200_plan_download", "gcta_b200_plan_device_results", "gcta_b200_plan_destroy",
     "gcta_b200_bed_decode", "gcta_b200_diag_accum", "gcta_b200_diag_accum_static", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles",
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
-    "gcta_b200_partition", "gcta_b200_tile_list", "gcta_b200_allele_counts",
+    "gcta_b200_partition", "gcta_b200_tile_list", "gcta_b200_allele_counts", "gcta_b200_nonmiss_matrix", "gcta_b200_count_tiles",
 ]
 
 

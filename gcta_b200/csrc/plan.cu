@@ -266,6 +266,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         int64_t kc = a->chunk_snps > 0 ? a->chunk_snps : budget / (p->ldz * 2);
         kc = std::max<int64_t>(64, kc / 64 * 64);
         kc = std::min<int64_t>(kc, round_up(m, 64));
+        kc = std::min<int64_t>(kc, 1 << 23);   // counts of one chunk must stay exact in the FP32 accumulator
         p->chunk = kc;
         PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz, err, errcap));
         p->overlap = getenv("GCTA_B200_OVERLAP") && atoi(getenv("GCTA_B200_OVERLAP")) > 0;
@@ -432,14 +433,33 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     GB_CUDA(cudaStreamSynchronize(st));
     p->total_missing = (int64_t)tm;
     const size_t e_pc = 2 + 4 * nchunks, e_fin = e_pc + 1;
-    if (tm > 0) {
+    // N_ij is only needed when something is missing (otherwise N == m, which is what grm.cpp:291 yields).
+    // Default: indicator matrix + the SYRK kernel in counting mode (exact, tensor rate).  GCTA_B200_N_MODE=popc
+    // selects the AND+popc kernel over bit planes instead (same integers, ~8x slower; kept as the cross-check).
+    const char* nmode = getenv("GCTA_B200_N_MODE");
+    const bool use_popc = nmode && strcmp(nmode, "popc") == 0;
+    if (tm > 0 && !p->d_Ntiles) {
+        int rc = dev_alloc(p, &p->d_Ntiles, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap);
+        if (rc) return rc;
+        rc = dev_alloc(p, &p->d_N_lower, (size_t)p->band_count, err, errcap);
+        if (rc) return rc;
+    }
+    if (tm > 0 && !use_popc) {
+        GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
+        for (int64_t c = 0; c < nchunks; c++) {   // the Z buffer is free again: reuse it for the indicator chunks
+            const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
+            int rc = gcta_b200_nonmiss_matrix(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, p->operand,
+                                              p->d_Zbuf[0], p->ldz, st, err, errcap);
+            if (rc) return rc;
+            rc = gcta_b200_count_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_Ntiles, st, err, errcap);
+            if (rc) return rc;
+            launches += 2;
+        }
+    }
+    if (tm > 0 && use_popc) {
         const int64_t nwords = (p->m + 31) / 32;
         if (!p->d_planes) {
             int rc = dev_alloc(p, &p->d_planes, (size_t)nwords * p->ldz, err, errcap);
-            if (rc) return rc;
-            rc = dev_alloc(p, &p->d_Ntiles, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap);
-            if (rc) return rc;
-            rc = dev_alloc(p, &p->d_N_lower, (size_t)p->band_count, err, errcap);
             if (rc) return rc;
         }
         GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));

@@ -44,6 +44,10 @@ __device__ __forceinline__ uint64_t make_mn_desc(uint32_t smem_addr)
            (1ull << 46) | (2ull << 61);
 }
 
+// INT_ACC = false: S (float) += accumulator.  INT_ACC = true: the operands are 0/1 indicators, every
+// partial sum is an integer below 2^24 and therefore exact in FP32, and the epilogue adds it into an
+// int32 tile - the pair counts N_ij on the tensor cores, bit-exact.
+template <bool INT_ACC>
 __global__ void __launch_bounds__(SYRK_THREADS, 1)
 syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__ tiles, int ntiles, int nkb,
                   float* __restrict__ S, uint32_t idesc)
@@ -152,12 +156,22 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restri
 #pragma unroll
                 for (int g = 0; g < 8; g++) {
                     float4* p = Stile + (size_t)(c0 / 4 + g) * TILE_M + r;
-                    float4 o = *p;
-                    o.x += __uint_as_float(v[4 * g + 0]);
-                    o.y += __uint_as_float(v[4 * g + 1]);
-                    o.z += __uint_as_float(v[4 * g + 2]);
-                    o.w += __uint_as_float(v[4 * g + 3]);
-                    *p = o;
+                    if (INT_ACC) {
+                        int4* pi = reinterpret_cast<int4*>(p);
+                        int4 o = *pi;
+                        o.x += __float2int_rn(__uint_as_float(v[4 * g + 0]));
+                        o.y += __float2int_rn(__uint_as_float(v[4 * g + 1]));
+                        o.z += __float2int_rn(__uint_as_float(v[4 * g + 2]));
+                        o.w += __float2int_rn(__uint_as_float(v[4 * g + 3]));
+                        *pi = o;
+                    } else {
+                        float4 o = *p;
+                        o.x += __uint_as_float(v[4 * g + 0]);
+                        o.y += __uint_as_float(v[4 * g + 1]);
+                        o.z += __uint_as_float(v[4 * g + 2]);
+                        o.w += __uint_as_float(v[4 * g + 3]);
+                        *p = o;
+                    }
                 }
             }
             tc_fence_before();
@@ -193,8 +207,8 @@ static EncodeTiledFn get_encode_fn()
 
 }  // namespace gb
 
-extern "C" int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
-                                    int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
+static int syrk_launch(bool int_acc, const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
+                       int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
 {
     using namespace gb;
     GB_ARG(d_Z && d_tiles && d_S, "syrk: null pointer");
@@ -228,12 +242,31 @@ extern "C" int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad
 
     static bool attr_set[64] = {};
     if (dev < 64 && !attr_set[dev]) {
-        GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
+        GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
+        GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
         attr_set[dev] = true;
     }
     int grid = (int)(ntiles < sms ? ntiles : sms);
-    syrk_tiles_kernel<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, reinterpret_cast<const int2*>(d_tiles),
-                                                                                (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
+    if (int_acc)
+        syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(
+            tmap, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
+    else
+        syrk_tiles_kernel<false><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(
+            tmap, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
     GB_CUDA(cudaGetLastError());
     return 0;
+}
+
+extern "C" int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
+                                    int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
+{
+    return syrk_launch(false, d_Z, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap);
+}
+
+extern "C" int gcta_b200_count_tiles(const void* d_OK, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
+                                     int64_t ntiles, int32_t* d_Ntiles, void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(kc_pad < (1 << 24), "count_tiles: more than 2^24 SNPs per call would not be exact in FP32");
+    return syrk_launch(true, d_OK, ldz, kc_pad, operand, d_tiles, ntiles, reinterpret_cast<float*>(d_Ntiles), stream, err, errcap);
 }

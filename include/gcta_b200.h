@@ -198,6 +198,17 @@ int gcta_b200_paircount_tiles(const uint32_t* d_planes, int64_t ldm, int64_t nwo
                               const int32_t* d_tiles, int64_t ntiles, int32_t* d_Ntiles,
                               void* stream, char* err, size_t errcap);
 
+/* K1n + K2 in counting mode - the default way N is computed: the non-missing indicator of every genotype as a
+ * 16-bit 0/1 matrix laid out like Z (gcta_b200_nonmiss_matrix), contracted by the SYRK kernel with an int32
+ * epilogue (gcta_b200_count_tiles).  0/1 products and integer partial sums below 2^24 are exact in the FP32
+ * tensor-core accumulator, so the result is bit-identical to K3's AND+popc (tests assert this) at the tensor
+ * rate.  d_Ntiles as for gcta_b200_paircount_tiles.  grm.cpp:270, 291. */
+int gcta_b200_nonmiss_matrix(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_keep, int64_t n,
+                             const int32_t* d_include, int64_t k0, int64_t kc, int32_t operand, void* d_OK, int64_t ldz,
+                             void* stream, char* err, size_t errcap);
+int gcta_b200_count_tiles(const void* d_OK, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
+                          int64_t ntiles, int32_t* d_Ntiles, void* stream, char* err, size_t errcap);
+
 /* K4 - A = S / N with the reference's zero-count rules (grm.cpp:273-275, 294), exact diagonal
  * from K1d, packed to .grm.gz order.  d_Ntiles NULL means N == m_const for every pair. */
 int gcta_b200_finalize_tiles(const float* d_S, const int32_t* d_Ntiles, int32_t m_const,

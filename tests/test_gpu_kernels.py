@@ -238,6 +238,18 @@ def test_diag_planes_paircount_finalize():
     Nd = s_tiles_to_dense(Nt.cpu().numpy(), tiles, ldm)
     ii, jj = np.tril_indices(n)
     assert np.array_equal(Nd[ii, jj], Nref[ii, jj])
+    # K1n + K2 in counting mode: the tensor-core route must give the very same integers as AND+popc
+    for operand, dt in ((abi.FP16, torch.float16), (abi.BF16, torch.bfloat16)):
+        OK = torch.full((r["kc_pad"], ldm), 7, dtype=torch.int16, device="cuda")
+        abi.call("gcta_b200_nonmiss_matrix", ptr(r["d_bed"]), I64(r["pitch"]), I64(n), P(None), I64(n), P(None), I64(0), I64(m),
+                 I32(operand), ptr(OK), I64(ldm), stream())
+        okm = OK.view(dt).float().cpu().numpy()
+        assert np.array_equal(okm[:m, :n], ok.astype(np.float32)) and not okm[m:].any() and not okm[:, n:].any()
+        Nt2 = torch.zeros_like(Nt)
+        for _ in range(2):   # two "chunks" of the same data: counts accumulate in int32
+            abi.call("gcta_b200_count_tiles", ptr(OK), I64(ldm), I64(r["kc_pad"]), I32(operand), ptr(d_tiles), I64(len(tiles)), ptr(Nt2), stream())
+        Nd2 = s_tiles_to_dense(Nt2.cpu().numpy(), tiles, ldm)
+        assert np.array_equal(Nd2[ii, jj], 2 * Nref[ii, jj])
     # K2 + K4
     S, _ = run_syrk(r["Z"].view(torch.float16), n, abi.FP16)
     A = torch.zeros(n * (n + 1) // 2, dtype=torch.float32, device="cuda")

@@ -123,6 +123,20 @@ def test_larger_with_missing_sub_block_check():
     assert np.array_equal(mu[:200], mu_ref)
 
 
+def test_tensor_core_counts_equal_popc_counts(monkeypatch):
+    """N via the indicator SYRK (default) and via AND+popc over bit planes (GCTA_B200_N_MODE=popc) are the same
+    integers, with a keep list (gather path), several chunks and heavy missingness."""
+    n_file, m = 900, 2100
+    bed = synth.make_bed_payload(63, n_file, m, miss_rate=0.2)
+    keep = np.sort(np.random.default_rng(2).choice(n_file, 611, replace=False)).astype(np.int32)
+    A0, N0, _, o0 = abi.make_grm(bed, n_file, m, keep=keep, chunk_snps=512)
+    monkeypatch.setenv("GCTA_B200_N_MODE", "popc")
+    A1, N1, _, o1 = abi.make_grm(bed, n_file, m, keep=keep, chunk_snps=512)
+    assert np.array_equal(N0, N1) and np.array_equal(A0, A1)
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n_file, keep=keep)
+    check_grm(A0, N0, pack_lower(Aref), pack_lower(Nref))
+
+
 def test_errors_are_reported_not_thrown():
     bed = synth.make_bed_payload(1, 40, 50)
     with pytest.raises(abi.GctaB200Error) as e:
