@@ -191,19 +191,42 @@ def main_ours(a, rank, world, local_rank):
         A_ptr = h_A.data_ptr() - 4 * base  # the ABI indexes the whole packed triangle; only the band is touched
         N_ptr = h_N.ctypes.data - 4 * base
         e2e_steps = max(1, min(a.steps, a.e2e_steps))
-        for _ in range(1):
-            plan.run_streamed(h_bed.data_ptr()); plan.download(A_ptr, N_ptr)
+        if world == 1:
+            def e2e_step():
+                plan.run_streamed(h_bed.data_ptr())   # H2D of chunk c+1 overlaps the compute of chunk c
+                plan.download(A_ptr, N_ptr)
+            api = "gcta_b200_plan_run_streamed + plan_download (what gcta_b200_make_grm does), pinned host buffers"
+            h2d = stride * m
+        else:
+            # every rank pulls 1/N of the SNP rows over its own PCIe link, the ranks all-gather the packed rows over
+            # NVLink (NCCL) into the buffer the plan reads, then each computes its row band
+            import torch.distributed as tdist
+            rows_per = -(-m // world)
+            pitch = plan.use_device_bed(None)
+            d_all = torch.zeros(rows_per * world * pitch, dtype=torch.uint8, device="cuda")
+            plan.use_device_bed(d_all.data_ptr())
+            r0, r1 = min(m, rank * rows_per), min(m, (rank + 1) * rows_per)
+            mine = d_all[rank * rows_per * pitch:(rank + 1) * rows_per * pitch]
+
+            def e2e_step():
+                plan.upload_rows(h_bed.data_ptr(), r0, r1)
+                tdist.all_gather_into_tensor(d_all, mine)
+                torch.cuda.synchronize()
+                plan.run()
+                plan.download(A_ptr, N_ptr)
+            api = ("gcta_b200_plan_upload_rows (1/N of the rows per rank) + NCCL all-gather of the packed rows over NVLink + "
+                   "plan_run + plan_download, pinned host buffers")
+            h2d = stride * (r1 - r0)
+        e2e_step()
         barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
-            plan.run_streamed(h_bed.data_ptr())   # H2D of chunk c+1 overlaps the compute of chunk c
-            plan.download(A_ptr, N_ptr)
+            e2e_step()
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         d2h = sum_over_ranks(cnt * 4 * (2 if o.total_missing > 0 else 1))
-        e2e = {"value": pairs_total * m * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(stride * m * world),
-               "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
-               "api": "gcta_b200_plan_run_streamed + plan_download (what gcta_b200_make_grm does), pinned host buffers"}
+        e2e = {"value": pairs_total * m * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(h2d)),
+               "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps, "api": api}
         if rank == 0:
             diag_idx = np.arange(min(1000, row_end - row_begin))
             di = (diag_idx + row_begin) * (diag_idx + row_begin + 1) // 2 + diag_idx + row_begin - base

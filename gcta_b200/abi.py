@@ -22,6 +22,7 @@ EXPORTS = [
     "gcta_b200_bed_decode", "gcta_b200_diag_accum", "gcta_b200_diag_accum_static", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles",
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
     "gcta_b200_partition", "gcta_b200_tile_list", "gcta_b200_allele_counts", "gcta_b200_nonmiss_matrix", "gcta_b200_count_tiles",
+    "gcta_b200_plan_use_device_bed", "gcta_b200_plan_upload_rows",
 ]
 
 
@@ -163,6 +164,17 @@ class Plan:
         thr = np.ascontiguousarray(thr, dtype=np.uint32)
         err = C.create_string_buffer(ERRCAP)
         _check(lib().gcta_b200_plan_synth(self._h, C.c_uint64(seed), C.c_void_p(thr.ctypes.data), err, ERRCAP), err)
+
+    def use_device_bed(self, d_bed=None) -> int:
+        """make the plan read genotypes from caller-owned device memory; returns the row pitch in bytes"""
+        pitch = C.c_int64()
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_plan_use_device_bed(self._h, C.c_void_p(_ptr(d_bed)), C.byref(pitch), err, ERRCAP), err)
+        return pitch.value
+
+    def upload_rows(self, bed_host, row_begin, row_end):
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_plan_upload_rows(self._h, C.c_void_p(_ptr(bed_host)), C.c_int64(row_begin), C.c_int64(row_end), err, ERRCAP), err)
 
     def download_bed(self, bed_host):
         err = C.create_string_buffer(ERRCAP)

@@ -57,7 +57,7 @@ struct DecodeParams {
     int64_t n_file;
     const uint32_t* keepmask;
     const int32_t* keep;
-    int64_t n;
+    int64_t n, n_out;
     const uint32_t* sexmale;
     const int32_t* include;
     int64_t k0, kc, kc_pad;
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
     for (int ch = tid; ch < nchunk; ch += GROUP) {
         const int64_t i0 = (int64_t)ch * 8;
         uint32_t o[4] = {0, 0, 0, 0};
-        if (i0 < p.n) {
+        if (i0 < p.n_out) {
             if (!p.keep) {
                 const uint32_t w = __ldg(row2 + ch);
                 // sexmale marks individual 16w+t at bit 2t, i.e. the same 2-bit slots as the genotypes
@@ -177,14 +177,14 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
                     const uint32_t code = (w >> (2 * e)) & 3u;
                     const uint64_t lut = (XCHR && ((mb >> (2 * e)) & 1u)) ? lutM : lutF;
                     uint32_t v = (uint32_t)(lut >> (16 * code)) & 0xFFFFu;
-                    if (i0 + e >= p.n) v = 0;
+                    if (i0 + e >= p.n_out) v = 0;
                     o[e >> 1] |= v << (16 * (e & 1));
                 }
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; e++) {
                     uint32_t v = 0;
-                    if (i0 + e < p.n) {
+                    if (i0 + e < p.n_out) {
                         const int f = p.keep[i0 + e];
                         const uint32_t code = (row[f >> 2] >> ((f & 3) * 2)) & 3u;
                         const bool male = XCHR && ((p.sexmale[f >> 4] >> ((f & 15) * 2)) & 1u);
@@ -367,13 +367,13 @@ extern "C" int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t
     GB_ARG(pitch > 0 && pitch % 16 == 0 && ((uintptr_t)d_bed & 15) == 0, "bed_decode: bed pitch and pointer must be multiples of 16 bytes");
     GB_ARG(pitch * 4 >= n_file && n_file > 0, "bed_decode: pitch too small for n_file");
     GB_ARG(n > 0 && n <= n_file && (d_keep || n == n_file), "bed_decode: n must equal n_file when keep is NULL");
-    GB_ARG(ldz % 256 == 0 && ldz >= n, "bed_decode: ldz must be a multiple of 256 and >= n");
+    GB_ARG(ldz > 0 && ldz % 256 == 0, "bed_decode: ldz must be a positive multiple of 256");
     GB_ARG(((uintptr_t)d_Z & 15) == 0, "bed_decode: Z must be 16-byte aligned");
     GB_ARG(kc > 0 && k0 >= 0, "bed_decode: empty SNP range");
     GB_ARG(!xchr || d_sexmale, "bed_decode: xchr needs the male mask");
     GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "bed_decode: unknown operand type");
     DecodeParams p;
-    p.bed = d_bed; p.pitch = pitch; p.n_file = n_file; p.keepmask = d_keepmask; p.keep = d_keep; p.n = n;
+    p.bed = d_bed; p.pitch = pitch; p.n_file = n_file; p.keepmask = d_keepmask; p.keep = d_keep; p.n = n; p.n_out = n < ldz ? n : ldz;  // a Z narrower than n keeps only the first ldz individuals (row bands need no more)
     p.sexmale = d_sexmale; p.include = d_include; p.k0 = k0; p.kc = kc; p.kc_pad = (kc + 63) / 64 * 64;
     p.mu_in = d_mu_in; p.divide = alg == 0; p.bf16 = operand == GCTA_B200_BF16;
     p.Z = (uint16_t*)d_Z; p.ldz = ldz; p.mu = d_mu; p.cnt = d_cnt; p.sum = d_sum; p.zlut = d_zlut;
@@ -417,8 +417,9 @@ extern "C" int gcta_b200_nonmiss_planes(const uint8_t* d_bed, int64_t pitch, int
     GB_ARG(d_bed && d_planes, "nonmiss_planes: null pointer");
     GB_ARG(pitch > 0 && pitch % 16 == 0, "nonmiss_planes: pitch must be a multiple of 16");
     GB_ARG(k0 % 32 == 0 && kc > 0, "nonmiss_planes: k0 must be a multiple of 32");
-    GB_ARG(ldm % 256 == 0 && ldm >= n, "nonmiss_planes: ldm must be a multiple of 256 and >= n");
+    GB_ARG(ldm > 0 && ldm % 256 == 0, "nonmiss_planes: ldm must be a positive multiple of 256");
     GB_ARG(d_keep || n == n_file, "nonmiss_planes: n must equal n_file when keep is NULL");
+    if (n > ldm) n = ldm;   // planes narrower than n keep only the first ldm individuals
     const unsigned words = (unsigned)((kc + 31) / 32);
     if (!d_keep) {
         dim3 grid((unsigned)((ldm / 16 + 127) / 128), words);

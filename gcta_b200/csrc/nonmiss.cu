@@ -58,8 +58,9 @@ extern "C" int gcta_b200_nonmiss_matrix(const uint8_t* d_bed, int64_t pitch, int
     GB_ARG(d_bed && d_OK, "nonmiss_matrix: null pointer");
     GB_ARG(pitch > 0 && pitch % 16 == 0, "nonmiss_matrix: pitch must be a multiple of 16");
     GB_ARG(kc > 0 && k0 >= 0, "nonmiss_matrix: empty SNP range");
-    GB_ARG(ldz % 256 == 0 && ldz >= n, "nonmiss_matrix: ldz must be a multiple of 256 and >= n");
+    GB_ARG(ldz > 0 && ldz % 256 == 0, "nonmiss_matrix: ldz must be a positive multiple of 256");
     GB_ARG(d_keep || n == n_file, "nonmiss_matrix: n must equal n_file when keep is NULL");
+    if (n > ldz) n = ldz;   // a matrix narrower than n keeps only the first ldz individuals
     GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "nonmiss_matrix: unknown operand type");
     const int64_t kc_pad = (kc + 63) / 64 * 64;
     const uint32_t one16 = operand == GCTA_B200_BF16 ? 0x3F80u : 0x3C00u;   // 1.0 in bf16 / fp16

@@ -60,22 +60,38 @@ extern "C" int gcta_b200_partition(int64_t n, int32_t part_rank, int32_t part_wo
     if (part_world <= 1) { *row_begin = 0; *row_end = n; return 0; }
     if (part_rank < 0 || part_rank >= part_world) return GCTA_B200_ERR_ARG;
     const int64_t nrb = (n + TILE_M - 1) / TILE_M;
-    int64_t total = 0;
-    for (int64_t b = 0; b < nrb; b++) total += tiles_in_row_block(b, n);
-    // boundary g = first row block whose tile prefix reaches g/G of the total
-    auto boundary = [&](int g) -> int64_t {
-        if (g <= 0) return 0;
-        if (g >= part_world) return nrb;
-        const double target = (double)total * g / part_world;
-        int64_t acc = 0;
-        for (int64_t b = 0; b < nrb; b++) {
-            if ((double)acc >= target) return b;
-            acc += tiles_in_row_block(b, n);
+    // Cost of a band of row blocks [b0, b1), in units of one 256x256 tile of SYRK work:
+    //   tiles(b0, b1)            the tensor work
+    // + ALPHA * b1               K1 standardises columns [0, 256*b1) for this band (HBM-bound, replicated per GPU)
+    // + BETA * (b1 - b0)         K1d sums the diagonal of the band's own individuals
+    // ALPHA and BETA are measured ratios on B200 (one column block of K1 costs ~2.1 tiles, of K1d ~1; both
+    // scale with M like the tiles do, so the ratios do not depend on M).  Boundaries minimise the largest band.
+    const double ALPHA = 2.1, BETA = 1.0;
+    std::vector<int64_t> pref(nrb + 1, 0);
+    for (int64_t b = 0; b < nrb; b++) pref[b + 1] = pref[b] + tiles_in_row_block(b, n);
+    auto cost = [&](int64_t b0, int64_t b1) { return (double)(pref[b1] - pref[b0]) + ALPHA * b1 + BETA * (b1 - b0); };
+    auto cut = [&](double cap, std::vector<int64_t>& bounds) {   // greedy: longest band within `cap`, G bands at most
+        bounds.assign(part_world + 1, nrb);
+        bounds[0] = 0;
+        int64_t b = 0;
+        for (int g = 0; g < part_world; g++) {
+            int64_t e = b;
+            while (e < nrb && cost(b, e + 1) <= cap) e++;
+            bounds[g + 1] = e;
+            b = e;
         }
-        return nrb;
+        return b >= nrb;
     };
-    *row_begin = std::min<int64_t>(boundary(part_rank) * TILE_M, n);
-    *row_end = std::min<int64_t>(boundary(part_rank + 1) * TILE_M, n);
+    double lo = 0.0, hi = cost(0, nrb);
+    std::vector<int64_t> bounds, best;
+    cut(hi, best);
+    for (int it = 0; it < 60; it++) {
+        const double mid = 0.5 * (lo + hi);
+        if (cut(mid, bounds)) { hi = mid; best = bounds; }
+        else lo = mid;
+    }
+    *row_begin = std::min<int64_t>(best[part_rank] * TILE_M, n);
+    *row_end = std::min<int64_t>(best[part_rank + 1] * TILE_M, n);
     return 0;
 }
 
@@ -111,6 +127,7 @@ struct gcta_b200_plan {
     cudaStream_t stream = nullptr, stream2 = nullptr, stream_copy = nullptr;
     std::vector<cudaEvent_t> upload_events;
     std::vector<int32_t> h_include;
+    int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
     uint8_t* d_bed = nullptr;
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
@@ -207,6 +224,10 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         gcta_b200_plan_destroy(p);
         return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: plan_create: bad part_rank / part_world");
     }
+    // a row band only multiplies individuals [0, row_end): standardise (and store) no more columns than that
+    p->ldz = round_up(std::max<int64_t>(p->row_end, 1), TILE_N);
+    p->diag_f0 = p->row_begin;   // identity keep: file individual == kept individual (overridden below for a keep list)
+    p->diag_f1 = p->row_end;
     p->ntiles = gcta_b200_tile_list(n, p->row_begin, p->row_end, nullptr);
     p->band_count = p->row_end * (p->row_end + 1) / 2 - p->row_begin * (p->row_begin + 1) / 2;
     PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
@@ -243,6 +264,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     if (p->has_keep) {
         PLAN_TRY(dev_alloc(p, &p->d_keep, (size_t)n, err, errcap));
         PLAN_CUDA(cudaMemcpy(p->d_keep, a->keep, (size_t)n * 4, cudaMemcpyHostToDevice));
+        if (p->row_end > p->row_begin) { p->diag_f0 = a->keep[p->row_begin] / 16 * 16; p->diag_f1 = (int64_t)a->keep[p->row_end - 1] + 1; }
     }
     if (p->has_include) {
         PLAN_TRY(dev_alloc(p, &p->d_include, (size_t)m, err, errcap));
@@ -285,6 +307,31 @@ extern "C" int gcta_b200_plan_upload(gcta_b200_plan* p, const uint8_t* bed_host,
     if (p->pitch != p->stride) GB_CUDA(cudaMemsetAsync(p->d_bed, 0, (size_t)p->pitch * p->m_file, p->stream));
     GB_CUDA(cudaMemcpy2DAsync(p->d_bed, (size_t)p->pitch, bed_host, (size_t)p->stride, (size_t)p->stride, (size_t)p->m_file,
                               cudaMemcpyHostToDevice, p->stream));
+    GB_CUDA(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_use_device_bed(gcta_b200_plan* p, void* d_bed, int64_t* pitch, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p, "plan_use_device_bed: null plan");
+    if (pitch) *pitch = p->pitch;
+    if (d_bed) {
+        GB_ARG(((uintptr_t)d_bed & 15) == 0, "plan_use_device_bed: buffer must be 16-byte aligned");
+        p->d_bed = (uint8_t*)d_bed;   // the plan's own buffer stays allocated and is freed with the plan
+    }
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_upload_rows(gcta_b200_plan* p, const uint8_t* bed_host, int64_t row_begin, int64_t row_end, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && bed_host, "plan_upload_rows: null argument");
+    GB_ARG(row_begin >= 0 && row_begin <= row_end && row_end <= p->m_file, "plan_upload_rows: bad row range");
+    GB_CUDA(cudaSetDevice(p->device));
+    if (row_end > row_begin)
+        GB_CUDA(cudaMemcpy2DAsync(p->d_bed + row_begin * p->pitch, (size_t)p->pitch, bed_host + row_begin * p->stride, (size_t)p->stride,
+                                  (size_t)p->stride, (size_t)(row_end - row_begin), cudaMemcpyHostToDevice, p->stream));
     GB_CUDA(cudaStreamSynchronize(p->stream));
     return 0;
 }
@@ -417,7 +464,9 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
                                       p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
                                       p->d_total_missing, sd, err, errcap);
         if (rc) return rc;
-        rc = gcta_b200_diag_accum(p->d_bed, p->pitch, p->n_file, p->d_sexmale, p->d_include, k0, kc, p->d_zlut, p->d_diag, p->d_nii, sd, err, errcap);
+        // the diagonal is only needed for this band's own individuals: hand K1d that slice of columns
+        rc = p->diag_f1 > p->diag_f0 ? gcta_b200_diag_accum(p->d_bed + p->diag_f0 / 4, p->pitch, p->diag_f1 - p->diag_f0, p->d_sexmale ? p->d_sexmale + p->diag_f0 / 16 : nullptr,
+                                                             p->d_include, k0, kc, p->d_zlut, p->d_diag + p->diag_f0, p->d_nii + p->diag_f0, sd, err, errcap) : 0;
         if (rc) return rc;
         GB_CUDA(cudaEventRecord(EV(c, 1), sd));
         GB_CUDA(cudaStreamWaitEvent(st, EV(c, 1), 0));

@@ -106,6 +106,13 @@ int gcta_b200_plan_upload(gcta_b200_plan* plan, const uint8_t* bed_host, char* e
 /* fill the HBM genotype buffer on the device from the counter-based generator of
  * gcta_b200/synth.py (thr = uint32[m_file][4] thresholds in HOST memory); bench/test use only */
 int gcta_b200_plan_synth(gcta_b200_plan* plan, uint64_t seed, const uint32_t* thr_host, char* err, size_t errcap);
+/* Multi-GPU hosts (one process per GPU): instead of every rank pulling the whole .bed over PCIe, each rank uploads
+ * 1/G of the SNP rows (plan_upload_rows) and the ranks all-gather the packed rows over NVLink (NCCL, by the host -
+ * bench.py uses torch.distributed).  plan_use_device_bed makes the plan read its genotypes from a caller-owned device
+ * buffer of m_file rows x *pitch bytes (pad bytes zero), e.g. the all-gather's output; d_bed == NULL only queries the
+ * pitch.  plan_upload_rows copies host rows [row_begin,row_end) into whichever buffer the plan currently uses. */
+int gcta_b200_plan_use_device_bed(gcta_b200_plan* plan, void* d_bed, int64_t* pitch, char* err, size_t errcap);
+int gcta_b200_plan_upload_rows(gcta_b200_plan* plan, const uint8_t* bed_host, int64_t row_begin, int64_t row_end, char* err, size_t errcap);
 /* inverse of plan_upload: copy the plan's HBM genotype buffer to host memory in .bed payload layout
  * (bench/test use: obtain the host copy of a device-generated data set) */
 int gcta_b200_plan_download_bed(gcta_b200_plan* plan, uint8_t* bed_host, char* err, size_t errcap);
