@@ -247,7 +247,7 @@ def main_ours(a, rank, world, local_rank):
                                          "finalize": fin_ms / a.steps},
             "roofline": {"kernel": "syrk_tiles_kernel (K2)", "bound": "tensor", "achieved": syrk_tflops_min, "peak": sust, "unit": "TFLOP/s",
                          "frac": syrk_tflops_min / sust, "frac_of_burst_peak": syrk_tflops_min / burst, "peak_source": which + " (sustained bf16, kernel timed inside a long step)",
-                         "traffic": None, "launches_per_step": nchunks,
+                         "traffic": k2_traffic(n, world), "launches_per_step": nchunks,
                          "k1_decode_GBps": k1_bytes / (dec_ms / a.steps * 1e-3) / 1e9 if dec_ms > 0 else None, "hbm_peak_GBps": hbm},
             "clocks": clocks, "gpu_launches": launches_total,
         }
@@ -266,6 +266,19 @@ def main_ours(a, rank, world, local_rank):
         print(json.dumps(line))
     plan.close()
     ranks.close()
+
+
+def k2_traffic(n, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one K2 launch from the committed ncu capture (profiles/),
+    only when this run matches the captured shape (whole triangle of n individuals on one GPU); else None."""
+    p = os.path.join(ROOT, "profiles", "k2_traffic.json")
+    if world != 1 or not os.path.exists(p):
+        return None
+    d = json.load(open(p))
+    if d.get("n") != n:
+        return None
+    return {"bytes_per_launch": d["dram_bytes_read"] + d["dram_bytes_write"], "snps_per_launch": d["snps_per_launch"],
+            "unit": "B", "source": d["source"]}
 
 
 def plan_chunk(plan, n, m):
