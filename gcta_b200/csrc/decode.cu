@@ -22,7 +22,7 @@ namespace gb {
 // code (2 bits, low bit first): 00 -> 2 copies of allele 1, 10b -> 1, 11 -> 0, 01b -> missing
 // (data.cpp:176-181: _snp_2 = !low, _snp_1 = !high, missing iff _snp_1 && !_snp_2).
 struct SnpCounts {
-    int cnt, sum, cntM, sumM;
+    int cnt, sum, cntM, sumM, het, hetM;   // non-missing, allele-1 dosage sum, the same for males, heterozygotes
 };
 
 template <bool XCHR>
@@ -32,10 +32,12 @@ __device__ __forceinline__ void count_word(uint32_t w, uint32_t km, uint32_t mm,
     const uint32_t nm = ~(lo & ~hi) & km;  // kept and not missing (even bit positions)
     c.cnt += __popc(nm);
     c.sum += __popc(nm & ~hi) + __popc(nm & ~lo);
+    c.het += __popc(nm & hi & ~lo);   // code 10b
     if (XCHR) {
         const uint32_t nmm = nm & mm;
         c.cntM += __popc(nmm);
         c.sumM += __popc(nmm & ~hi) + __popc(nmm & ~lo);
+        c.hetM += __popc(nmm & hi & ~lo);
     }
 }
 
@@ -69,6 +71,7 @@ struct DecodeParams {
     int32_t* cnt;
     int32_t* sum;
     float* zlut;
+    double* dk;   // optional: per-SNP mean of z^2 (--grm-alg 1)
     unsigned long long* total_missing;
 };
 
@@ -106,20 +109,24 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
     }
     c.cnt = warp_sum(c.cnt);
     c.sum = warp_sum(c.sum);
+    c.het = warp_sum(c.het);
     if (XCHR) {
         c.cntM = warp_sum(c.cntM);
         c.sumM = warp_sum(c.sumM);
+        c.hetM = warp_sum(c.hetM);
     }
     if (GROUP > 32) {
-        __shared__ int red[8][4];
+        __shared__ int red[8][6];
         const int w = threadIdx.x >> 5;
         if ((threadIdx.x & 31) == 0) {
-            red[w][0] = c.cnt; red[w][1] = c.sum; red[w][2] = c.cntM; red[w][3] = c.sumM;
+            red[w][0] = c.cnt; red[w][1] = c.sum; red[w][2] = c.cntM; red[w][3] = c.sumM; red[w][4] = c.het; red[w][5] = c.hetM;
         }
         __syncthreads();
-        c = {0, 0, 0, 0};
+        c = {0, 0, 0, 0, 0, 0};
 #pragma unroll
-        for (int i = 0; i < 8; i++) { c.cnt += red[i][0]; c.sum += red[i][1]; c.cntM += red[i][2]; c.sumM += red[i][3]; }
+        for (int i = 0; i < 8; i++) {
+            c.cnt += red[i][0]; c.sum += red[i][1]; c.cntM += red[i][2]; c.sumM += red[i][3]; c.het += red[i][4]; c.hetM += red[i][5];
+        }
     }
 
     // ---- per-SNP constants: mu = 2p and the doubly-rounded z values (data.cpp:801, 1027-1040) ----
@@ -159,6 +166,15 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
             p.zlut[k * 8 + 4 + code] = zm[code];
         }
         atomicAdd(p.total_missing, (unsigned long long)(p.n - c.cnt));
+        if (p.dk) {
+            // --grm-alg 1: d_k = mean over non-missing individuals of z^2 (grm.cpp:230-237), from the genotype
+            // counts: n2 (code 00) = (sum - het) / 2, n1 = het, n0 = cnt - n1 - n2, split by sex for the X chromosome
+            const int n1m = c.hetM, n2m = (c.sumM - c.hetM) / 2, n0m = c.cntM - n1m - n2m;
+            const int n1f = c.het - n1m, n2f = (c.sum - c.het) / 2 - n2m, n0f = (c.cnt - c.cntM) - n1f - n2f;
+            double ss = (double)n0f * ((double)zf[3] * zf[3]) + (double)n1f * ((double)zf[2] * zf[2]) + (double)n2f * ((double)zf[0] * zf[0]);
+            ss += (double)n0m * ((double)zm[3] * zm[3]) + (double)n1m * ((double)zm[2] * zm[2]) + (double)n2m * ((double)zm[0] * zm[0]);
+            p.dk[k] = c.cnt > 0 ? ss / (double)c.cnt : 0.0;
+        }
     }
 
     // ---- pass 2: write the standardised row (8 individuals = one 16-byte store per lane) ----
@@ -210,14 +226,18 @@ constexpr int DIAG_TILE = 192;              // SNPs per shared-memory tile (mult
 constexpr int DIAG_SPLIT = 4 * DIAG_TILE;   // SNPs per block slice
 constexpr int DIAG_THREADS = 256;
 
-template <bool XCHR>
+// ALG1 (--grm-alg 1): additionally dw[f] += sum over non-missing SNPs of d_k, the diagonal's denominator
+// (grm.cpp:257-264), through a second [SNP][code] table {d_k, 0, d_k, d_k}.
+template <bool XCHR, bool ALG1 = false>
 __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n_file,
                                                                    const uint32_t* __restrict__ sexmale,
                                                                    const int32_t* __restrict__ include, int64_t k0, int64_t kc,
                                                                    const float* __restrict__ zlut, double* __restrict__ diag,
-                                                                   int32_t* __restrict__ nii)
+                                                                   int32_t* __restrict__ nii, const double* __restrict__ dk = nullptr,
+                                                                   double* __restrict__ dw = nullptr)
 {
-    __shared__ __align__(16) float q_s[(XCHR ? 2 : 1) * DIAG_TILE * 4];   // [sex][SNP][code] squares
+    __shared__ __align__(16) float q_s[((XCHR ? 2 : 1) + (ALG1 ? 1 : 0)) * DIAG_TILE * 4];   // [sex][SNP][code] squares (+ d_k table)
+    constexpr uint32_t DK_OFF = (XCHR ? 2 : 1) * DIAG_TILE * 16;   // byte offset of the d_k table
     __shared__ int64_t row_s[DIAG_TILE];                                   // byte offset of each SNP row
     const int64_t col = (int64_t)blockIdx.x * DIAG_THREADS + threadIdx.x;
     const bool active = col * 16 < n_file;
@@ -231,10 +251,10 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
 #pragma unroll
         for (int e = 0; e < 16; e++) moff[e] = ((mm >> (2 * e)) & 1u) ? DIAG_TILE * 16 : 0;
     }
-    double dacc[16];
+    double dacc[16], dacc2[ALG1 ? 16 : 1];
     int miss[16];
 #pragma unroll
-    for (int e = 0; e < 16; e++) { dacc[e] = 0.0; miss[e] = 0; }
+    for (int e = 0; e < 16; e++) { dacc[e] = 0.0; miss[e] = 0; if (ALG1) dacc2[e] = 0.0; }
     const char* q_bytes = reinterpret_cast<const char*>(q_s);
 
     for (int64_t t0 = kbeg; t0 < kend; t0 += DIAG_TILE) {
@@ -250,12 +270,16 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
                 const float4 lm = __ldg(reinterpret_cast<const float4*>(zlut + k * 8 + 4));
                 reinterpret_cast<float4*>(q_s)[DIAG_TILE + i] = make_float4(lm.x * lm.x, 0.0f, lm.z * lm.z, lm.w * lm.w);
             }
+            if (ALG1) {
+                const float d = (float)dk[k];
+                reinterpret_cast<float4*>(q_s)[(XCHR ? 2 : 1) * DIAG_TILE + i] = make_float4(d, 0.0f, d, d);
+            }
         }
         __syncthreads();
         if (!active) continue;
-        float acc[16];
+        float acc[16], acc2[ALG1 ? 16 : 1];
 #pragma unroll
-        for (int e = 0; e < 16; e++) acc[e] = 0.0f;
+        for (int e = 0; e < 16; e++) { acc[e] = 0.0f; if (ALG1) acc2[e] = 0.0f; }
         uint32_t c8[4] = {0, 0, 0, 0};
         uint32_t c2 = 0;
         int in3 = 0;
@@ -268,6 +292,7 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
                 // byte offset of the code inside the 16-byte row: ((w >> 2e) & 3) * 4
                 const uint32_t off = e == 0 ? (w << 2) & 0xCu : (w >> (2 * e - 2)) & 0xCu;
                 acc[e] += *reinterpret_cast<const float*>(qrow + off + (XCHR ? moff[e] : 0u));
+                if (ALG1) acc2[e] += *reinterpret_cast<const float*>(qrow + off + DK_OFF);
             }
             c2 += (w & 0x55555555u) & ~(w >> 1);   // missing = code 01b, one count per 2-bit lane
             if (++in3 == 3) {
@@ -282,6 +307,7 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
 #pragma unroll
         for (int e = 0; e < 16; e++) {
             dacc[e] += (double)acc[e];
+            if (ALG1) dacc2[e] += (double)acc2[e];
             miss[e] += (int)((c8[e & 3] >> (8 * (e >> 2))) & 0xFFu);   // byte b of c8[g] = individual 4b + g
         }
     }
@@ -293,6 +319,7 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
         if (f < n_file) {
             atomicAdd(diag + f, dacc[e]);
             atomicAdd(nii + f, span - miss[e]);
+            if (ALG1) atomicAdd(dw + f, dacc2[e]);
         }
     }
 }
@@ -362,6 +389,16 @@ extern "C" int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t
                                     void* d_Z, int64_t ldz, double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
                                     unsigned long long* d_total_missing, void* stream, char* err, size_t errcap)
 {
+    return gcta_b200_bed_decode_ex(d_bed, pitch, n_file, d_keepmask, d_keep, n, d_sexmale, d_include, k0, kc, d_mu_in, xchr, alg, operand,
+                                   d_Z, ldz, d_mu, d_cnt, d_sum, d_zlut, nullptr, d_total_missing, stream, err, errcap);
+}
+
+extern "C" int gcta_b200_bed_decode_ex(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_keepmask,
+                                       const int32_t* d_keep, int64_t n, const uint32_t* d_sexmale, const int32_t* d_include,
+                                       int64_t k0, int64_t kc, const double* d_mu_in, int32_t xchr, int32_t alg, int32_t operand,
+                                       void* d_Z, int64_t ldz, double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
+                                       double* d_dk, unsigned long long* d_total_missing, void* stream, char* err, size_t errcap)
+{
     using namespace gb;
     GB_ARG(d_bed && d_keepmask && d_Z && d_mu && d_cnt && d_sum && d_zlut && d_total_missing, "bed_decode: null pointer");
     GB_ARG(pitch > 0 && pitch % 16 == 0 && ((uintptr_t)d_bed & 15) == 0, "bed_decode: bed pitch and pointer must be multiples of 16 bytes");
@@ -376,7 +413,7 @@ extern "C" int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t
     p.bed = d_bed; p.pitch = pitch; p.n_file = n_file; p.keepmask = d_keepmask; p.keep = d_keep; p.n = n; p.n_out = n < ldz ? n : ldz;  // a Z narrower than n keeps only the first ldz individuals (row bands need no more)
     p.sexmale = d_sexmale; p.include = d_include; p.k0 = k0; p.kc = kc; p.kc_pad = (kc + 63) / 64 * 64;
     p.mu_in = d_mu_in; p.divide = alg == 0; p.bf16 = operand == GCTA_B200_BF16;
-    p.Z = (uint16_t*)d_Z; p.ldz = ldz; p.mu = d_mu; p.cnt = d_cnt; p.sum = d_sum; p.zlut = d_zlut;
+    p.Z = (uint16_t*)d_Z; p.ldz = ldz; p.mu = d_mu; p.cnt = d_cnt; p.sum = d_sum; p.zlut = d_zlut; p.dk = d_dk;
     p.total_missing = d_total_missing;
     cudaStream_t st = (cudaStream_t)stream;
     const bool wide = pitch >= 4096;  // one CTA per row when a row is at least 4 KB, else one warp per row
@@ -397,14 +434,26 @@ extern "C" int gcta_b200_diag_accum(const uint8_t* d_bed, int64_t pitch, int64_t
                                     const int32_t* d_include, int64_t k0, int64_t kc, const float* d_zlut, double* d_diag,
                                     int32_t* d_nii, void* stream, char* err, size_t errcap)
 {
+    return gcta_b200_diag_accum_ex(d_bed, pitch, n_file, d_sexmale, d_include, k0, kc, d_zlut, d_diag, d_nii, nullptr, nullptr, stream, err, errcap);
+}
+
+extern "C" int gcta_b200_diag_accum_ex(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_sexmale,
+                                       const int32_t* d_include, int64_t k0, int64_t kc, const float* d_zlut, double* d_diag,
+                                       int32_t* d_nii, const double* d_dk, double* d_dw, void* stream, char* err, size_t errcap)
+{
     using namespace gb;
     GB_ARG(d_bed && d_zlut && d_diag && d_nii, "diag_accum: null pointer");
     GB_ARG(pitch > 0 && pitch % 16 == 0, "diag_accum: pitch must be a multiple of 16");
     GB_ARG(kc > 0, "diag_accum: empty SNP range");
     const int64_t cols = (n_file + 15) / 16;
     dim3 grid((unsigned)((cols + DIAG_THREADS - 1) / DIAG_THREADS), (unsigned)((kc + DIAG_SPLIT - 1) / DIAG_SPLIT));
-    if (d_sexmale) diag_accum_kernel<true><<<grid, DIAG_THREADS, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, d_sexmale, d_include, k0, kc, d_zlut, d_diag, d_nii);
-    else diag_accum_kernel<false><<<grid, DIAG_THREADS, 0, (cudaStream_t)stream>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, d_zlut, d_diag, d_nii);
+    GB_ARG((d_dk == nullptr) == (d_dw == nullptr), "diag_accum: d_dk and d_dw go together");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (d_dk) {
+        if (d_sexmale) diag_accum_kernel<true, true><<<grid, DIAG_THREADS, 0, st>>>(d_bed, pitch, n_file, d_sexmale, d_include, k0, kc, d_zlut, d_diag, d_nii, d_dk, d_dw);
+        else diag_accum_kernel<false, true><<<grid, DIAG_THREADS, 0, st>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, d_zlut, d_diag, d_nii, d_dk, d_dw);
+    } else if (d_sexmale) diag_accum_kernel<true><<<grid, DIAG_THREADS, 0, st>>>(d_bed, pitch, n_file, d_sexmale, d_include, k0, kc, d_zlut, d_diag, d_nii);
+    else diag_accum_kernel<false><<<grid, DIAG_THREADS, 0, st>>>(d_bed, pitch, n_file, nullptr, d_include, k0, kc, d_zlut, d_diag, d_nii);
     GB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -13,7 +13,8 @@ namespace gb {
 __global__ void __launch_bounds__(256) nonmiss_matrix_kernel(const uint8_t* __restrict__ bed, int64_t pitch,
                                                               const int32_t* __restrict__ keep, int64_t n,
                                                               const int32_t* __restrict__ include, int64_t k0, int64_t kc,
-                                                              int64_t kc_pad, uint32_t one16, uint16_t* __restrict__ OK, int64_t ldz)
+                                                              int64_t kc_pad, uint32_t one16, const double* __restrict__ dk, int bf16,
+                                                              uint16_t* __restrict__ OK, int64_t ldz)
 {
     const int lane = threadIdx.x & 31;
     const int64_t kk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -25,6 +26,10 @@ __global__ void __launch_bounds__(256) nonmiss_matrix_kernel(const uint8_t* __re
         return;
     }
     const int64_t k = k0 + kk;
+    if (dk) {   // --grm-alg 1: indicator scaled by sqrt(d_k), so that the contraction gives sum_k ok ok d_k
+        const float w = sqrtf((float)dk[k]);
+        one16 = bf16 ? (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(w)) : (uint32_t)__half_as_ushort(__float2half_rn(w));
+    }
     const uint8_t* row = bed + (include ? (int64_t)include[k] : k) * pitch;
     const uint16_t* row2 = reinterpret_cast<const uint16_t*>(row);
     for (int ch = lane; ch < nchunk; ch += 32) {
@@ -54,6 +59,13 @@ extern "C" int gcta_b200_nonmiss_matrix(const uint8_t* d_bed, int64_t pitch, int
                                         const int32_t* d_include, int64_t k0, int64_t kc, int32_t operand, void* d_OK, int64_t ldz,
                                         void* stream, char* err, size_t errcap)
 {
+    return gcta_b200_nonmiss_matrix_ex(d_bed, pitch, n_file, d_keep, n, d_include, k0, kc, operand, nullptr, d_OK, ldz, stream, err, errcap);
+}
+
+extern "C" int gcta_b200_nonmiss_matrix_ex(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_keep, int64_t n,
+                                           const int32_t* d_include, int64_t k0, int64_t kc, int32_t operand, const double* d_dk,
+                                           void* d_OK, int64_t ldz, void* stream, char* err, size_t errcap)
+{
     using namespace gb;
     GB_ARG(d_bed && d_OK, "nonmiss_matrix: null pointer");
     GB_ARG(pitch > 0 && pitch % 16 == 0, "nonmiss_matrix: pitch must be a multiple of 16");
@@ -65,7 +77,7 @@ extern "C" int gcta_b200_nonmiss_matrix(const uint8_t* d_bed, int64_t pitch, int
     const int64_t kc_pad = (kc + 63) / 64 * 64;
     const uint32_t one16 = operand == GCTA_B200_BF16 ? 0x3F80u : 0x3C00u;   // 1.0 in bf16 / fp16
     nonmiss_matrix_kernel<<<(unsigned)((kc_pad + 7) / 8), 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, d_keep, n, d_include, k0, kc, kc_pad,
-                                                                                         one16, (uint16_t*)d_OK, ldz);
+                                                                                         one16, d_dk, operand == GCTA_B200_BF16, (uint16_t*)d_OK, ldz);
     GB_CUDA(cudaGetLastError());
     return 0;
 }

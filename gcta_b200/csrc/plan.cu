@@ -132,7 +132,8 @@ struct gcta_b200_plan {
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
     int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr;
-    double *d_mu_in = nullptr, *d_mu = nullptr, *d_diag = nullptr;
+    double *d_mu_in = nullptr, *d_mu = nullptr, *d_diag = nullptr, *d_dk = nullptr, *d_dw = nullptr;   // d_dk, d_dw: --grm-alg 1
+    float* d_Dtiles = nullptr;
     float *d_zlut = nullptr, *d_S = nullptr, *d_A_lower = nullptr;
     void* d_Zbuf[2] = {nullptr, nullptr};
     unsigned long long* d_total_missing = nullptr;
@@ -187,7 +188,6 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     if (n <= 0) return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: No individual is retained for analysis.");    // data.cpp:150
     GB_ARG(n <= a->n_file && m <= a->m_file, "plan_create: more kept than present");
     GB_ARG(a->alg == 0 || a->alg == 1, "plan_create: alg must be 0 or 1");
-    GB_ARG(a->alg == 0, "plan_create: --grm-alg 1 is not implemented on the device yet");
     GB_ARG(a->operand == GCTA_B200_FP16 || a->operand == GCTA_B200_BF16, "plan_create: unknown operand type");
     GB_ARG(!a->xchr || a->sex, "plan_create: xchr needs the sex array");
     if (gcta_b200_device_count() <= 0)
@@ -244,6 +244,10 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     PLAN_TRY(dev_alloc(p, &p->d_diag, (size_t)a->n_file, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_nii, (size_t)a->n_file, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_total_missing, 1, err, errcap));
+    if (a->alg == 1) {
+        PLAN_TRY(dev_alloc(p, &p->d_dk, (size_t)m, err, errcap));
+        PLAN_TRY(dev_alloc(p, &p->d_dw, (size_t)a->n_file, err, errcap));
+    }
     PLAN_TRY(dev_alloc(p, &p->d_tiles, (size_t)p->ntiles * 2, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_S, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_A_lower, (size_t)p->band_count, err, errcap));
@@ -452,6 +456,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     GB_CUDA(cudaMemsetAsync(p->d_diag, 0, (size_t)p->n_file * 8, st));
     GB_CUDA(cudaMemsetAsync(p->d_nii, 0, (size_t)p->n_file * 4, st));
     GB_CUDA(cudaMemsetAsync(p->d_total_missing, 0, 8, st));
+    if (p->d_dw) GB_CUDA(cudaMemsetAsync(p->d_dw, 0, (size_t)p->n_file * 8, st));
     GB_CUDA(cudaEventRecord(p->events[1], st));
     GB_CUDA(cudaStreamWaitEvent(sd, p->events[1], 0));
     for (int64_t c = 0; c < nchunks; c++) {
@@ -460,13 +465,14 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         if (c >= 2) GB_CUDA(cudaStreamWaitEvent(sd, EV(c - 2, 3), 0));   // the SYRK that last read this Z buffer
         if (bed_host) GB_CUDA(cudaStreamWaitEvent(sd, up[c], 0));        // this chunk's packed rows have landed
         GB_CUDA(cudaEventRecord(EV(c, 0), sd));
-        int rc = gcta_b200_bed_decode(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
-                                      p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
-                                      p->d_total_missing, sd, err, errcap);
+        int rc = gcta_b200_bed_decode_ex(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
+                                         p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
+                                         p->d_dk, p->d_total_missing, sd, err, errcap);
         if (rc) return rc;
         // the diagonal is only needed for this band's own individuals: hand K1d that slice of columns
-        rc = p->diag_f1 > p->diag_f0 ? gcta_b200_diag_accum(p->d_bed + p->diag_f0 / 4, p->pitch, p->diag_f1 - p->diag_f0, p->d_sexmale ? p->d_sexmale + p->diag_f0 / 16 : nullptr,
-                                                             p->d_include, k0, kc, p->d_zlut, p->d_diag + p->diag_f0, p->d_nii + p->diag_f0, sd, err, errcap) : 0;
+        rc = p->diag_f1 > p->diag_f0 ? gcta_b200_diag_accum_ex(p->d_bed + p->diag_f0 / 4, p->pitch, p->diag_f1 - p->diag_f0, p->d_sexmale ? p->d_sexmale + p->diag_f0 / 16 : nullptr,
+                                                                p->d_include, k0, kc, p->d_zlut, p->d_diag + p->diag_f0, p->d_nii + p->diag_f0, p->d_dk,
+                                                                p->d_dw ? p->d_dw + p->diag_f0 : nullptr, sd, err, errcap) : 0;
         if (rc) return rc;
         GB_CUDA(cudaEventRecord(EV(c, 1), sd));
         GB_CUDA(cudaStreamWaitEvent(st, EV(c, 1), 0));
@@ -523,10 +529,36 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         if (rc) return rc;
         launches++;
     }
+    // --grm-alg 1: denominators sum_k ok_ik ok_jk d_k.  Nothing missing: the constant sum_k d_k, added on the host in
+    // SNP order like grm.cpp:283.  Otherwise one more SYRK pass over ok * sqrt(d_k) into float tiles.
+    double d_const = 0.0;
+    if (p->alg == 1) {
+        std::vector<double> dk((size_t)p->m);
+        GB_CUDA(cudaMemcpyAsync(dk.data(), p->d_dk, (size_t)p->m * 8, cudaMemcpyDeviceToHost, st));
+        GB_CUDA(cudaStreamSynchronize(st));
+        for (int64_t k = 0; k < p->m; k++) d_const += dk[(size_t)k];
+        if (tm > 0) {
+            if (!p->d_Dtiles) {
+                int rc = dev_alloc(p, &p->d_Dtiles, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap);
+                if (rc) return rc;
+            }
+            GB_CUDA(cudaMemsetAsync(p->d_Dtiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
+            for (int64_t c = 0; c < nchunks; c++) {
+                const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
+                int rc = gcta_b200_nonmiss_matrix_ex(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, p->operand, p->d_dk,
+                                                     p->d_Zbuf[0], p->ldz, st, err, errcap);
+                if (rc) return rc;
+                rc = gcta_b200_syrk_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_Dtiles, st, err, errcap);
+                if (rc) return rc;
+                launches += 2;
+            }
+        }
+    }
     GB_CUDA(cudaEventRecord(p->events[e_pc], st));
     {
-        int rc = gcta_b200_finalize_tiles(p->d_S, tm > 0 ? p->d_Ntiles : nullptr, (int32_t)p->m, p->d_tiles, p->ntiles, p->n, p->d_keep,
-                                          p->d_diag, p->d_nii, p->row_begin, p->row_end, p->d_A_lower, tm > 0 ? p->d_N_lower : nullptr, st, err, errcap);
+        int rc = gcta_b200_finalize_tiles_ex(p->d_S, tm > 0 ? p->d_Ntiles : nullptr, (int32_t)p->m, (p->alg == 1 && tm > 0) ? p->d_Dtiles : nullptr,
+                                             d_const, p->alg == 1 ? p->d_dw : nullptr, p->d_tiles, p->ntiles, p->n, p->d_keep,
+                                             p->d_diag, p->d_nii, p->row_begin, p->row_end, p->d_A_lower, tm > 0 ? p->d_N_lower : nullptr, st, err, errcap);
         if (rc) return rc;
         launches++;
     }

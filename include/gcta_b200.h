@@ -225,6 +225,36 @@ int gcta_b200_finalize_tiles(const float* d_S, const int32_t* d_Ntiles, int32_t 
                              float* d_A_lower, int32_t* d_N_lower,
                              void* stream, char* err, size_t errcap);
 
+/* ---- --grm-alg 1 (grm.cpp:230-237, 257-264, 278-285): A_ij = sum_k z_ik z_jk / sum_k ok_ik ok_jk d_k with z centred
+ * only and d_k = mean over non-missing individuals of z_k^2.  The "_ex" variants add the extra operands; passing NULL
+ * for them is the plain call above.
+ *   bed_decode_ex    d_dk      out  double[>= k0+kc]: d_k per included SNP (call with alg = 1)
+ *   diag_accum_ex    d_dk in, d_dw out  double per FILE individual: dw[f] += sum_k ok_fk d_k (diagonal denominator)
+ *   nonmiss_matrix_ex d_dk in  the matrix holds ok * sqrt(d_k) instead of ok, so that the SYRK kernel in float mode
+ *                              (gcta_b200_syrk_tiles) yields the off-diagonal denominators D_ij
+ *   finalize_tiles_ex d_Dtiles (float tiles like S, or NULL when nothing is missing and D_ij == d_const), d_dw */
+int gcta_b200_bed_decode_ex(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
+                            const uint32_t* d_keepmask, const int32_t* d_keep, int64_t n,
+                            const uint32_t* d_sexmale, const int32_t* d_include, int64_t k0, int64_t kc,
+                            const double* d_mu_in, int32_t xchr, int32_t alg, int32_t operand,
+                            void* d_Z, int64_t ldz,
+                            double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut, double* d_dk,
+                            unsigned long long* d_total_missing, void* stream, char* err, size_t errcap);
+int gcta_b200_diag_accum_ex(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
+                            const uint32_t* d_sexmale, const int32_t* d_include, int64_t k0, int64_t kc,
+                            const float* d_zlut, double* d_diag, int32_t* d_nii, const double* d_dk, double* d_dw,
+                            void* stream, char* err, size_t errcap);
+int gcta_b200_nonmiss_matrix_ex(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_keep, int64_t n,
+                                const int32_t* d_include, int64_t k0, int64_t kc, int32_t operand, const double* d_dk,
+                                void* d_OK, int64_t ldz, void* stream, char* err, size_t errcap);
+int gcta_b200_finalize_tiles_ex(const float* d_S, const int32_t* d_Ntiles, int32_t m_const,
+                                const float* d_Dtiles, double d_const, const double* d_dw,
+                                const int32_t* d_tiles, int64_t ntiles, int64_t n,
+                                const int32_t* d_keep, const double* d_diag, const int32_t* d_nii,
+                                int64_t row_begin, int64_t row_end,
+                                float* d_A_lower, int32_t* d_N_lower,
+                                void* stream, char* err, size_t errcap);
+
 /* index of element (r, c), r < 256, c < 256, inside one S / N tile */
 static inline int64_t gcta_b200_s_tile_index(int r, int c) { return ((int64_t)(c >> 2) * 256 + r) * 4 + (c & 3); }
 

@@ -22,6 +22,7 @@ def _names(path):
 @pytest.mark.parametrize("case,txt,binf,kw", [
     ("g1_basic", "o", "ob", {}),
     ("g2_edge", "o", "ob", {}),
+    ("g2_edge", "o_alg1", "ob_alg1", {"alg": 1}),
     ("g4_xchr", "o", "ob", {"xchr": 1}),
     ("g5_subset", "o", "ob", {"subset": True}),
     ("g7_nomiss", "o", "ob", {}),
@@ -36,7 +37,7 @@ def test_golden(case, txt, binf, kw, operand):
         keep = np.array([i for i, (f, _) in enumerate(ids) if f in kn], dtype=np.int32)
         en = set(_names(d + "/extract.txt"))
         include = np.array([k for k, s in enumerate(snps) if s in en], dtype=np.int32)
-    A, N, mu, out = abi.make_grm(bed, n, m, keep=keep, include=include, sex=sex, xchr=kw.get("xchr", 0), operand=operand)
+    A, N, mu, out = abi.make_grm(bed, n, m, keep=keep, include=include, sex=sex, xchr=kw.get("xchr", 0), alg=kw.get("alg", 0), operand=operand)
     Aref = pack_lower(grmio.read_grm_bin(f"{d}/{binf}.grm.bin"))
     _, Nref, _ = grmio.read_grm_gz(f"{d}/{txt}.grm.gz")
     # BF16 operands carry 8 significand bits: the diagonal is exact anyway (float64 side sum), off-diagonals need the looser bar
@@ -144,3 +145,19 @@ def test_errors_are_reported_not_thrown():
     assert "No individual is retained" in str(e.value)
     with pytest.raises(abi.GctaB200Error):
         abi.make_grm(bed, 40, 50, xchr=1, sex=np.zeros(40, dtype=np.int32))
+
+
+@pytest.mark.parametrize("miss,xchr", [(0.0, 0), (0.03, 0), (0.03, 1)])
+def test_grm_alg1(miss, xchr):
+    """--grm-alg 1 (grm.cpp:230-237, 257-264, 278-285): centred genotypes, denominators sum_k ok ok d_k.
+    Without missing data the denominator is the constant sum_k d_k; with missing data it comes from a second
+    SYRK over ok*sqrt(d_k); chunked so that S, N and D all accumulate over several launches."""
+    n, m = 420, 1300
+    bed = synth.make_bed_payload(91, n, m, miss_rate=miss)
+    sex = np.random.default_rng(3).integers(1, 3, size=n).astype(np.int32)
+    A, N, mu, out = abi.make_grm(bed, n, m, alg=1, xchr=xchr, sex=sex, chunk_snps=512)
+    Aref, Nref, _ = oracle.make_grm(bed, n, sex=sex, xchr=xchr, alg=1)
+    check_grm(A, N, Aref, Nref)
+    # and it is a different matrix from the default algorithm
+    A0, _, _, _ = abi.make_grm(bed, n, m, xchr=xchr, sex=sex)
+    assert np.abs(A0 - A).max() > 1e-3

@@ -171,3 +171,9 @@ def test_reference_reader_accepts_our_multi_member_gz(tmp_path):
     A, N, _ = grmio.read_grm_gz(str(tmp_path / "mine.grm.gz"))
     A2, N2, _ = grmio.read_grm_gz(str(tmp_path / "re.grm.gz"))
     assert np.array_equal(N, N2) and np.abs(A - A2).max() <= 1e-6 * max(1.0, np.abs(A).max())
+
+
+@pytest.mark.gpu
+def test_cli_grm_alg1(tmp_path):
+    _full_case(tmp_path, "g2_edge", ["--bfile", "t", "--make-grm", "--grm-alg", "1"], "o_alg1",
+               ["--bfile", "t", "--make-grm-bin", "--grm-alg", "1"], "ob_alg1", same_log=False)
