@@ -179,6 +179,41 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
 
     // ---- pass 2: write the standardised row (8 individuals = one 16-byte store per lane) ----
     const uint16_t* row2 = reinterpret_cast<const uint16_t*>(row);
+    if (GROUP == 256 && !XCHR && !p.keep) {
+        // Fast path (one CTA per row, everyone kept, one LUT for all): a 256-entry table "packed byte -> four
+        // 16-bit values" in shared memory turns the emit loop into 2 LDS.64 + 1 STG.128 per 8 genotypes; the
+        // per-genotype shift/mask/select version below is issue-bound (ncu: SM 91 %, HBM 61 %).
+        __shared__ uint2 tab[256];
+        {
+            const uint32_t b = threadIdx.x;
+            uint32_t v[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) v[e] = (uint32_t)(lutF >> (16 * ((b >> (2 * e)) & 3u))) & 0xFFFFu;
+            tab[b] = make_uint2(v[0] | (v[1] << 16), v[2] | (v[3] << 16));
+        }
+        __syncthreads();
+        const int nfull = (int)(p.n_out / 8);   // chunks entirely below n_out
+        for (int ch = tid; ch < nchunk; ch += GROUP) {
+            uint4 o = make_uint4(0, 0, 0, 0);
+            if (ch < nfull) {
+                const uint32_t w = __ldg(row2 + ch);
+                const uint2 a = tab[w & 0xFFu], b = tab[w >> 8];
+                o = make_uint4(a.x, a.y, b.x, b.y);
+            } else if ((int64_t)ch * 8 < p.n_out) {   // the one chunk that straddles n_out
+                const uint32_t w = __ldg(row2 + ch);
+                uint32_t h[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    uint32_t v = (uint32_t)(lutF >> (16 * ((w >> (2 * e)) & 3u))) & 0xFFFFu;
+                    if ((int64_t)ch * 8 + e >= p.n_out) v = 0;
+                    h[e >> 1] |= v << (16 * (e & 1));
+                }
+                o = make_uint4(h[0], h[1], h[2], h[3]);
+            }
+            zrow[ch] = o;
+        }
+        return;
+    }
     const uint16_t* male2 = reinterpret_cast<const uint16_t*>(p.sexmale);
     for (int ch = tid; ch < nchunk; ch += GROUP) {
         const int64_t i0 = (int64_t)ch * 8;
@@ -218,9 +253,10 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
 // K1d: thread = one 32-bit column (16 file individuals) x a slice of SNPs.
 // The squares z^2 of the (at most) three values a SNP takes are staged per tile of 192 SNPs as a
 // [SNP][code] float table in shared memory; per genotype the inner loop is shift, mask, one LDS
-// (code -> z^2; a warp touches at most 4 banks) and one FADD.  FP32 partial sums over a tile are
-// folded into FP64 per tile; missing genotypes are counted bit-sliced (2-bit lanes -> 8-bit
-// lanes every 3 SNPs -> 32-bit per tile), so counting costs ~0.3 instructions per genotype.
+// (code -> z^2; a warp touches at most 4 banks) and one FADD.  FP32 partial sums run over the
+// block's 768-SNP slice (keeps the kernel at 64 registers, 4 blocks/SM) and are folded into FP64
+// by the final atomics; missing genotypes are counted bit-sliced (2-bit lanes -> 8-bit lanes every
+// 3 SNPs -> 32-bit per tile), so counting costs ~0.3 instructions per genotype.
 // ------------------------------------------------------------------------------------------------
 constexpr int DIAG_TILE = 192;              // SNPs per shared-memory tile (multiple of 3, <= 255)
 constexpr int DIAG_SPLIT = 4 * DIAG_TILE;   // SNPs per block slice
@@ -251,10 +287,11 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
 #pragma unroll
         for (int e = 0; e < 16; e++) moff[e] = ((mm >> (2 * e)) & 1u) ? DIAG_TILE * 16 : 0;
     }
-    double dacc[16], dacc2[ALG1 ? 16 : 1];
+    // FP32 partial sums over the whole 768-SNP slice (rounding ~1e-6 relative, unbiased), folded into FP64 by the atomics
+    float acc[16], acc2[ALG1 ? 16 : 1];
     int miss[16];
 #pragma unroll
-    for (int e = 0; e < 16; e++) { dacc[e] = 0.0; miss[e] = 0; if (ALG1) dacc2[e] = 0.0; }
+    for (int e = 0; e < 16; e++) { acc[e] = 0.0f; miss[e] = 0; if (ALG1) acc2[e] = 0.0f; }
     const char* q_bytes = reinterpret_cast<const char*>(q_s);
 
     for (int64_t t0 = kbeg; t0 < kend; t0 += DIAG_TILE) {
@@ -277,9 +314,6 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
         }
         __syncthreads();
         if (!active) continue;
-        float acc[16], acc2[ALG1 ? 16 : 1];
-#pragma unroll
-        for (int e = 0; e < 16; e++) { acc[e] = 0.0f; if (ALG1) acc2[e] = 0.0f; }
         uint32_t c8[4] = {0, 0, 0, 0};
         uint32_t c2 = 0;
         int in3 = 0;
@@ -306,8 +340,6 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
         for (int g = 0; g < 4; g++) c8[g] += (c2 >> (2 * g)) & 0x03030303u;
 #pragma unroll
         for (int e = 0; e < 16; e++) {
-            dacc[e] += (double)acc[e];
-            if (ALG1) dacc2[e] += (double)acc2[e];
             miss[e] += (int)((c8[e & 3] >> (8 * (e >> 2))) & 0xFFu);   // byte b of c8[g] = individual 4b + g
         }
     }
@@ -317,9 +349,9 @@ __global__ void __launch_bounds__(DIAG_THREADS) diag_accum_kernel(const uint8_t*
     for (int e = 0; e < 16; e++) {
         const int64_t f = col * 16 + e;
         if (f < n_file) {
-            atomicAdd(diag + f, dacc[e]);
+            atomicAdd(diag + f, (double)acc[e]);
             atomicAdd(nii + f, span - miss[e]);
-            if (ALG1) atomicAdd(dw + f, dacc2[e]);
+            if (ALG1) atomicAdd(dw + f, (double)acc2[e]);
         }
     }
 }
