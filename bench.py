@@ -293,8 +293,8 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=50000)
-    ap.add_argument("--m", type=int, default=1000000)
+    ap.add_argument("--n", "--individuals", dest="n", type=int, default=50000)   # --individuals: unambiguous under torchrun
+    ap.add_argument("--m", "--snps", dest="m", type=int, default=1000000)
     ap.add_argument("--miss", type=float, default=0.0)
     ap.add_argument("--operand", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--ref-n", type=int, default=600, help="individuals in the CPU reference sample")
