@@ -12,7 +12,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libgcta_b200.so")
-FP16, BF16 = 0, 1
+FP16, BF16, FP16X2 = 0, 1, 2
 ERRCAP = 512
 TILE_M, TILE_N = 256, 256
 

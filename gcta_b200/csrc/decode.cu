@@ -66,6 +66,7 @@ struct DecodeParams {
     const double* mu_in;
     int divide, bf16;
     uint16_t* Z;
+    uint16_t* Z2;   // optional residual plane (split FP16 mode)
     int64_t ldz;
     double* mu;
     int32_t* cnt;
@@ -87,6 +88,10 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
     const int nchunk = (int)(p.ldz / 8);
     if (kk >= p.kc) {  // padding row of the last 64-SNP block
         for (int c = tid; c < nchunk; c += GROUP) zrow[c] = make_uint4(0, 0, 0, 0);
+        if (p.Z2) {
+            uint4* zrow2 = reinterpret_cast<uint4*>(p.Z2 + kk * p.ldz);
+            for (int c = tid; c < nchunk; c += GROUP) zrow2[c] = make_uint4(0, 0, 0, 0);
+        }
         return;
     }
     const int64_t k = p.k0 + kk;
@@ -150,11 +155,20 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
         zf[code] = z;
         zm[code] = XCHR ? __double2float_rn(__dmul_rn((double)z, __dsqrt_rn(0.5))) : z;  // data.cpp:1048-1054
     }
-    uint64_t lutF = 0, lutM = 0;
+    // 16-bit operand tables.  Split mode (Z2 != NULL): a second plane holds the FP16 residual z - fp16(z), so that
+    // hi*hi + hi*lo + lo*hi reproduces the FP32 products to ~2^-22 (the "tight" operand mode)
+    uint64_t lutF_hi = 0, lutM_hi = 0, lutF_lo = 0, lutM_lo = 0;
 #pragma unroll
     for (int code = 0; code < 4; code++) {
-        lutF |= (uint64_t)to16(zf[code], p.bf16) << (16 * code);
-        lutM |= (uint64_t)to16(zm[code], p.bf16) << (16 * code);
+        const uint32_t hf = to16(zf[code], p.bf16), hm = to16(zm[code], p.bf16);
+        lutF_hi |= (uint64_t)hf << (16 * code);
+        lutM_hi |= (uint64_t)hm << (16 * code);
+        if (p.Z2) {
+            const float rf = zf[code] - __half2float(__ushort_as_half((unsigned short)hf));
+            const float rm = zm[code] - __half2float(__ushort_as_half((unsigned short)hm));
+            lutF_lo |= (uint64_t)to16(rf, 0) << (16 * code);
+            lutM_lo |= (uint64_t)to16(rm, 0) << (16 * code);
+        }
     }
     if (tid == 0) {
         p.mu[k] = mu;
@@ -179,11 +193,16 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
 
     // ---- pass 2: write the standardised row (8 individuals = one 16-byte store per lane) ----
     const uint16_t* row2 = reinterpret_cast<const uint16_t*>(row);
+    const int nplanes = p.Z2 ? 2 : 1;
+    for (int plane = 0; plane < nplanes; plane++) {
+    const uint64_t lutF = plane ? lutF_lo : lutF_hi, lutM = plane ? lutM_lo : lutM_hi;
+    if (plane) zrow = reinterpret_cast<uint4*>(p.Z2 + kk * p.ldz);
     if (GROUP == 256 && !XCHR && !p.keep) {
         // Fast path (one CTA per row, everyone kept, one LUT for all): a 256-entry table "packed byte -> four
         // 16-bit values" in shared memory turns the emit loop into 2 LDS.64 + 1 STG.128 per 8 genotypes; the
         // per-genotype shift/mask/select version below is issue-bound (ncu: SM 91 %, HBM 61 %).
         __shared__ uint2 tab[256];
+        if (plane) __syncthreads();   // everyone is done reading the previous plane's table
         {
             const uint32_t b = threadIdx.x;
             uint32_t v[4];
@@ -212,7 +231,7 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
             }
             zrow[ch] = o;
         }
-        return;
+        continue;
     }
     const uint16_t* male2 = reinterpret_cast<const uint16_t*>(p.sexmale);
     for (int ch = tid; ch < nchunk; ch += GROUP) {
@@ -247,6 +266,7 @@ __global__ void __launch_bounds__(256) bed_decode_kernel(const DecodeParams p)
         }
         zrow[ch] = make_uint4(o[0], o[1], o[2], o[3]);
     }
+    }   // plane
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -440,12 +460,14 @@ extern "C" int gcta_b200_bed_decode_ex(const uint8_t* d_bed, int64_t pitch, int6
     GB_ARG(((uintptr_t)d_Z & 15) == 0, "bed_decode: Z must be 16-byte aligned");
     GB_ARG(kc > 0 && k0 >= 0, "bed_decode: empty SNP range");
     GB_ARG(!xchr || d_sexmale, "bed_decode: xchr needs the male mask");
-    GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "bed_decode: unknown operand type");
+    GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16 || operand == GCTA_B200_FP16X2, "bed_decode: unknown operand type");
     DecodeParams p;
     p.bed = d_bed; p.pitch = pitch; p.n_file = n_file; p.keepmask = d_keepmask; p.keep = d_keep; p.n = n; p.n_out = n < ldz ? n : ldz;  // a Z narrower than n keeps only the first ldz individuals (row bands need no more)
     p.sexmale = d_sexmale; p.include = d_include; p.k0 = k0; p.kc = kc; p.kc_pad = (kc + 63) / 64 * 64;
     p.mu_in = d_mu_in; p.divide = alg == 0; p.bf16 = operand == GCTA_B200_BF16;
-    p.Z = (uint16_t*)d_Z; p.ldz = ldz; p.mu = d_mu; p.cnt = d_cnt; p.sum = d_sum; p.zlut = d_zlut; p.dk = d_dk;
+    p.Z = (uint16_t*)d_Z;
+    p.Z2 = operand == GCTA_B200_FP16X2 ? (uint16_t*)d_Z + p.kc_pad * ldz : nullptr;   // split mode: the residual plane follows the first
+    p.ldz = ldz; p.mu = d_mu; p.cnt = d_cnt; p.sum = d_sum; p.zlut = d_zlut; p.dk = d_dk;
     p.total_missing = d_total_missing;
     cudaStream_t st = (cudaStream_t)stream;
     const bool wide = pitch >= 4096;  // one CTA per row when a row is at least 4 KB, else one warp per row

@@ -188,7 +188,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     if (n <= 0) return set_err(err, errcap, GCTA_B200_ERR_ARG, "Error: No individual is retained for analysis.");    // data.cpp:150
     GB_ARG(n <= a->n_file && m <= a->m_file, "plan_create: more kept than present");
     GB_ARG(a->alg == 0 || a->alg == 1, "plan_create: alg must be 0 or 1");
-    GB_ARG(a->operand == GCTA_B200_FP16 || a->operand == GCTA_B200_BF16, "plan_create: unknown operand type");
+    GB_ARG(a->operand == GCTA_B200_FP16 || a->operand == GCTA_B200_BF16 || a->operand == GCTA_B200_FP16X2, "plan_create: unknown operand type");
     GB_ARG(!a->xchr || a->sex, "plan_create: xchr needs the sex array");
     if (gcta_b200_device_count() <= 0)
         return set_err(err, errcap, GCTA_B200_ERR_NO_DEVICE, "Error: no CUDA device is available (gcta_b200 has no CPU fallback).");
@@ -289,14 +289,15 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         size_t free_b = 0, total_b = 0;
         PLAN_CUDA(cudaMemGetInfo(&free_b, &total_b));
         int64_t budget = std::min<int64_t>((int64_t)(free_b / 4), 8ll << 30);   // per Z buffer (two when overlapping)
-        int64_t kc = a->chunk_snps > 0 ? a->chunk_snps : budget / (p->ldz * 2);
+        const int planes = a->operand == GCTA_B200_FP16X2 ? 2 : 1;   // split mode keeps a residual plane behind the first
+        int64_t kc = a->chunk_snps > 0 ? a->chunk_snps : budget / (p->ldz * 2 * planes);
         kc = std::max<int64_t>(64, kc / 64 * 64);
         kc = std::min<int64_t>(kc, round_up(m, 64));
         kc = std::min<int64_t>(kc, 1 << 23);   // counts of one chunk must stay exact in the FP32 accumulator
         p->chunk = kc;
-        PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz, err, errcap));
+        PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz * planes, err, errcap));
         p->overlap = getenv("GCTA_B200_OVERLAP") && atoi(getenv("GCTA_B200_OVERLAP")) > 0;
-        if (p->overlap && kc < round_up(m, 64)) PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[1], (size_t)kc * p->ldz, err, errcap));
+        if (p->overlap && kc < round_up(m, 64)) PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[1], (size_t)kc * p->ldz * planes, err, errcap));
     }
     *out_plan = p;
     return 0;
@@ -477,7 +478,17 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         GB_CUDA(cudaEventRecord(EV(c, 1), sd));
         GB_CUDA(cudaStreamWaitEvent(st, EV(c, 1), 0));
         GB_CUDA(cudaEventRecord(EV(c, 2), st));
-        rc = gcta_b200_syrk_tiles(Z, p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+        if (p->operand == GCTA_B200_FP16X2) {
+            // z = hi + lo: S += hi'hi + hi'lo + lo'hi (lo'lo ~ 2^-22 z^2 is dropped)
+            const int64_t kp = round_up(kc, 64);
+            const uint16_t* hi = (const uint16_t*)Z;
+            const uint16_t* lo = hi + kp * p->ldz;
+            rc = gcta_b200_syrk_tiles(hi, p->ldz, kp, GCTA_B200_FP16, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+            if (!rc) rc = gcta_b200_syrk_tiles_ab(hi, lo, p->ldz, kp, GCTA_B200_FP16, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+            if (!rc) rc = gcta_b200_syrk_tiles_ab(lo, hi, p->ldz, kp, GCTA_B200_FP16, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+            launches += 2;
+        } else
+            rc = gcta_b200_syrk_tiles(Z, p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
         if (rc) return rc;
         GB_CUDA(cudaEventRecord(EV(c, 3), st));
         launches += 3;
@@ -491,6 +502,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     // N_ij is only needed when something is missing (otherwise N == m, which is what grm.cpp:291 yields).
     // Default: indicator matrix + the SYRK kernel in counting mode (exact, tensor rate).  GCTA_B200_N_MODE=popc
     // selects the AND+popc kernel over bit planes instead (same integers, ~8x slower; kept as the cross-check).
+    const int op16 = p->operand == GCTA_B200_FP16X2 ? GCTA_B200_FP16 : p->operand;   // indicator matrices are single-plane
     const char* nmode = getenv("GCTA_B200_N_MODE");
     const bool use_popc = nmode && strcmp(nmode, "popc") == 0;
     if (tm > 0 && !p->d_Ntiles) {
@@ -503,10 +515,10 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
         for (int64_t c = 0; c < nchunks; c++) {   // the Z buffer is free again: reuse it for the indicator chunks
             const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
-            int rc = gcta_b200_nonmiss_matrix(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, p->operand,
+            int rc = gcta_b200_nonmiss_matrix(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16,
                                               p->d_Zbuf[0], p->ldz, st, err, errcap);
             if (rc) return rc;
-            rc = gcta_b200_count_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_Ntiles, st, err, errcap);
+            rc = gcta_b200_count_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), op16, p->d_tiles, p->ntiles, p->d_Ntiles, st, err, errcap);
             if (rc) return rc;
             launches += 2;
         }
@@ -545,10 +557,10 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             GB_CUDA(cudaMemsetAsync(p->d_Dtiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
             for (int64_t c = 0; c < nchunks; c++) {
                 const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
-                int rc = gcta_b200_nonmiss_matrix_ex(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, p->operand, p->d_dk,
+                int rc = gcta_b200_nonmiss_matrix_ex(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16, p->d_dk,
                                                      p->d_Zbuf[0], p->ldz, st, err, errcap);
                 if (rc) return rc;
-                rc = gcta_b200_syrk_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_Dtiles, st, err, errcap);
+                rc = gcta_b200_syrk_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), op16, p->d_tiles, p->ntiles, p->d_Dtiles, st, err, errcap);
                 if (rc) return rc;
                 launches += 2;
             }

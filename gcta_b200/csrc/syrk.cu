@@ -49,8 +49,8 @@ __device__ __forceinline__ uint64_t make_mn_desc(uint32_t smem_addr)
 // int32 tile - the pair counts N_ij on the tensor cores, bit-exact.
 template <bool INT_ACC>
 __global__ void __launch_bounds__(SYRK_THREADS, 1)
-syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restrict__ tiles, int ntiles, int nkb,
-                  float* __restrict__ S, uint32_t idesc)
+syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
+                  const int2* __restrict__ tiles, int ntiles, int nkb, float* __restrict__ S, uint32_t idesc)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -64,7 +64,8 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restri
     const int lane = threadIdx.x & 31;
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tmap);
+        tma_prefetch_desc(&tmapA);
+        tma_prefetch_desc(&tmapB);
         for (int s = 0; s < NUM_STAGES; s++) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -96,10 +97,10 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmap, const int2* __restri
                     mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
 #pragma unroll
                     for (int g = 0; g < A_GROUPS; g++)
-                        tma_load_2d(st + g * GROUP_BYTES, &tmap, &full_bar[stage], row0 + g * GROUP_MN, kb * BLOCK_K);
+                        tma_load_2d(st + g * GROUP_BYTES, &tmapA, &full_bar[stage], row0 + g * GROUP_MN, kb * BLOCK_K);
 #pragma unroll
                     for (int g = 0; g < B_GROUPS; g++)
-                        tma_load_2d(st + (A_GROUPS + g) * GROUP_BYTES, &tmap, &full_bar[stage], col0 + g * GROUP_MN,
+                        tma_load_2d(st + (A_GROUPS + g) * GROUP_BYTES, &tmapB, &full_bar[stage], col0 + g * GROUP_MN,
                                     kb * BLOCK_K);
                     if (++stage == NUM_STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -207,14 +208,14 @@ static EncodeTiledFn get_encode_fn()
 
 }  // namespace gb
 
-static int syrk_launch(bool int_acc, const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
+static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
                        int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
 {
     using namespace gb;
-    GB_ARG(d_Z && d_tiles && d_S, "syrk: null pointer");
+    GB_ARG(d_Z && d_Zb && d_tiles && d_S, "syrk: null pointer");
     GB_ARG(ldz > 0 && ldz % TILE_N == 0, "syrk: ldz must be a positive multiple of 256");
     GB_ARG(kc_pad > 0 && kc_pad % BLOCK_K == 0, "syrk: kc_pad must be a positive multiple of 64");
-    GB_ARG(((uintptr_t)d_Z & 127) == 0, "syrk: Z must be 128-byte aligned");
+    GB_ARG(((uintptr_t)d_Z & 127) == 0 && ((uintptr_t)d_Zb & 127) == 0, "syrk: Z must be 128-byte aligned");
     GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "syrk: unknown operand type");
     if (ntiles == 0) return 0;
     int dev = 0, sms = 0;
@@ -223,7 +224,7 @@ static int syrk_launch(bool int_acc, const void* d_Z, int64_t ldz, int64_t kc_pa
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return set_err(err, errcap, GCTA_B200_ERR_NO_DEVICE, "Error: cuTensorMapEncodeTiled is not available from the driver.");
 
-    CUtensorMap tmap;
+    CUtensorMap tmap, tmapB;
     cuuint64_t gdim[2] = {(cuuint64_t)ldz, (cuuint64_t)kc_pad};
     cuuint64_t gstride[1] = {(cuuint64_t)ldz * 2};
     cuuint32_t box[2] = {GROUP_MN, BLOCK_K};
@@ -231,6 +232,10 @@ static int syrk_launch(bool int_acc, const void* d_Z, int64_t ldz, int64_t kc_pa
     CUresult cr = enc(&tmap, operand == GCTA_B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
                       const_cast<void*>(d_Z), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                       CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr == CUDA_SUCCESS)   // the B operand may come from another matrix of the same shape (split-FP16 cross terms)
+        cr = enc(&tmapB, operand == GCTA_B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                 const_cast<void*>(d_Zb), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS)
         return set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: cuTensorMapEncodeTiled failed with code " + std::to_string((int)cr));
 
@@ -249,10 +254,10 @@ static int syrk_launch(bool int_acc, const void* d_Z, int64_t ldz, int64_t kc_pa
     int grid = (int)(ntiles < sms ? ntiles : sms);
     if (int_acc)
         syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(
-            tmap, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
+            tmap, tmapB, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
     else
         syrk_tiles_kernel<false><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(
-            tmap, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
+            tmap, tmapB, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
     GB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -260,7 +265,14 @@ static int syrk_launch(bool int_acc, const void* d_Z, int64_t ldz, int64_t kc_pa
 extern "C" int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
                                     int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
 {
-    return syrk_launch(false, d_Z, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap);
+    return syrk_launch(false, d_Z, d_Z, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap);
+}
+
+// S += Za^T Zb on the same tile list: rows of a tile come from Za, columns from Zb (two matrices of one shape)
+extern "C" int gcta_b200_syrk_tiles_ab(const void* d_Za, const void* d_Zb, int64_t ldz, int64_t kc_pad, int32_t operand,
+                                       const int32_t* d_tiles, int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
+{
+    return syrk_launch(false, d_Za, d_Zb, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap);
 }
 
 extern "C" int gcta_b200_count_tiles(const void* d_OK, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
@@ -268,5 +280,5 @@ extern "C" int gcta_b200_count_tiles(const void* d_OK, int64_t ldz, int64_t kc_p
 {
     using namespace gb;
     GB_ARG(kc_pad < (1 << 24), "count_tiles: more than 2^24 SNPs per call would not be exact in FP32");
-    return syrk_launch(true, d_OK, ldz, kc_pad, operand, d_tiles, ntiles, reinterpret_cast<float*>(d_Ntiles), stream, err, errcap);
+    return syrk_launch(true, d_OK, d_OK, ldz, kc_pad, operand, d_tiles, ntiles, reinterpret_cast<float*>(d_Ntiles), stream, err, errcap);
 }

@@ -92,7 +92,8 @@ static void option(int argc, char* argv_in[])
             cout << "--operand " << v << endl;
             if (v == "fp16") operand = GCTA_B200_FP16;
             else if (v == "bf16") operand = GCTA_B200_BF16;
-            else throw("\nError: --operand should be fp16 or bf16.\n");
+            else if (v == "fp16x2") operand = GCTA_B200_FP16X2;
+            else throw("\nError: --operand should be fp16, bf16 or fp16x2.\n");
         }
         else if (is("--chunk-snps")) { chunk_snps = atoll(argv[++i]); cout << "--chunk-snps " << chunk_snps << endl; }
         else if (is("gcta")) break;

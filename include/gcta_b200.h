@@ -40,7 +40,12 @@ typedef enum {
 /* operand type of the standardised genotypes fed to the tensor cores (FP32 accumulate). */
 typedef enum {
     GCTA_B200_FP16 = 0, /* default: 11-bit significand, |z| <= 65504 (MAF >= 1e-9) */
-    GCTA_B200_BF16 = 1
+    GCTA_B200_BF16 = 1,
+    /* "tight" mode: z = hi + lo with hi = fp16(z), lo = fp16(z - hi); S = hi'hi + hi'lo + lo'hi on the tensor
+     * cores (3x the SYRK work, twice the Z traffic).  Products are then exact to ~2^-22 relative, so A agrees
+     * with the reference to FP32-accumulation accuracy (max|dA| ~1e-7).  The north-star's "TF32 mode for tighter
+     * agreement": TF32 itself has FP16's 10-bit mantissa and would not be tighter than the default. */
+    GCTA_B200_FP16X2 = 2
 } gcta_b200_operand;
 
 /* ------------------------------------------------------------------------------------------
@@ -198,6 +203,13 @@ int gcta_b200_nonmiss_planes(const uint8_t* d_bed, int64_t pitch, int64_t n_file
 int gcta_b200_syrk_tiles(const void* d_Z, int64_t ldz, int64_t kc_pad, int32_t operand,
                          const int32_t* d_tiles, int64_t ntiles, float* d_S,
                          void* stream, char* err, size_t errcap);
+
+/* K2 with different row and column operands:  S += Za^T Zb  on the same tile list (two matrices of one shape).
+ * Used for the cross terms hi'lo + lo'hi of the split-FP16 operand mode (GCTA_B200_FP16X2), where
+ * gcta_b200_bed_decode writes the residual plane kc_pad*ldz elements behind the first. */
+int gcta_b200_syrk_tiles_ab(const void* d_Za, const void* d_Zb, int64_t ldz, int64_t kc_pad, int32_t operand,
+                            const int32_t* d_tiles, int64_t ntiles, float* d_S,
+                            void* stream, char* err, size_t errcap);
 
 /* K3 - bit-exact pair counts N_ij = sum_k ok_ik ok_jk by AND + popc over the K1m bit planes
  * (grm.cpp:291), accumulated into int32 tiles laid out like K2's S tiles. */

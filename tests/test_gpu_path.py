@@ -138,6 +138,22 @@ def test_tensor_core_counts_equal_popc_counts(monkeypatch):
     check_grm(A0, N0, pack_lower(Aref), pack_lower(Nref))
 
 
+def test_split_fp16_operand_mode_is_tighter():
+    """GCTA_B200_FP16X2 (hi + lo planes, three tensor passes): agreement with the reference at FP32-accumulation
+    level, an order of magnitude tighter than plain FP16 operands; several chunks and missing data."""
+    n, m = 900, 12000
+    bed = synth.make_bed_payload(17, n, m, miss_rate=0.01)
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n)
+    ref = pack_lower(Aref)
+    A1, N1, _, _ = abi.make_grm(bed, n, m, operand=abi.FP16, chunk_snps=4096)
+    A2, N2, _, o2 = abi.make_grm(bed, n, m, operand=abi.FP16X2, chunk_snps=4096)
+    assert np.array_equal(N1, pack_lower(Nref)) and np.array_equal(N2, N1)
+    e1, e2 = np.abs(A1 - ref).max(), np.abs(A2 - ref).max()
+    print(f"max|dA| fp16 {e1:.2e}  fp16x2 {e2:.2e}")
+    assert e2 <= 5e-7 and e2 < e1 / 5
+    check_grm(A2, N2, ref, pack_lower(Nref), atol=1e-6)
+
+
 def test_errors_are_reported_not_thrown():
     bed = synth.make_bed_payload(1, 40, 50)
     with pytest.raises(abi.GctaB200Error) as e:
