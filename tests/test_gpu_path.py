@@ -138,6 +138,36 @@ def test_tensor_core_counts_equal_popc_counts(monkeypatch):
     check_grm(A0, N0, pack_lower(Aref), pack_lower(Nref))
 
 
+@pytest.mark.parametrize("with_keep", [False, True])
+def test_row_bands_on_the_wide_row_decode_path(with_keep):
+    """n >= 16384 takes K1's one-CTA-per-SNP path (byte-table emit loop); row bands then standardise only the
+    first row_end individuals (narrower Z) and sum the diagonal only for their own slice.  Four bands written into
+    one buffer must equal the single-GPU result bit for bit, with and without a keep list (gather path)."""
+    n_file, m = 17000, 320
+    bed = synth.make_bed_payload(23, n_file, m, miss_rate=0.01)
+    keep = None
+    if with_keep:
+        keep = np.sort(np.random.default_rng(5).choice(n_file, 16500, replace=False)).astype(np.int32)
+    n = n_file if keep is None else len(keep)
+    A0, N0, mu0, _ = abi.make_grm(bed, n_file, m, keep=keep)
+    A = np.full(n * (n + 1) // 2, np.nan, dtype=np.float32)
+    N = np.full(n * (n + 1) // 2, -1, dtype=np.int32)
+    for r in range(4):
+        with abi.Plan(n_file, m, keep=keep, part_rank=r, part_world=4) as p:
+            p.upload(bed)
+            p.run()
+            p.download(A, N)
+    assert np.array_equal(N, N0) and np.array_equal(A, A0)
+    # oracle on a sub-block that straddles band boundaries
+    sub = np.sort(np.random.default_rng(6).choice(n, 300, replace=False))
+    ksub = sub if keep is None else keep[sub]
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n_file, keep=ksub, mu=mu0)
+    ii, jj = np.tril_indices(len(sub))
+    gi, gj = sub[ii].astype(np.int64), sub[jj].astype(np.int64)
+    idx = gi * (gi + 1) // 2 + gj
+    check_grm(A[idx], N[idx], Aref[ii, jj], Nref[ii, jj])
+
+
 def test_split_fp16_operand_mode_is_tighter():
     """GCTA_B200_FP16X2 (hi + lo planes, three tensor passes): agreement with the reference at FP32-accumulation
     level, an order of magnitude tighter than plain FP16 operands; several chunks and missing data."""

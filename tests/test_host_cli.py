@@ -174,6 +174,21 @@ def test_reference_reader_accepts_our_multi_member_gz(tmp_path):
 
 
 @pytest.mark.gpu
+def test_cli_two_gpus_when_present(tmp_path):
+    """--gpus 2: one host thread per GPU, each computing its row band into the shared host buffers."""
+    from gcta_b200 import abi
+    if abi.lib().gcta_b200_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    d = tmp_path / "g1_basic"
+    shutil.copytree(os.path.join(GOLDEN, "g1_basic"), d)
+    r = run_cli(["--bfile", "t", "--make-grm", "--gpus", "2", "--out", "mine2"], d)
+    assert r.stderr.strip() == "", r.stderr
+    A, N, _ = grmio.read_grm_gz(str(d / "mine2.grm.gz"))
+    Aref, Nref, _ = grmio.read_grm_gz(os.path.join(GOLDEN, "g1_basic", "o.grm.gz"))
+    check_grm(A, N, Aref, Nref)
+
+
+@pytest.mark.gpu
 def test_cli_grm_alg1(tmp_path):
     _full_case(tmp_path, "g2_edge", ["--bfile", "t", "--make-grm", "--grm-alg", "1"], "o_alg1",
                ["--bfile", "t", "--make-grm-bin", "--grm-alg", "1"], "ob_alg1", same_log=False)
