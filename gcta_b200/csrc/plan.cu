@@ -27,14 +27,15 @@ static int64_t tiles_in_row_block(int64_t bi, int64_t n)
     return last_row / TILE_N + 1;
 }
 
-// row blocks per raster group (measured on cfg3: 4-8 equivalent, 2 and 12 are 15 % slower; profiles/README.md)
+// row blocks per raster group: with the wave barrier of K2 a wave of 148 tiles is ~12 x 12 tiles sharing 12 + 12 operand
+// panels (measured on cfg3 with the barrier: 6: 1420, 12: 1433, 24: 1406 TFLOP/s; without it 6 was best; profiles/README.md)
 static int raster_rows()
 {
     static int v = 0;
     if (!v) {
         const char* e = getenv("GCTA_B200_RASTER");
-        v = e ? atoi(e) : 6;
-        if (v < 1) v = 6;
+        v = e ? atoi(e) : 12;
+        if (v < 1) v = 12;
     }
     return v;
 }

@@ -18,6 +18,9 @@
 //                       in HBM (S carries the sum over SNP chunks)
 #include <cuda.h>
 
+#include <atomic>
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace gb {
@@ -50,7 +53,8 @@ __device__ __forceinline__ uint64_t make_mn_desc(uint32_t smem_addr)
 template <bool INT_ACC>
 __global__ void __launch_bounds__(SYRK_THREADS, 1)
 syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
-                  const int2* __restrict__ tiles, int ntiles, int nkb, float* __restrict__ S, uint32_t idesc)
+                  const int2* __restrict__ tiles, int ntiles, int nkb, float* __restrict__ S, uint32_t idesc,
+                  unsigned int* wave_counter)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -88,7 +92,18 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            const int nwaves = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;
+            for (int w = 0; w < nwaves; w++) {
+                const int t = blockIdx.x + w * (int)gridDim.x;
+                if (wave_counter) {
+                    // Wave barrier (cooperative launch): every CTA starts wave w together.  CTAs that share
+                    // an operand panel then stream it within the few k-blocks of history L2 keeps per CTA, instead of
+                    // drifting apart over the launch and re-fetching it from HBM.
+                    atomicAdd(wave_counter, 1u);
+                    const unsigned int target = gridDim.x * (unsigned int)(w + 1);
+                    while (*reinterpret_cast<volatile unsigned int*>(wave_counter) < target) {}
+                }
+                if (t >= ntiles) break;
                 const int2 tl = tiles[t];
                 const int row0 = tl.x * TILE_M, col0 = tl.y * TILE_N;
                 for (int kb = 0; kb < nkb; kb++) {
@@ -189,6 +204,11 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     }
 }
 
+// arrival counters of the wave barrier; launches take slots round-robin so that launches in flight on different
+// streams of one device never share a counter
+constexpr int WAVE_SLOTS = 64;
+static __device__ unsigned int g_wave_counter[WAVE_SLOTS];
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -252,12 +272,28 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
         attr_set[dev] = true;
     }
     int grid = (int)(ntiles < sms ? ntiles : sms);
-    if (int_acc)
-        syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(
-            tmap, tmapB, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
+    const int2* tl = reinterpret_cast<const int2*>(d_tiles);
+    int nt = (int)ntiles, nkb = (int)(kc_pad / BLOCK_K);
+    uint32_t id = idesc;
+    unsigned int* counter = nullptr;
+    // Wave barrier on by default (cfg3: +10 % whole-job, HBM reads of K2 -40 %; profiles/README.md); GCTA_B200_WAVESYNC=0 disables
+    static const bool wave_sync = !(getenv("GCTA_B200_WAVESYNC") && atoi(getenv("GCTA_B200_WAVESYNC")) == 0);
+    if (wave_sync && ntiles > grid) {
+        static unsigned int* cached[64] = {};
+        static std::atomic<unsigned> next_slot{0};
+        if (dev < 64 && !cached[dev]) GB_CUDA(cudaGetSymbolAddress((void**)&cached[dev], g_wave_counter));
+        counter = dev < 64 ? cached[dev] + (next_slot++ % WAVE_SLOTS) : nullptr;
+    }
+    if (counter) {
+        // the barrier needs all CTAs resident at once: cooperative launch guarantees it (or fails loudly)
+        GB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), (cudaStream_t)stream));
+        void* args[] = {&tmap, &tmapB, &tl, &nt, &nkb, &d_S, &id, &counter};
+        const void* fn = int_acc ? (const void*)syrk_tiles_kernel<true> : (const void*)syrk_tiles_kernel<false>;
+        GB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SYRK_THREADS), args, SYRK_SMEM, (cudaStream_t)stream));
+    } else if (int_acc)
+        syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
     else
-        syrk_tiles_kernel<false><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(
-            tmap, tmapB, reinterpret_cast<const int2*>(d_tiles), (int)ntiles, (int)(kc_pad / BLOCK_K), d_S, idesc);
+        syrk_tiles_kernel<false><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
     GB_CUDA(cudaGetLastError());
     return 0;
 }
