@@ -283,7 +283,7 @@ def k2_traffic(n, world):
 def plan_chunk(plan, n, m):
     """SNPs per chunk the plan chose (mirrors plan.cu: <= 8 GiB of Z)."""
     ldz = (n + 255) // 256 * 256
-    kc = (8 << 30) // (ldz * 2) // 64 * 64
+    kc = (int(os.environ.get("GCTA_B200_ZCAP_GIB", "16")) << 30) // (ldz * 2) // 64 * 64
     return max(64, min(kc, (m + 63) // 64 * 64))
 
 

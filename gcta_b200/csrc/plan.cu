@@ -289,7 +289,11 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     {
         size_t free_b = 0, total_b = 0;
         PLAN_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        int64_t budget = std::min<int64_t>((int64_t)(free_b / 4), 8ll << 30);   // per Z buffer (two when overlapping)
+        // per Z buffer (two when overlapping).  Larger chunks mean fewer SYRK launches, hence fewer epilogues and
+        // less read-modify-write of S; 16 GiB leaves room for everything else at every BASELINE configuration.
+        int64_t zcap = 16ll << 30;
+        if (const char* e = getenv("GCTA_B200_ZCAP_GIB")) zcap = std::max<int64_t>(1, atoll(e)) << 30;
+        int64_t budget = std::min<int64_t>((int64_t)(free_b / 4), zcap);
         const int planes = a->operand == GCTA_B200_FP16X2 ? 2 : 1;   // split mode keeps a residual plane behind the first
         int64_t kc = a->chunk_snps > 0 ? a->chunk_snps : budget / (p->ldz * 2 * planes);
         kc = std::max<int64_t>(64, kc / 64 * 64);
