@@ -132,7 +132,8 @@ struct gcta_b200_plan {
     uint8_t* d_bed = nullptr;
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
-    int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr;
+    int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr, *d_pairs = nullptr;   // d_pairs: CTA-pair work list of the cta_group::2 SYRK
+    int64_t npairs = 0;
     double *d_mu_in = nullptr, *d_mu = nullptr, *d_diag = nullptr, *d_dk = nullptr, *d_dw = nullptr;   // d_dk, d_dw: --grm-alg 1
     float* d_Dtiles = nullptr;
     float *d_zlut = nullptr, *d_S = nullptr, *d_A_lower = nullptr;
@@ -284,6 +285,14 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         std::vector<int32_t> tl((size_t)p->ntiles * 2 + 2);
         gcta_b200_tile_list(n, p->row_begin, p->row_end, tl.data());
         PLAN_CUDA(cudaMemcpy(p->d_tiles, tl.data(), (size_t)p->ntiles * 8, cudaMemcpyHostToDevice));
+        // GCTA_B200_2CTA=1: run K2 as CTA pairs (tcgen05.mma.cta_group::2, syrk2.cu) over the same tile storage
+        if (getenv("GCTA_B200_2CTA") && atoi(getenv("GCTA_B200_2CTA")) > 0 && p->ntiles > 0) {
+            p->npairs = gcta_b200_pair_list(tl.data(), p->ntiles, raster_rows(), nullptr);
+            std::vector<int32_t> pl((size_t)p->npairs * 4 + 4);
+            gcta_b200_pair_list(tl.data(), p->ntiles, raster_rows(), pl.data());
+            PLAN_TRY(dev_alloc(p, &p->d_pairs, (size_t)p->npairs * 4, err, errcap));
+            PLAN_CUDA(cudaMemcpy(p->d_pairs, pl.data(), (size_t)p->npairs * 16, cudaMemcpyHostToDevice));
+        }
     }
     // SNP chunk: Z buffer of at most ~8 GiB (or what is left of HBM), multiple of 64 SNPs
     {
@@ -457,6 +466,12 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     }
     auto EV = [&](int64_t c, int which) { return p->events[(size_t)(2 + 4 * c + which)]; };
     int launches = 0;
+    // K2 dispatch: out (+)= Za^T Zb over the band's tiles, as single CTAs (syrk.cu) or as CTA pairs (syrk2.cu)
+    auto syrk = [&](const void* Za, const void* Zb, int64_t kp, int op, void* outp, bool int_acc, cudaStream_t s) -> int {
+        if (p->d_pairs) return gcta_b200_syrk_pairs(Za, Zb, p->ldz, kp, op, p->d_pairs, p->npairs, outp, int_acc, s, err, errcap);
+        if (int_acc) return gcta_b200_count_tiles(Za, p->ldz, kp, op, p->d_tiles, p->ntiles, (int32_t*)outp, s, err, errcap);
+        return gcta_b200_syrk_tiles_ab(Za, Zb, p->ldz, kp, op, p->d_tiles, p->ntiles, (float*)outp, s, err, errcap);
+    };
     GB_CUDA(cudaEventRecord(p->events[0], st));
     GB_CUDA(cudaMemsetAsync(p->d_S, 0, (size_t)p->ntiles * TILE_M * TILE_N * sizeof(float), st));
     GB_CUDA(cudaMemsetAsync(p->d_diag, 0, (size_t)p->n_file * 8, st));
@@ -488,12 +503,12 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             const int64_t kp = round_up(kc, 64);
             const uint16_t* hi = (const uint16_t*)Z;
             const uint16_t* lo = hi + kp * p->ldz;
-            rc = gcta_b200_syrk_tiles(hi, p->ldz, kp, GCTA_B200_FP16, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
-            if (!rc) rc = gcta_b200_syrk_tiles_ab(hi, lo, p->ldz, kp, GCTA_B200_FP16, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
-            if (!rc) rc = gcta_b200_syrk_tiles_ab(lo, hi, p->ldz, kp, GCTA_B200_FP16, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+            rc = syrk(hi, hi, kp, GCTA_B200_FP16, p->d_S, false, st);
+            if (!rc) rc = syrk(hi, lo, kp, GCTA_B200_FP16, p->d_S, false, st);
+            if (!rc) rc = syrk(lo, hi, kp, GCTA_B200_FP16, p->d_S, false, st);
             launches += 2;
         } else
-            rc = gcta_b200_syrk_tiles(Z, p->ldz, round_up(kc, 64), p->operand, p->d_tiles, p->ntiles, p->d_S, st, err, errcap);
+            rc = syrk(Z, Z, round_up(kc, 64), p->operand, p->d_S, false, st);
         if (rc) return rc;
         GB_CUDA(cudaEventRecord(EV(c, 3), st));
         launches += 3;
@@ -523,7 +538,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             int rc = gcta_b200_nonmiss_matrix(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16,
                                               p->d_Zbuf[0], p->ldz, st, err, errcap);
             if (rc) return rc;
-            rc = gcta_b200_count_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), op16, p->d_tiles, p->ntiles, p->d_Ntiles, st, err, errcap);
+            rc = syrk(p->d_Zbuf[0], p->d_Zbuf[0], round_up(kc, 64), op16, p->d_Ntiles, true, st);
             if (rc) return rc;
             launches += 2;
         }
@@ -565,7 +580,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
                 int rc = gcta_b200_nonmiss_matrix_ex(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16, p->d_dk,
                                                      p->d_Zbuf[0], p->ldz, st, err, errcap);
                 if (rc) return rc;
-                rc = gcta_b200_syrk_tiles(p->d_Zbuf[0], p->ldz, round_up(kc, 64), op16, p->d_tiles, p->ntiles, p->d_Dtiles, st, err, errcap);
+                rc = syrk(p->d_Zbuf[0], p->d_Zbuf[0], round_up(kc, 64), op16, p->d_Dtiles, false, st);
                 if (rc) return rc;
                 launches += 2;
             }

@@ -211,6 +211,18 @@ int gcta_b200_syrk_tiles_ab(const void* d_Za, const void* d_Zb, int64_t ldz, int
                             const int32_t* d_tiles, int64_t ntiles, float* d_S,
                             void* stream, char* err, size_t errcap);
 
+/* K2 as CTA pairs (tcgen05.mma.cta_group::2): two SMs work on two vertically adjacent 256x256 tiles and share the
+ * column operand, each staging only half of it (csrc/syrk2.cu).  Same tile storage as gcta_b200_syrk_tiles.
+ *   gcta_b200_pair_list  host helper: from a band's tile list (gcta_b200_tile_list order = storage order) to the work
+ *                        list int32[count][4] = {column block, first row block, storage index of the upper tile or -1,
+ *                        storage index of the lower tile or -1}; returns count (pairs == NULL: count only)
+ *   gcta_b200_syrk_pairs d_S (+)= Za^T Zb over the pair list; int_acc != 0: counting mode (d_S is int32 tiles)
+ * Selected for the whole path with GCTA_B200_2CTA=1. */
+int64_t gcta_b200_pair_list(const int32_t* tiles, int64_t ntiles, int32_t raster_rows, int32_t* pairs);
+int gcta_b200_syrk_pairs(const void* d_Za, const void* d_Zb, int64_t ldz, int64_t kc_pad, int32_t operand,
+                         const int32_t* d_pairs, int64_t npairs, void* d_S, int32_t int_acc,
+                         void* stream, char* err, size_t errcap);
+
 /* K3 - bit-exact pair counts N_ij = sum_k ok_ik ok_jk by AND + popc over the K1m bit planes
  * (grm.cpp:291), accumulated into int32 tiles laid out like K2's S tiles. */
 int gcta_b200_paircount_tiles(const uint32_t* d_planes, int64_t ldm, int64_t nwords,

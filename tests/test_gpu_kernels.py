@@ -200,6 +200,52 @@ def test_syrk_accumulates_over_chunks_and_random_data():
     assert np.abs(got[ii, jj] - ref[ii, jj]).max() < 2e-3  # fp32 accumulation of 640 terms of O(1)
 
 
+@pytest.mark.parametrize("n,kc,operand", [(300, 128, abi.FP16), (1000, 512, abi.BF16), (6000, 256, abi.FP16), (2500, 4096, abi.FP16)])
+def test_syrk_cta_pairs_exact_on_integer_operands(n, kc, operand):
+    """cta_group::2 variant (csrc/syrk2.cu): same tile storage, exact on integer operands; n=6000 gives 300 tiles =
+    more pair items than SM pairs, so the persistent loop, the wave barrier and odd row-block counts are exercised;
+    a second launch in counting mode (int32 epilogue) accumulates on top of the first."""
+    ldz = (n + 255) // 256 * 256
+    g = torch.Generator(device="cuda").manual_seed(n + kc + 1)
+    Zi = torch.randint(-3, 4, (kc, ldz), generator=g, device="cuda", dtype=torch.int32)
+    Zi[:, n:] = 0
+    Zt = Zi.to(torch.float16 if operand == abi.FP16 else torch.bfloat16).contiguous()
+    tiles = abi.tile_list(n)
+    L = abi.lib()
+    L.gcta_b200_pair_list.restype = C.c_int64
+    npairs = L.gcta_b200_pair_list(P(tiles.ctypes.data), I64(len(tiles)), I32(12), P(None))
+    pairs = np.zeros((npairs, 4), dtype=np.int32)
+    L.gcta_b200_pair_list(P(tiles.ctypes.data), I64(len(tiles)), I32(12), P(pairs.ctypes.data))
+    # every tile appears exactly once as an upper or lower member of a pair
+    seen = sorted([t for t in pairs[:, 2:].ravel() if t >= 0])
+    assert seen == list(range(len(tiles)))
+    d_pairs = dev(pairs)
+    S = torch.zeros(len(tiles) * 256 * 256, dtype=torch.float32, device="cuda")
+    abi.call("gcta_b200_syrk_pairs", P(Zt.data_ptr()), P(Zt.data_ptr()), I64(ldz), I64(kc), I32(operand), P(d_pairs.data_ptr()),
+             I64(npairs), P(S.data_ptr()), I32(0), stream())
+    torch.cuda.synchronize()
+    ref = (Zi.double().T @ Zi.double()).cpu().numpy()
+    got = s_tiles_to_dense(S.cpu().numpy(), tiles, ldz)
+    for (bi, bj) in tiles:
+        r = slice(bi * 256, (bi + 1) * 256)
+        c = slice(bj * 256, (bj + 1) * 256)
+        assert np.array_equal(got[r, c], ref[r, c]), f"tile {(bi, bj)} wrong, max diff {np.abs(got[r, c] - ref[r, c]).max()}"
+    # counting mode on |Z| in {0,1}
+    Ok = (Zi != 0).to(torch.float16 if operand == abi.FP16 else torch.bfloat16).contiguous()
+    Nt = torch.zeros(len(tiles) * 256 * 256, dtype=torch.int32, device="cuda")
+    for _ in range(2):
+        abi.call("gcta_b200_syrk_pairs", P(Ok.data_ptr()), P(Ok.data_ptr()), I64(ldz), I64(kc), I32(operand), P(d_pairs.data_ptr()),
+                 I64(npairs), P(Nt.data_ptr()), I32(1), stream())
+    torch.cuda.synchronize()
+    okd = (Zi != 0).double()
+    refn = (2 * (okd.T @ okd)).cpu().numpy()
+    gotn = s_tiles_to_dense(Nt.cpu().numpy(), tiles, ldz)
+    for (bi, bj) in tiles:
+        r = slice(bi * 256, (bi + 1) * 256)
+        c = slice(bj * 256, (bj + 1) * 256)
+        assert np.array_equal(gotn[r, c], refn[r, c])
+
+
 def test_diag_planes_paircount_finalize():
     n, m = 600, 1000
     bed = synth.make_bed_payload(21, n, m, miss_rate=0.04)
