@@ -289,7 +289,15 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
         GB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), (cudaStream_t)stream));
         void* args[] = {&tmap, &tmapB, &tl, &nt, &nkb, &d_S, &id, &counter};
         const void* fn = int_acc ? (const void*)syrk_tiles_kernel<true> : (const void*)syrk_tiles_kernel<false>;
-        GB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SYRK_THREADS), args, SYRK_SMEM, (cudaStream_t)stream));
+        cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SYRK_THREADS), args, SYRK_SMEM, (cudaStream_t)stream);
+        if (ce == cudaErrorCooperativeLaunchTooLarge || ce == cudaErrorNotSupported || ce == cudaErrorLaunchOutOfResources) {
+            // e.g. part of the GPU is held by another context: run the same kernel without the barrier
+            cudaGetLastError();
+            counter = nullptr;
+            if (int_acc) syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
+            else syrk_tiles_kernel<false><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
+        } else
+            GB_CUDA(ce);
     } else if (int_acc)
         syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
     else
