@@ -167,6 +167,7 @@ def main_ours(a, rank, world, local_rank):
     dev_ms_max = max_over_ranks(dev_ms)
     wall_ms_max = max_over_ranks(wall_ms)
     launches_total = int(sum_over_ranks(launches))
+    per_rank = ranks.gather([row_begin, row_end, dev_ms / a.steps, syrk_ms / a.steps, dec_ms / a.steps, clocks.get("sm_mhz") or 0.0])
     value = pairs_total * m * a.steps / (dev_ms_max * 1e-3)
 
     # roofline of the dominant kernel (K2, tensor bound): algorithmic flops of this rank's band / K2 device time
@@ -250,6 +251,8 @@ def main_ours(a, rank, world, local_rank):
                          "traffic": k2_traffic(n, world), "launches_per_step": nchunks,
                          "k1_decode_GBps": k1_bytes / (dec_ms / a.steps * 1e-3) / 1e9 if dec_ms > 0 else None, "hbm_peak_GBps": hbm},
             "clocks": clocks, "gpu_launches": launches_total,
+            "per_rank": [{"rows": [int(r[0]), int(r[1])], "ms_total": round(r[2], 2), "ms_syrk": round(r[3], 2), "ms_decode": round(r[4], 2),
+                          "sm_mhz": r[5]} for r in per_rank],
         }
         if e2e:
             line["e2e"] = e2e

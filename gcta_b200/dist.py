@@ -60,6 +60,17 @@ class Ranks:
     def sum(self, x: float) -> float:
         return self._reduce(x, "SUM")
 
+    def gather(self, values):
+        """list (one entry per rank) of each rank's list of floats"""
+        if self._dist is None:
+            return [list(map(float, values))]
+        import torch
+        dev = self.device if self.device is not None else "cpu"
+        t = torch.tensor(list(values), dtype=torch.float64, device=dev)
+        out = [torch.zeros_like(t) for _ in range(self.world)]
+        self._dist.all_gather(out, t)
+        return [o.cpu().tolist() for o in out]
+
     def close(self):
         if self._dist is not None:
             self._dist.destroy_process_group()
