@@ -8,6 +8,7 @@
 #include <fstream>
 #include <iomanip>
 #include <iostream>
+#include <chrono>
 #include <thread>
 
 #include "../../include/gcta_b200.h"
@@ -196,6 +197,7 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
     vector<string> errs(G);
     vector<int> rcs(G, 0);
     vector<gcta_b200_out> outs(G);
+    const auto t_c0 = std::chrono::steady_clock::now();
     auto work = [&](int g) {
         gcta_b200_args a;
         memset(&a, 0, sizeof a);
@@ -223,12 +225,16 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
     cout << n << " of " << n << " individuals.\r";   // the reference prints one such line per row (grm.cpp:297)
     cout << endl << endl;
     if (getenv("GCTA_B200_TIMING")) {
+        std::cerr << "{\"compute_wall_s\": " << std::chrono::duration<double>(std::chrono::steady_clock::now() - t_c0).count() << "}" << endl;
         for (int g = 0; g < G; g++)
             std::cerr << "{\"gpu\": " << g << ", \"rows\": [" << outs[g].row_begin << ", " << outs[g].row_end << "], \"ms_h2d\": " << outs[g].ms_h2d
                       << ", \"ms_decode\": " << outs[g].ms_decode << ", \"ms_syrk\": " << outs[g].ms_syrk << ", \"ms_paircount\": " << outs[g].ms_paircount
                       << ", \"ms_finalize\": " << outs[g].ms_finalize << ", \"ms_d2h\": " << outs[g].ms_d2h << ", \"launches\": " << outs[g].launches << "}" << endl;
     }
+    const auto t_w0 = std::chrono::steady_clock::now();
     output_grm(A, N, output_bin);
+    if (getenv("GCTA_B200_TIMING"))
+        std::cerr << "{\"write_s\": " << std::chrono::duration<double>(std::chrono::steady_clock::now() - t_w0).count() << "}" << endl;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -238,7 +244,9 @@ static void gz_member(const string& text, string& out)
 {
     z_stream s;
     memset(&s, 0, sizeof s);
-    if (deflateInit2(&s, Z_DEFAULT_COMPRESSION, Z_DEFLATED, 15 + 16 /* gzip wrapper */, 8, Z_DEFAULT_STRATEGY) != Z_OK)
+    // default level like the reference's gzopen(name, "w") (zfstream.cpp:51-76); GCTA_B200_GZ_LEVEL=1 trades ~20 % size for ~3x speed
+    static const int level = getenv("GCTA_B200_GZ_LEVEL") ? std::max(1, std::min(9, atoi(getenv("GCTA_B200_GZ_LEVEL")))) : Z_DEFAULT_COMPRESSION;
+    if (deflateInit2(&s, level, Z_DEFLATED, 15 + 16 /* gzip wrapper */, 8, Z_DEFAULT_STRATEGY) != Z_OK)
         throw string("Error: zlib deflateInit2 failed.");
     out.resize(deflateBound(&s, (uLong)text.size()) + 64);
     s.next_in = (Bytef*)text.data();
