@@ -535,10 +535,13 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
         for (int64_t c = 0; c < nchunks; c++) {   // the Z buffer is free again: reuse it for the indicator chunks
             const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
-            int rc = gcta_b200_nonmiss_matrix(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16,
+            // 8-bit E4M3 indicators (kind::f8f6f4: twice the MMA rate, half the bytes) unless the CTA-pair kernel or
+            // GCTA_B200_N_MODE=tensor16 asks for the 16-bit route; both give the same integers
+            const int opN = (p->d_pairs || (nmode && strcmp(nmode, "tensor16") == 0)) ? op16 : GCTA_B200_E4M3;
+            int rc = gcta_b200_nonmiss_matrix(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, opN,
                                               p->d_Zbuf[0], p->ldz, st, err, errcap);
             if (rc) return rc;
-            rc = syrk(p->d_Zbuf[0], p->d_Zbuf[0], round_up(kc, 64), op16, p->d_Ntiles, true, st);
+            rc = syrk(p->d_Zbuf[0], p->d_Zbuf[0], round_up(kc, opN == GCTA_B200_E4M3 ? 128 : 64), opN, p->d_Ntiles, true, st);
             if (rc) return rc;
             launches += 2;
         }

@@ -26,11 +26,20 @@
 namespace gb {
 
 constexpr int NUM_STAGES = 3;
-constexpr int GROUP_MN = 64;                                  // individuals per swizzle atom row (128 B)
-constexpr int A_GROUPS = TILE_M / GROUP_MN;                   // 4
-constexpr int B_GROUPS = TILE_N / GROUP_MN;                   // 4
-constexpr int GROUP_BYTES = BLOCK_K * GROUP_MN * 2;           // 8192: [64 k][64 mn] 16-bit
-constexpr int STAGE_BYTES = (A_GROUPS + B_GROUPS) * GROUP_BYTES;  // 65536
+constexpr int STAGE_BYTES = 65536;   // 256 A rows + 256 B columns x one K block, for either element size
+// Element-size dependent geometry.  EB = 2: FP16 / BF16 operands, kind::f16, UMMA K = 16.  EB = 1: E4M3 operands
+// (0/1 indicators of the counting pass), kind::f8f6f4, UMMA K = 32 - twice the MMA rate on half the bytes.
+// A 128-byte swizzle row holds 128/EB individuals; a K block is sized so that one group is 128 B x KB rows.
+template <int EB> struct Geo {
+    static constexpr int GROUP_MN = 128 / EB;                     // individuals per swizzle atom row
+    static constexpr int KB = 64 * (2 / EB);                      // SNPs per pipeline stage: 64 (16-bit) or 128 (8-bit)
+    static constexpr int GROUP_BYTES = KB * 128;                  // 8192 or 16384
+    static constexpr int A_GROUPS = TILE_M / GROUP_MN;            // 4 or 2
+    static constexpr int B_GROUPS = TILE_N / GROUP_MN;
+    static constexpr int UK = 32 / EB;                            // SNPs per tcgen05.mma
+    static constexpr int K_STEP_BYTES = UK * 128;                 // 2048 or 4096
+    static_assert((A_GROUPS + B_GROUPS) * GROUP_BYTES == STAGE_BYTES, "stage size");
+};
 constexpr int EPI_WARPS = 8;
 constexpr int SYRK_THREADS = 64 + 32 * EPI_WARPS;             // 320
 constexpr int TMEM_COLS = 512;
@@ -41,21 +50,36 @@ constexpr size_t SYRK_SMEM = (size_t)NUM_STAGES * STAGE_BYTES + 1024 /*align sla
 // 16-bit elements, LBO = byte distance between 64-wide MN groups, SBO = byte distance between
 // groups of 8 SNP rows (8 x 128 B).  Bits: [0,14) addr>>4, [16,30) LBO>>4, [32,46) SBO>>4,
 // [46,48) version = 1 (Blackwell), [61,64) layout = 2 (SWIZZLE_128B).
+template <int EB>
 __device__ __forceinline__ uint64_t make_mn_desc(uint32_t smem_addr)
 {
-    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(GROUP_BYTES >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) |
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(Geo<EB>::GROUP_BYTES >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) |
            (1ull << 46) | (2ull << 61);
+}
+
+// D[tmem] (+)= A[smem] * B[smem], kind::f8f6f4 (E4M3 in, FP32 accumulate); SASS UTCQMMA
+__device__ __forceinline__ void umma_f8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 
 // INT_ACC = false: S (float) += accumulator.  INT_ACC = true: the operands are 0/1 indicators, every
 // partial sum is an integer below 2^24 and therefore exact in FP32, and the epilogue adds it into an
 // int32 tile - the pair counts N_ij on the tensor cores, bit-exact.
-template <bool INT_ACC>
+template <bool INT_ACC, int EB = 2>
 __global__ void __launch_bounds__(SYRK_THREADS, 1)
 syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                   const int2* __restrict__ tiles, int ntiles, int nkb, float* __restrict__ S, uint32_t idesc,
                   unsigned int* wave_counter)
 {
+    using G = Geo<EB>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = (uint64_t*)(smem + NUM_STAGES * STAGE_BYTES);
@@ -111,12 +135,12 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                     uint8_t* st = smem + stage * STAGE_BYTES;
                     mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
 #pragma unroll
-                    for (int g = 0; g < A_GROUPS; g++)
-                        tma_load_2d(st + g * GROUP_BYTES, &tmapA, &full_bar[stage], row0 + g * GROUP_MN, kb * BLOCK_K);
+                    for (int g = 0; g < G::A_GROUPS; g++)
+                        tma_load_2d(st + g * G::GROUP_BYTES, &tmapA, &full_bar[stage], row0 + g * G::GROUP_MN, kb * G::KB);
 #pragma unroll
-                    for (int g = 0; g < B_GROUPS; g++)
-                        tma_load_2d(st + (A_GROUPS + g) * GROUP_BYTES, &tmapB, &full_bar[stage], col0 + g * GROUP_MN,
-                                    kb * BLOCK_K);
+                    for (int g = 0; g < G::B_GROUPS; g++)
+                        tma_load_2d(st + (G::A_GROUPS + g) * G::GROUP_BYTES, &tmapB, &full_bar[stage], col0 + g * G::GROUP_MN,
+                                    kb * G::KB);
                     if (++stage == NUM_STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -135,16 +159,21 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
-                    const uint64_t a0_desc = make_mn_desc(a_addr);                                        // rows   0..127
-                    const uint64_t a1_desc = make_mn_desc(a_addr + (UMMA_M / GROUP_MN) * GROUP_BYTES);    // rows 128..255
-                    const uint64_t b_desc = make_mn_desc(a_addr + A_GROUPS * GROUP_BYTES);
+                    const uint64_t a0_desc = make_mn_desc<EB>(a_addr);                                               // rows   0..127
+                    const uint64_t a1_desc = make_mn_desc<EB>(a_addr + (UMMA_M / G::GROUP_MN) * G::GROUP_BYTES);     // rows 128..255
+                    const uint64_t b_desc = make_mn_desc<EB>(a_addr + G::A_GROUPS * G::GROUP_BYTES);
 #pragma unroll
-                    for (int k4 = 0; k4 < BLOCK_K / 16; k4++) {
-                        // 16 SNPs = two 8-row swizzle atoms = 2048 B further along K
-                        const uint64_t adv = (uint64_t)((k4 * 2048) >> 4);
+                    for (int k4 = 0; k4 < G::KB / G::UK; k4++) {
+                        // one MMA consumes UK SNPs = UK/8 swizzle atoms of 8 rows x 128 B further along K
+                        const uint64_t adv = (uint64_t)((k4 * G::K_STEP_BYTES) >> 4);
                         const uint32_t acc = (kb | k4) != 0 ? 1u : 0u;
-                        umma_f16(tmem_base, a0_desc + adv, b_desc + adv, idesc, acc);
-                        umma_f16(tmem_base + TILE_N, a1_desc + adv, b_desc + adv, idesc, acc);
+                        if (EB == 2) {
+                            umma_f16(tmem_base, a0_desc + adv, b_desc + adv, idesc, acc);
+                            umma_f16(tmem_base + TILE_N, a1_desc + adv, b_desc + adv, idesc, acc);
+                        } else {
+                            umma_f8(tmem_base, a0_desc + adv, b_desc + adv, idesc, acc);
+                            umma_f8(tmem_base + TILE_N, a1_desc + adv, b_desc + adv, idesc, acc);
+                        }
                     }
                     umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
                     if (++stage == NUM_STAGES) { stage = 0; phase ^= 1; }
@@ -234,9 +263,13 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
     using namespace gb;
     GB_ARG(d_Z && d_Zb && d_tiles && d_S, "syrk: null pointer");
     GB_ARG(ldz > 0 && ldz % TILE_N == 0, "syrk: ldz must be a positive multiple of 256");
-    GB_ARG(kc_pad > 0 && kc_pad % BLOCK_K == 0, "syrk: kc_pad must be a positive multiple of 64");
+    const int eb = operand == GCTA_B200_E4M3 ? 1 : 2;      // bytes per operand element
+    const int kblock = eb == 1 ? Geo<1>::KB : Geo<2>::KB;  // SNPs per pipeline stage
+    GB_ARG(kc_pad > 0 && kc_pad % kblock == 0, eb == 1 ? "syrk: kc_pad must be a positive multiple of 128 for 8-bit operands"
+                                                        : "syrk: kc_pad must be a positive multiple of 64");
     GB_ARG(((uintptr_t)d_Z & 127) == 0 && ((uintptr_t)d_Zb & 127) == 0, "syrk: Z must be 128-byte aligned");
-    GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "syrk: unknown operand type");
+    GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16 || (operand == GCTA_B200_E4M3 && int_acc),
+           "syrk: unknown operand type (E4M3 is for the counting mode only)");
     if (ntiles == 0) return 0;
     int dev = 0, sms = 0;
     GB_CUDA(cudaGetDevice(&dev));
@@ -246,21 +279,22 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
 
     CUtensorMap tmap, tmapB;
     cuuint64_t gdim[2] = {(cuuint64_t)ldz, (cuuint64_t)kc_pad};
-    cuuint64_t gstride[1] = {(cuuint64_t)ldz * 2};
-    cuuint32_t box[2] = {GROUP_MN, BLOCK_K};
+    cuuint64_t gstride[1] = {(cuuint64_t)ldz * eb};
+    cuuint32_t box[2] = {(cuuint32_t)(128 / eb), (cuuint32_t)kblock};   // 128 bytes of individuals x one K block
     cuuint32_t estr[2] = {1, 1};
-    CUresult cr = enc(&tmap, operand == GCTA_B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
-                      const_cast<void*>(d_Z), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    const CUtensorMapDataType dt = eb == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                           : (operand == GCTA_B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
+    CUresult cr = enc(&tmap, dt, 2, const_cast<void*>(d_Z), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                       CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr == CUDA_SUCCESS)   // the B operand may come from another matrix of the same shape (split-FP16 cross terms)
-        cr = enc(&tmapB, operand == GCTA_B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+        cr = enc(&tmapB, dt, 2,
                  const_cast<void*>(d_Zb), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS)
         return set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: cuTensorMapEncodeTiled failed with code " + std::to_string((int)cr));
 
-    // instruction descriptor (kind::f16): D=F32 [4,6), A fmt [7,10), B fmt [10,13), A MN-major bit 15,
-    // B MN-major bit 16, N>>3 [17,23), M>>4 [24,29)
+    // instruction descriptor: D=F32 [4,6), A fmt [7,10), B fmt [10,13) (kind::f16: 0 = F16, 1 = BF16; kind::f8f6f4: 0 = E4M3),
+    // A MN-major bit 15, B MN-major bit 16, N>>3 [17,23), M>>4 [24,29)
     const uint32_t fmt = operand == GCTA_B200_BF16 ? 1u : 0u;
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(TILE_N >> 3) << 17) |
                            ((uint32_t)(UMMA_M >> 4) << 24);
@@ -269,12 +303,15 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
     if (dev < 64 && !attr_set[dev]) {
         GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
         GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
+        GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
         attr_set[dev] = true;
     }
     int grid = (int)(ntiles < sms ? ntiles : sms);
     const int2* tl = reinterpret_cast<const int2*>(d_tiles);
-    int nt = (int)ntiles, nkb = (int)(kc_pad / BLOCK_K);
+    int nt = (int)ntiles, nkb = (int)(kc_pad / kblock);
     uint32_t id = idesc;
+    typedef void (*KernelFn)(const CUtensorMap, const CUtensorMap, const int2*, int, int, float*, uint32_t, unsigned int*);
+    const KernelFn kfn = eb == 1 ? (KernelFn)syrk_tiles_kernel<true, 1> : (int_acc ? (KernelFn)syrk_tiles_kernel<true> : (KernelFn)syrk_tiles_kernel<false>);
     unsigned int* counter = nullptr;
     // Wave barrier on by default (cfg3: +10 % whole-job, HBM reads of K2 -40 %; profiles/README.md); GCTA_B200_WAVESYNC=0 disables
     static const bool wave_sync = !(getenv("GCTA_B200_WAVESYNC") && atoi(getenv("GCTA_B200_WAVESYNC")) == 0);
@@ -288,20 +325,16 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
         // the barrier needs all CTAs resident at once: cooperative launch guarantees it (or fails loudly)
         GB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), (cudaStream_t)stream));
         void* args[] = {&tmap, &tmapB, &tl, &nt, &nkb, &d_S, &id, &counter};
-        const void* fn = int_acc ? (const void*)syrk_tiles_kernel<true> : (const void*)syrk_tiles_kernel<false>;
-        cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SYRK_THREADS), args, SYRK_SMEM, (cudaStream_t)stream);
+        cudaError_t ce = cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid), dim3(SYRK_THREADS), args, SYRK_SMEM, (cudaStream_t)stream);
         if (ce == cudaErrorCooperativeLaunchTooLarge || ce == cudaErrorNotSupported || ce == cudaErrorLaunchOutOfResources) {
             // e.g. part of the GPU is held by another context: run the same kernel without the barrier
             cudaGetLastError();
             counter = nullptr;
-            if (int_acc) syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
-            else syrk_tiles_kernel<false><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
+            kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
         } else
             GB_CUDA(ce);
-    } else if (int_acc)
-        syrk_tiles_kernel<true><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
-    else
-        syrk_tiles_kernel<false><<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
+    } else
+        kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
     GB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -45,7 +45,10 @@ typedef enum {
      * cores (3x the SYRK work, twice the Z traffic).  Products are then exact to ~2^-22 relative, so A agrees
      * with the reference to FP32-accumulation accuracy (max|dA| ~1e-7).  The north-star's "TF32 mode for tighter
      * agreement": TF32 itself has FP16's 10-bit mantissa and would not be tighter than the default. */
-    GCTA_B200_FP16X2 = 2
+    GCTA_B200_FP16X2 = 2,
+    /* 8-bit E4M3 0/1 indicators: only for gcta_b200_nonmiss_matrix + gcta_b200_count_tiles (the N pass), where the
+     * tensor cores run kind::f8f6f4 at twice the 16-bit rate on half the bytes; counts stay exact. */
+    GCTA_B200_E4M3 = 3
 } gcta_b200_operand;
 
 /* ------------------------------------------------------------------------------------------

@@ -296,6 +296,18 @@ def test_diag_planes_paircount_finalize():
             abi.call("gcta_b200_count_tiles", ptr(OK), I64(ldm), I64(r["kc_pad"]), I32(operand), ptr(d_tiles), I64(len(tiles)), ptr(Nt2), stream())
         Nd2 = s_tiles_to_dense(Nt2.cpu().numpy(), tiles, ldm)
         assert np.array_equal(Nd2[ii, jj], 2 * Nref[ii, jj])
+    # the same counts from 8-bit E4M3 indicators (kind::f8f6f4, K block 128)
+    E4M3 = 3
+    kp8 = (m + 127) // 128 * 128
+    OK8 = torch.full((kp8, ldm), 7, dtype=torch.uint8, device="cuda")
+    abi.call("gcta_b200_nonmiss_matrix", ptr(r["d_bed"]), I64(r["pitch"]), I64(n), P(None), I64(n), P(None), I64(0), I64(m),
+             I32(E4M3), ptr(OK8), I64(ldm), stream())
+    ok8 = OK8.cpu().numpy()
+    assert np.array_equal(ok8[:m, :n], ok.astype(np.uint8) * 0x38) and not ok8[m:].any() and not ok8[:, n:].any()
+    Nt8 = torch.zeros_like(Nt)
+    for _ in range(2):
+        abi.call("gcta_b200_count_tiles", ptr(OK8), I64(ldm), I64(kp8), I32(E4M3), ptr(d_tiles), I64(len(tiles)), ptr(Nt8), stream())
+    assert np.array_equal(s_tiles_to_dense(Nt8.cpu().numpy(), tiles, ldm)[ii, jj], 2 * Nref[ii, jj])
     # K2 + K4
     S, _ = run_syrk(r["Z"].view(torch.float16), n, abi.FP16)
     A = torch.zeros(n * (n + 1) // 2, dtype=torch.float32, device="cuda")
