@@ -168,6 +168,39 @@ def test_row_bands_on_the_wide_row_decode_path(with_keep):
     check_grm(A[idx], N[idx], Aref[ii, jj], Nref[ii, jj])
 
 
+@pytest.mark.parametrize("seed", range(12))
+def test_randomised_shapes_against_the_oracle(seed):
+    """Seeded random sweep over the corners the fixed cases do not pin: n around multiples of 256 / 512, M not a
+    multiple of the 64 / 128-SNP K blocks, random keep / include lists, chunk sizes that split M unevenly, missing
+    rates from 0 to 30 %, alg 0 / 1, X chromosome, 1-3 row bands.  N exact, A within the north-star tolerance."""
+    rng = np.random.default_rng(1000 + seed)
+    n_file = int(rng.choice([255, 256, 257, 300, 511, 512, 513, 640, 769, 1030]))
+    m_file = int(rng.integers(70, 900))
+    miss = float(rng.choice([0.0, 0.0, 0.01, 0.1, 0.3]))
+    bed = synth.make_bed_payload(500 + seed, n_file, m_file, miss_rate=miss)
+    keep = include = None
+    if rng.random() < 0.5:
+        keep = np.sort(rng.choice(n_file, int(rng.integers(n_file // 2, n_file)), replace=False)).astype(np.int32)
+    if rng.random() < 0.5:
+        include = np.sort(rng.choice(m_file, int(rng.integers(m_file // 2, m_file)), replace=False)).astype(np.int32)
+    xchr = int(rng.random() < 0.25)
+    alg = int(rng.random() < 0.3)
+    sex = rng.integers(1, 3, size=n_file).astype(np.int32)
+    chunk = int(rng.choice([0, 64, 128, 192, 320]))
+    world = int(rng.choice([1, 1, 2, 3]))
+    n = n_file if keep is None else len(keep)
+    A = np.full(n * (n + 1) // 2, np.nan, dtype=np.float32)
+    N = np.full(n * (n + 1) // 2, -1, dtype=np.int32)
+    for r in range(world):
+        with abi.Plan(n_file, m_file, keep=keep, include=include, sex=sex, xchr=xchr, alg=alg, chunk_snps=chunk,
+                      part_rank=r, part_world=world) as p:
+            p.upload(bed)
+            p.run()
+            p.download(A, N)
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n_file, keep=keep, include=include, sex=sex, xchr=xchr, alg=alg)
+    check_grm(A, N, pack_lower(Aref), pack_lower(Nref))
+
+
 def test_split_fp16_operand_mode_is_tighter():
     """GCTA_B200_FP16X2 (hi + lo planes, three tensor passes): agreement with the reference at FP32-accumulation
     level, an order of magnitude tighter than plain FP16 operands; several chunks and missing data."""
