@@ -130,8 +130,11 @@ static void option(int argc, char* argv_in[])
     else throw("Error: no analysis has been launched by the option(s).\n");
 }
 
+int gcta_host_selftest_format();   // gcta_host_grm.cpp
+
 int main(int argc, char* argv[])
 {
+    if (argc == 2 && strcmp(argv[1], "--selftest-format") == 0) return gcta_host_selftest_format();
     cout << "*******************************************************************" << endl;
     cout << "* Genome-wide Complex Trait Analysis (GCTA)" << endl;
     cout << "* version 0.93.9 - B200 build of the --make-grm path (" << gcta_b200_version() << ")" << endl;

@@ -43,6 +43,13 @@ def test_binary_is_built():
     assert os.access(BIN, os.X_OK), "python -m gcta_b200.build builds gcta_b200/gcta64_b200"
 
 
+def test_fast_number_formatter_equals_printf():
+    """The .grm.gz writer formats n(n+1)/2 lines with its own %.6e routine; the binary checks it against snprintf
+    on 4.5 million values (float-valued like A, 7-digit decimals, specials)."""
+    r = subprocess.run([BIN, "--selftest-format"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=120)
+    assert r.returncode == 0 and "0 mismatches" in r.stdout, r.stdout + r.stderr
+
+
 @pytest.mark.parametrize("case,args,log", [
     ("g8_errors", ["--bfile", "t", "--make-grm", "--out", "o"], "ref_stdout_o.txt"),                # chr 23 without --autosome
     ("g8_errors", ["--bfile", "missing_prefix", "--make-grm", "--out", "o2"], "ref_stdout_o2.txt"),  # cannot open .fam
