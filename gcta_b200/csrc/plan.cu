@@ -216,6 +216,10 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     p->pitch = round_up(p->stride, 16);
     p->ldz = round_up(n, TILE_N);
     p->xchr = a->xchr; p->alg = a->alg; p->operand = a->operand; p->device = a->device;
+    // Rounding errors of 16-bit operands average out like 1/sqrt(M); with few SNPs they do not (a single FP16 product
+    // is only good to ~1e-3 relative and A_ij is then O(1)).  Short contractions therefore use the split-FP16 mode,
+    // which costs nothing measurable at these sizes and keeps max|dA| <= 1e-3 for any M.
+    if (p->operand == GCTA_B200_FP16 && m < 8192) p->operand = GCTA_B200_FP16X2;
     p->has_keep = a->keep != nullptr && !(n == a->n_file);
     p->has_include = a->include != nullptr;
     p->has_mu = a->mu != nullptr;
@@ -303,7 +307,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         int64_t zcap = 16ll << 30;
         if (const char* e = getenv("GCTA_B200_ZCAP_GIB")) zcap = std::max<int64_t>(1, atoll(e)) << 30;
         int64_t budget = std::min<int64_t>((int64_t)(free_b / 4), zcap);
-        const int planes = a->operand == GCTA_B200_FP16X2 ? 2 : 1;   // split mode keeps a residual plane behind the first
+        const int planes = p->operand == GCTA_B200_FP16X2 ? 2 : 1;   // split mode keeps a residual plane behind the first
         int64_t kc = a->chunk_snps > 0 ? a->chunk_snps : budget / (p->ldz * 2 * planes);
         kc = std::max<int64_t>(64, kc / 64 * 64);
         kc = std::min<int64_t>(kc, round_up(m, 64));

@@ -39,7 +39,8 @@ typedef enum {
 
 /* operand type of the standardised genotypes fed to the tensor cores (FP32 accumulate). */
 typedef enum {
-    GCTA_B200_FP16 = 0, /* default: 11-bit significand, |z| <= 65504 (MAF >= 1e-9) */
+    GCTA_B200_FP16 = 0, /* default: 11-bit significand, |z| <= 65504 (MAF >= 1e-9); with fewer than 8192 included
+                           SNPs the plan upgrades it to GCTA_B200_FP16X2 (rounding no longer averages out) */
     GCTA_B200_BF16 = 1,
     /* "tight" mode: z = hi + lo with hi = fp16(z), lo = fp16(z - hi); S = hi'hi + hi'lo + lo'hi on the tensor
      * cores (3x the SYRK work, twice the Z traffic).  Products are then exact to ~2^-22 relative, so A agrees

@@ -180,6 +180,62 @@ def test_reference_reader_accepts_our_multi_member_gz(tmp_path):
     assert np.array_equal(N, N2) and np.abs(A - A2).max() <= 1e-6 * max(1.0, np.abs(A).max())
 
 
+def _flag_dataset(d):
+    """n=90, M=400 with chromosomes 1..23 mixed, both sexes, 3 % missing, plus the list files the flags need."""
+    from gcta_b200 import synth
+    n, m = 90, 400
+    rng = np.random.default_rng(77)
+    chrom = rng.integers(1, 24, size=m)
+    sex = rng.integers(1, 3, size=n)
+    synth.write_plink(str(d / "t"), synth.make_bed_payload(77, n, m, miss_rate=0.03), n, chrom=chrom, sex=sex)
+    open(d / "remove.txt", "w").write("".join(f"F{i} I{i}\n" for i in range(0, n, 7)))
+    open(d / "keep.txt", "w").write("".join(f"F{i} I{i} extra columns ignored\n" for i in range(0, n, 2)))
+    open(d / "exclude.txt", "w").write("".join(f"rs{k}\n" for k in range(0, m, 5)))
+    open(d / "sex.txt", "w").write("".join(f"F{i} I{i} {'M' if i % 3 else 'F'}\n" for i in range(n)))
+    open(d / "refA.txt", "w").write("".join(f"rs{k} {'G' if k % 2 else 'A'}\n" for k in range(m)))
+    return n, m
+
+
+FLAG_SETS = [
+    ["--autosome", "--remove", "remove.txt", "--exclude", "exclude.txt", "--make-grm"],
+    ["--chr", "3", "--make-grm"],
+    ["--autosome", "--keep", "keep.txt", "--remove", "remove.txt", "--make-grm"],
+    ["--autosome", "--exclude-snp", "rs7", "--max-maf", "0.3", "--make-grm"],
+    ["--extract-snp", "rs5", "--autosome-num", "23", "--make-grm"],
+    ["--update-sex", "sex.txt", "--make-grm-xchr"],
+    ["--autosome", "--update-ref-allele", "refA.txt", "--make-grm"],
+    ["--autosome", "--update-ref-allele", "refA.txt", "--freq"],
+    ["--autosome-num", "10", "--make-grm"],                     # chromosomes above 10 -> "autosomal SNPs only" error
+    ["--autosome", "--maf", "0.05", "--grm-alg", "1", "--make-grm"],
+    ["--make-grm-xchr"],                                        # autosomal data is filtered to chr 23 first (option.cpp:571)
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
+@pytest.mark.parametrize("flags", FLAG_SETS, ids=[" ".join(f) for f in FLAG_SETS])
+def test_cli_flags_live_against_the_reference(flags, tmp_path):
+    """Same command line through the compiled reference and through gcta64_b200: stderr, log lines, .grm.id, .freq
+    identical; N identical; A within tolerance."""
+    _flag_dataset(tmp_path)
+    rr = oracle.run_ref(["--bfile", "t"] + flags + ["--out", "ref"], cwd=tmp_path)
+    rm = run_cli(["--bfile", "t"] + flags + ["--out", "mine"], tmp_path)
+    assert rm.stderr.strip() == rr.stderr.strip()
+    ours = [ln.replace("[mine.", "[X.") for ln in body(rm.stdout) if not ln.startswith("--out")]
+    theirs = [ln.replace("[ref.", "[X.") for ln in body(rr.stdout) if not ln.startswith("--out")]
+    if not rr.stderr.strip():
+        assert ours == theirs
+    if os.path.exists(tmp_path / "ref.grm.gz"):
+        A, N, _ = grmio.read_grm_gz(str(tmp_path / "mine.grm.gz"))
+        Aref, Nref, _ = grmio.read_grm_gz(str(tmp_path / "ref.grm.gz"))
+        check_grm(A, N, Aref, Nref)   # also with M = 1 or 17 SNPs: short contractions run in the split-FP16 mode
+        assert open(tmp_path / "mine.grm.id").read() == open(tmp_path / "ref.grm.id").read()
+    else:
+        assert not os.path.exists(tmp_path / "mine.grm.gz")
+    if os.path.exists(tmp_path / "ref.freq"):
+        assert open(tmp_path / "mine.freq").read() == open(tmp_path / "ref.freq").read()
+
+
 @pytest.mark.gpu
 def test_cli_two_gpus_when_present(tmp_path):
     """--gpus 2: one host thread per GPU, each computing its row band into the shared host buffers."""
