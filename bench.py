@@ -194,9 +194,9 @@ def main_ours(a, rank, world, local_rank):
         e2e_steps = max(1, min(a.steps, a.e2e_steps))
         if world == 1:
             def e2e_step():
-                plan.run_streamed(h_bed.data_ptr())   # H2D of chunk c+1 overlaps the compute of chunk c
-                plan.download(A_ptr, N_ptr)
-            api = "gcta_b200_plan_run_streamed + plan_download (what gcta_b200_make_grm does), pinned host buffers"
+                # H2D of chunk c+1 overlaps the compute of chunk c; finalize + D2H overlap the last chunk's SYRK
+                plan.run_to_host(h_bed.data_ptr(), A_ptr, N_ptr)
+            api = "gcta_b200_plan_run_to_host (what gcta_b200_make_grm runs: upload, compute and download pipelined), pinned host buffers"
             h2d = stride * m
         else:
             # every rank pulls 1/N of the SNP rows over its own PCIe link, the ranks all-gather the packed rows over

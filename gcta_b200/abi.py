@@ -22,7 +22,7 @@ EXPORTS = [
     "gcta_b200_bed_decode", "gcta_b200_diag_accum", "gcta_b200_diag_accum_static", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles",
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
     "gcta_b200_partition", "gcta_b200_tile_list", "gcta_b200_allele_counts", "gcta_b200_nonmiss_matrix", "gcta_b200_count_tiles",
-    "gcta_b200_plan_use_device_bed", "gcta_b200_plan_upload_rows",
+    "gcta_b200_plan_use_device_bed", "gcta_b200_plan_upload_rows", "gcta_b200_plan_run_to_host",
 ]
 
 
@@ -189,6 +189,13 @@ class Plan:
         """upload + run with the host->HBM copy of chunk c+1 hidden behind the compute of chunk c"""
         err = C.create_string_buffer(ERRCAP)
         _check(lib().gcta_b200_plan_run_streamed(self._h, C.c_void_p(_ptr(bed_host)), C.byref(self.out), err, ERRCAP), err)
+        return self.out
+
+    def run_to_host(self, bed_host, A_lower, N_lower=None, mu=None):
+        """upload + run + download, all pipelined (what gcta_b200_make_grm runs)"""
+        self.out.A_lower, self.out.N_lower, self.out.mu_out = _ptr(A_lower), _ptr(N_lower), _ptr(mu)
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_plan_run_to_host(self._h, C.c_void_p(_ptr(bed_host)), C.byref(self.out), err, ERRCAP), err)
         return self.out
 
     def download(self, A_lower, N_lower=None, mu=None):

@@ -127,7 +127,8 @@ struct gcta_b200_plan {
     // device
     cudaStream_t stream = nullptr, stream2 = nullptr, stream_copy = nullptr;
     std::vector<cudaEvent_t> upload_events;
-    std::vector<int32_t> h_include;
+    std::vector<int32_t> h_include, h_tiles;
+    bool downloaded = false;   // the last run already streamed A (and filled N) into the caller's buffers
     int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
     uint8_t* d_bed = nullptr;
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
@@ -289,6 +290,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         std::vector<int32_t> tl((size_t)p->ntiles * 2 + 2);
         gcta_b200_tile_list(n, p->row_begin, p->row_end, tl.data());
         PLAN_CUDA(cudaMemcpy(p->d_tiles, tl.data(), (size_t)p->ntiles * 8, cudaMemcpyHostToDevice));
+        p->h_tiles.assign(tl.begin(), tl.begin() + p->ntiles * 2);
         // GCTA_B200_2CTA=1: run K2 as CTA pairs (tcgen05.mma.cta_group::2, syrk2.cu) over the same tile storage
         if (getenv("GCTA_B200_2CTA") && atoi(getenv("GCTA_B200_2CTA")) > 0 && p->ntiles > 0) {
             p->npairs = gcta_b200_pair_list(tl.data(), p->ntiles, raster_rows(), nullptr);
@@ -422,12 +424,80 @@ extern "C" int gcta_b200_plan_synth(gcta_b200_plan* p, uint64_t seed, const uint
     return 0;
 }
 
+// Last SNP chunk of a run whose results go straight to host buffers and in which nothing is missing: the tile list
+// is cut at raster-group boundaries into a few segments; each segment's SYRK is followed by its own finalize and an
+// asynchronous device->host copy of its rows on the copy stream, so the download of A hides behind the remaining
+// tensor work, and N (== m everywhere) is filled on the host meanwhile.
+static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp, gcta_b200_out* out, cudaStream_t st, int* launches,
+                                    char* err, size_t errcap)
+{
+    using namespace gb;
+    if (!p->stream_copy) GB_CUDA(cudaStreamCreateWithFlags(&p->stream_copy, cudaStreamNonBlocking));
+    const int64_t band_base = p->row_begin * (p->row_begin + 1) / 2;
+    std::vector<std::thread> fill;
+    if (out->N_lower) {
+        const int nt = (int)std::min<int64_t>(16, std::max<int64_t>(1, p->band_count >> 22));
+        int32_t* dst = out->N_lower + band_base;
+        const int32_t mval = (int32_t)p->m;
+        const int64_t cnt = p->band_count;
+        for (int t = 0; t < nt; t++)
+            fill.emplace_back([=]() { std::fill(dst + cnt * t / nt, dst + cnt * (t + 1) / nt, mval); });
+    }
+    // segment boundaries: tile indices where a new raster group of row blocks starts
+    const int R = raster_rows();
+    const int64_t b0 = p->row_begin / TILE_M;
+    std::vector<int64_t> gstart;   // first tile index of each group
+    int64_t last_g = -1;
+    for (int64_t t = 0; t < p->ntiles; t++) {
+        const int64_t g = (p->h_tiles[2 * t] - b0) / R;
+        if (g != last_g) { gstart.push_back(t); last_g = g; }
+    }
+    gstart.push_back(p->ntiles);
+    const int ngroups = (int)gstart.size() - 1;
+    const int nseg = std::min(8, ngroups);
+    std::vector<cudaEvent_t> evs;
+    int rc = 0;
+    int gi = 0;
+    for (int s = 0; s < nseg && !rc; s++) {
+        // groups [gi, ge): about 1/nseg of the tiles each
+        const int64_t want = p->ntiles * (s + 1) / nseg;
+        int ge = gi + 1;
+        while (ge < ngroups && (s == nseg - 1 || gstart[ge] < want)) ge++;
+        if (s == nseg - 1) ge = ngroups;
+        const int64_t t0 = gstart[gi], t1 = gstart[ge];
+        const int64_t r0 = (b0 + (int64_t)gi * R) * TILE_M, r1 = std::min<int64_t>((b0 + (int64_t)ge * R) * TILE_M, p->row_end);
+        gi = ge;
+        if (t1 <= t0) continue;
+        rc = gcta_b200_syrk_tiles_ab(Z, Z, p->ldz, kp, p->operand, p->d_tiles + 2 * t0, t1 - t0, p->d_S + t0 * (TILE_M * TILE_N), st, err, errcap);
+        if (rc) break;
+        const int64_t seg_base = r0 * (r0 + 1) / 2, seg_cnt = r1 * (r1 + 1) / 2 - seg_base;
+        rc = gcta_b200_finalize_tiles(p->d_S + t0 * (TILE_M * TILE_N), nullptr, (int32_t)p->m, p->d_tiles + 2 * t0, t1 - t0, p->n, p->d_keep, p->d_diag,
+                                      p->d_nii, r0, r1, p->d_A_lower + (seg_base - band_base), nullptr, st, err, errcap);
+        if (rc) break;
+        *launches += 2;
+        cudaEvent_t ev;
+        cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        if (e == cudaSuccess) { evs.push_back(ev); e = cudaEventRecord(ev, st); }
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(p->stream_copy, ev, 0);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(out->A_lower + seg_base, p->d_A_lower + (seg_base - band_base), (size_t)seg_cnt * 4, cudaMemcpyDeviceToHost, p->stream_copy);
+        if (e != cudaSuccess) rc = set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed in the pipelined download: ") + cudaGetErrorString(e));
+    }
+    cudaError_t e2 = cudaStreamSynchronize(p->stream_copy);
+    for (auto& t : fill) t.join();
+    for (cudaEvent_t ev : evs) cudaEventDestroy(ev);
+    if (!rc && e2 != cudaSuccess) rc = set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed: ") + cudaGetErrorString(e2));
+    return rc;
+}
+
 // plan_run and plan_run_streamed.  With bed_host != NULL the packed rows of chunk c+1 travel host -> HBM on the
 // copy stream while chunk c is standardised and contracted, so the upload hides behind the tensor work.
-static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap)
+static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_out* out, bool to_host, char* err, size_t errcap)
 {
     using namespace gb;
     GB_ARG(p && out, "plan_run: null argument");
+    p->downloaded = false;
+    bool pipelined = false;
     GB_CUDA(cudaSetDevice(p->device));
     std::vector<cudaEvent_t>& up = p->upload_events;
     const int64_t nch_up = (p->m + p->chunk - 1) / p->chunk;
@@ -502,7 +572,16 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         GB_CUDA(cudaEventRecord(EV(c, 1), sd));
         GB_CUDA(cudaStreamWaitEvent(st, EV(c, 1), 0));
         GB_CUDA(cudaEventRecord(EV(c, 2), st));
-        if (p->operand == GCTA_B200_FP16X2) {
+        if (to_host && c == nchunks - 1 && out->A_lower && p->operand != GCTA_B200_FP16X2 && !p->d_pairs && p->alg == 0 && p->ntiles > 0) {
+            // results go to host buffers: if nothing is missing, pipeline finalize + download behind this last SYRK
+            unsigned long long tmq = 1;
+            GB_CUDA(cudaMemcpyAsync(&tmq, p->d_total_missing, 8, cudaMemcpyDeviceToHost, sd));
+            GB_CUDA(cudaStreamSynchronize(sd));
+            pipelined = tmq == 0;
+        }
+        if (pipelined) {
+            rc = run_last_chunk_pipelined(p, Z, round_up(kc, 64), out, st, &launches, err, errcap);
+        } else if (p->operand == GCTA_B200_FP16X2) {
             // z = hi + lo: S += hi'hi + hi'lo + lo'hi (lo'lo ~ 2^-22 z^2 is dropped)
             const int64_t kp = round_up(kc, 64);
             const uint16_t* hi = (const uint16_t*)Z;
@@ -594,7 +673,8 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         }
     }
     GB_CUDA(cudaEventRecord(p->events[e_pc], st));
-    {
+    if (pipelined) p->downloaded = true;   // A is on the host already, N filled
+    else {
         int rc = gcta_b200_finalize_tiles_ex(p->d_S, tm > 0 ? p->d_Ntiles : nullptr, (int32_t)p->m, (p->alg == 1 && tm > 0) ? p->d_Dtiles : nullptr,
                                              d_const, p->alg == 1 ? p->d_dw : nullptr, p->d_tiles, p->ntiles, p->n, p->d_keep,
                                              p->d_diag, p->d_nii, p->row_begin, p->row_end, p->d_A_lower, tm > 0 ? p->d_N_lower : nullptr, st, err, errcap);
@@ -625,14 +705,23 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
 
 extern "C" int gcta_b200_plan_run(gcta_b200_plan* p, gcta_b200_out* out, char* err, size_t errcap)
 {
-    return plan_run_impl(p, nullptr, out, err, errcap);
+    return plan_run_impl(p, nullptr, out, false, err, errcap);
 }
 
 extern "C" int gcta_b200_plan_run_streamed(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap)
 {
     using namespace gb;
     GB_ARG(bed_host, "plan_run_streamed: null bed");
-    return plan_run_impl(p, bed_host, out, err, errcap);
+    return plan_run_impl(p, bed_host, out, false, err, errcap);
+}
+
+extern "C" int gcta_b200_plan_run_to_host(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(bed_host && out && out->A_lower, "plan_run_to_host: null argument");
+    int rc = plan_run_impl(p, bed_host, out, true, err, errcap);
+    if (!rc) rc = gcta_b200_plan_download(p, out, err, errcap);   // whatever the pipelined path has not delivered yet
+    return rc;
 }
 
 extern "C" int gcta_b200_plan_device_results(gcta_b200_plan* p, const float** dA, const int32_t** dN, int64_t* count)
@@ -651,11 +740,12 @@ extern "C" int gcta_b200_plan_download(gcta_b200_plan* p, gcta_b200_out* out, ch
     GB_ARG(p->ran, "plan_download: plan_run has not completed");
     GB_CUDA(cudaSetDevice(p->device));
     const int64_t base = p->row_begin * (p->row_begin + 1) / 2;
-    GB_CUDA(cudaMemcpyAsync(out->A_lower + base, p->d_A_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
+    const bool have = p->downloaded;   // plan_run_to_host already delivered A and N behind the last SYRK
+    if (!have) GB_CUDA(cudaMemcpyAsync(out->A_lower + base, p->d_A_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
     if (out->N_lower && p->total_missing > 0)
         GB_CUDA(cudaMemcpyAsync(out->N_lower + base, p->d_N_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
     if (out->mu_out) GB_CUDA(cudaMemcpyAsync(out->mu_out, p->d_mu, (size_t)p->m * 8, cudaMemcpyDeviceToHost, p->stream));
-    if (out->N_lower && p->total_missing == 0) {
+    if (out->N_lower && p->total_missing == 0 && !have) {
         // nothing missing: N_ij == m for every pair (what grm.cpp:291 yields); fill on the host while the copies run
         const int nt = (int)std::min<int64_t>(16, std::max<int64_t>(1, p->band_count >> 22));
         std::vector<std::thread> th;
@@ -686,9 +776,9 @@ extern "C" int gcta_b200_make_grm(const gcta_b200_args* a, gcta_b200_out* out, c
     cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2); cudaEventCreate(&e3);
     cudaEventRecord(e0, p->stream);
     cudaEventRecord(e1, p->stream);   // the upload is streamed chunk by chunk inside the run (ms_h2d ~ 0)
-    if (!rc) rc = gcta_b200_plan_run_streamed(p, a->bed, out, err, errcap);
+    // upload, compute and download pipelined: plan_run_to_host
+    if (!rc) rc = gcta_b200_plan_run_to_host(p, a->bed, out, err, errcap);
     cudaEventRecord(e2, p->stream);
-    if (!rc) rc = gcta_b200_plan_download(p, out, err, errcap);
     cudaEventRecord(e3, p->stream);
     cudaEventSynchronize(e3);
     if (!rc) {

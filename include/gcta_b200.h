@@ -131,6 +131,10 @@ int gcta_b200_plan_run(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size
  * copy stream while chunk c is standardised and contracted (use pinned host memory for full overlap).  This is what
  * gcta_b200_make_grm runs. */
 int gcta_b200_plan_run_streamed(gcta_b200_plan* plan, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap);
+/* plan_run_streamed + plan_download in one call with the download pipelined too: when nothing is missing, the last
+ * SNP chunk is contracted in a few segments, each followed by its finalize and an asynchronous device->host copy of
+ * its rows, so A reaches out->A_lower (and N == m is filled on the host) behind the remaining tensor work. */
+int gcta_b200_plan_run_to_host(gcta_b200_plan* plan, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap);
 /* copy this plan's row band of A (and N when N_lower != NULL) to host memory */
 int gcta_b200_plan_download(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size_t errcap);
 /* device pointers of the finalised band (float A, int32 N; N is NULL when nothing is missing

@@ -201,6 +201,31 @@ def test_randomised_shapes_against_the_oracle(seed):
     check_grm(A, N, pack_lower(Aref), pack_lower(Nref))
 
 
+@pytest.mark.parametrize("n,world", [(7000, 1), (9000, 2)])
+def test_pipelined_download_equals_plain_download(n, world):
+    """plan_run_to_host cuts the last chunk into segments (3-4 raster groups here) and streams each segment's rows to
+    the host behind the remaining SYRK work; the result must be the very same bytes as run + download."""
+    m = 9000   # above the 8192-SNP threshold, so the single-plane FP16 path (the pipelined one) is taken
+    bed = synth.make_bed_payload(33, n, m)
+    tri = n * (n + 1) // 2
+    A0 = np.full(tri, np.nan, dtype=np.float32); N0 = np.full(tri, -1, dtype=np.int32)
+    A1 = np.full(tri, np.nan, dtype=np.float32); N1 = np.full(tri, -1, dtype=np.int32)
+    for r in range(world):
+        with abi.Plan(n, m, chunk_snps=4096, part_rank=r, part_world=world) as p:
+            p.upload(bed)
+            p.run()
+            p.download(A0, N0)
+        with abi.Plan(n, m, chunk_snps=4096, part_rank=r, part_world=world) as p:
+            o = p.run_to_host(bed, A1, N1)
+            assert o.total_missing == 0
+    assert np.array_equal(A0, A1) and np.array_equal(N0, N1) and (N1 == m).all()
+    sub = np.sort(np.random.default_rng(8).choice(n, 200, replace=False))
+    Aref, Nref, _ = oracle.make_grm_numpy(bed[:, :], n, keep=sub, mu=oracle.snp_mu(bed, n)[0])
+    ii, jj = np.tril_indices(len(sub))
+    idx = sub[ii].astype(np.int64) * (sub[ii] + 1) // 2 + sub[jj]
+    check_grm(A1[idx], N1[idx], Aref[ii, jj], Nref[ii, jj])
+
+
 def test_split_fp16_operand_mode_is_tighter():
     """GCTA_B200_FP16X2 (hi + lo planes, three tensor passes): agreement with the reference at FP32-accumulation
     level, an order of magnitude tighter than plain FP16 operands; several chunks and missing data."""
