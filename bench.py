@@ -213,10 +213,9 @@ def main_ours(a, rank, world, local_rank):
                 plan.upload_rows(h_bed.data_ptr(), r0, r1)
                 tdist.all_gather_into_tensor(d_all, mine)
                 torch.cuda.synchronize()
-                plan.run()
-                plan.download(A_ptr, N_ptr)
+                plan.run_to_host(None, A_ptr, N_ptr)   # genotypes resident after the all-gather; finalize + D2H pipelined
             api = ("gcta_b200_plan_upload_rows (1/N of the rows per rank) + NCCL all-gather of the packed rows over NVLink + "
-                   "plan_run + plan_download, pinned host buffers")
+                   "plan_run_to_host (finalize + download pipelined behind the last SYRK), pinned host buffers")
             h2d = stride * (r1 - r0)
         e2e_step()
         barrier()

@@ -718,7 +718,7 @@ extern "C" int gcta_b200_plan_run_streamed(gcta_b200_plan* p, const uint8_t* bed
 extern "C" int gcta_b200_plan_run_to_host(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap)
 {
     using namespace gb;
-    GB_ARG(bed_host && out && out->A_lower, "plan_run_to_host: null argument");
+    GB_ARG(out && out->A_lower, "plan_run_to_host: null argument");   // bed_host == NULL: genotypes already resident
     int rc = plan_run_impl(p, bed_host, out, true, err, errcap);
     if (!rc) rc = gcta_b200_plan_download(p, out, err, errcap);   // whatever the pipelined path has not delivered yet
     return rc;

@@ -133,7 +133,8 @@ int gcta_b200_plan_run(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size
 int gcta_b200_plan_run_streamed(gcta_b200_plan* plan, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap);
 /* plan_run_streamed + plan_download in one call with the download pipelined too: when nothing is missing, the last
  * SNP chunk is contracted in a few segments, each followed by its finalize and an asynchronous device->host copy of
- * its rows, so A reaches out->A_lower (and N == m is filled on the host) behind the remaining tensor work. */
+ * its rows, so A reaches out->A_lower (and N == m is filled on the host) behind the remaining tensor work.
+ * bed_host == NULL: the genotypes are already resident (plan_upload / plan_upload_rows + all-gather). */
 int gcta_b200_plan_run_to_host(gcta_b200_plan* plan, const uint8_t* bed_host, gcta_b200_out* out, char* err, size_t errcap);
 /* copy this plan's row band of A (and N when N_lower != NULL) to host memory */
 int gcta_b200_plan_download(gcta_b200_plan* plan, gcta_b200_out* out, char* err, size_t errcap);
