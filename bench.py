@@ -202,6 +202,9 @@ def main_ours(a, rank, world, local_rank):
             # every rank pulls 1/N of the SNP rows over its own PCIe link, the ranks all-gather the packed rows over
             # NVLink (NCCL) into the buffer the plan reads, then each computes its row band
             import torch.distributed as tdist
+            # (A chunk-by-chunk version of this exchange - gcta_b200_plan_set_chunk_events, all-gather of chunk c+1 queued
+            # behind the compute of chunk c - hung twice on the 2-GPU box with NCCL 2.28.9 and is not used here; the event
+            # mechanism itself is covered on one GPU by tests/test_gpu_path.py.)
             rows_per = -(-m // world)
             pitch = plan.use_device_bed(None)
             d_all = torch.zeros(rows_per * world * pitch, dtype=torch.uint8, device="cuda")

@@ -176,6 +176,29 @@ class Plan:
         err = C.create_string_buffer(ERRCAP)
         _check(lib().gcta_b200_plan_upload_rows(self._h, C.c_void_p(_ptr(bed_host)), C.c_int64(row_begin), C.c_int64(row_end), err, ERRCAP), err)
 
+    def chunk_rows(self):
+        """[(row_begin, row_end)] of the file rows each SNP chunk reads"""
+        L = lib()
+        L.gcta_b200_plan_num_chunks.restype = C.c_int64
+        out = []
+        for c in range(L.gcta_b200_plan_num_chunks(self._h)):
+            b, e = C.c_int64(), C.c_int64()
+            if L.gcta_b200_plan_chunk_rows(self._h, C.c_int64(c), C.byref(b), C.byref(e)):
+                raise GctaB200Error(1, "bad chunk index")
+            out.append((b.value, e.value))
+        return out
+
+    def upload_rows_async(self, bed_host, row_begin, row_end, stream):
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_plan_upload_rows_async(self._h, C.c_void_p(_ptr(bed_host)), C.c_int64(row_begin), C.c_int64(row_end),
+                                                      C.c_void_p(stream), err, ERRCAP), err)
+
+    def set_chunk_events(self, events):
+        """events: list of raw cudaEvent_t handles (torch.cuda.Event.cuda_event), one per chunk; [] clears"""
+        arr = (C.c_void_p * max(1, len(events)))(*events)
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_plan_set_chunk_events(self._h, arr, C.c_int64(len(events)), err, ERRCAP), err)
+
     def download_bed(self, bed_host):
         err = C.create_string_buffer(ERRCAP)
         _check(lib().gcta_b200_plan_download_bed(self._h, C.c_void_p(_ptr(bed_host)), err, ERRCAP), err)

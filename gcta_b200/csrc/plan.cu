@@ -127,6 +127,7 @@ struct gcta_b200_plan {
     // device
     cudaStream_t stream = nullptr, stream2 = nullptr, stream_copy = nullptr;
     std::vector<cudaEvent_t> upload_events;
+    std::vector<cudaEvent_t> chunk_ready;   // caller-owned events: chunk c's packed rows are in place (plan_set_chunk_events)
     std::vector<int32_t> h_include, h_tiles;
     bool downloaded = false;   // the last run already streamed A (and filled N) into the caller's buffers
     int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
@@ -348,6 +349,46 @@ extern "C" int gcta_b200_plan_use_device_bed(gcta_b200_plan* p, void* d_bed, int
     return 0;
 }
 
+// ---- chunk-wise delivery of the packed rows by the caller (multi-GPU: upload 1/G + all-gather per chunk) ----
+extern "C" int64_t gcta_b200_plan_num_chunks(gcta_b200_plan* p) { return p ? (p->m + p->chunk - 1) / p->chunk : 0; }
+
+extern "C" int gcta_b200_plan_chunk_rows(gcta_b200_plan* p, int64_t c, int64_t* row_begin, int64_t* row_end)
+{
+    if (!p || c < 0 || c >= gcta_b200_plan_num_chunks(p) || !row_begin || !row_end) return GCTA_B200_ERR_ARG;
+    const int64_t k0 = c * p->chunk, k1 = std::min<int64_t>(p->m, k0 + p->chunk);
+    *row_begin = k0;
+    *row_end = k1;
+    if (p->has_include) {
+        *row_begin = *std::min_element(p->h_include.begin() + k0, p->h_include.begin() + k1);
+        *row_end = *std::max_element(p->h_include.begin() + k0, p->h_include.begin() + k1) + 1;
+    }
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_upload_rows_async(gcta_b200_plan* p, const uint8_t* bed_host, int64_t row_begin, int64_t row_end, void* stream,
+                                                char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && bed_host, "plan_upload_rows_async: null argument");
+    GB_ARG(row_begin >= 0 && row_begin <= row_end && row_end <= p->m_file, "plan_upload_rows_async: bad row range");
+    GB_CUDA(cudaSetDevice(p->device));
+    if (row_end > row_begin)
+        GB_CUDA(cudaMemcpy2DAsync(p->d_bed + row_begin * p->pitch, (size_t)p->pitch, bed_host + row_begin * p->stride, (size_t)p->stride,
+                                  (size_t)p->stride, (size_t)(row_end - row_begin), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_set_chunk_events(gcta_b200_plan* p, void* const* events, int64_t count, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(p && (events || count == 0), "plan_set_chunk_events: null argument");
+    GB_ARG(count == 0 || count == gcta_b200_plan_num_chunks(p), "plan_set_chunk_events: one event per SNP chunk (or none)");
+    for (int64_t i = 0; i < count; i++) GB_ARG(events[i], "plan_set_chunk_events: null event");
+    p->chunk_ready.clear();
+    for (int64_t i = 0; i < count; i++) p->chunk_ready.push_back((cudaEvent_t)events[i]);
+    return 0;
+}
+
 extern "C" int gcta_b200_plan_upload_rows(gcta_b200_plan* p, const uint8_t* bed_host, int64_t row_begin, int64_t row_end, char* err, size_t errcap)
 {
     using namespace gb;
@@ -559,6 +600,8 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         void* Z = (p->overlap && p->d_Zbuf[1]) ? p->d_Zbuf[c & 1] : p->d_Zbuf[0];
         if (c >= 2) GB_CUDA(cudaStreamWaitEvent(sd, EV(c - 2, 3), 0));   // the SYRK that last read this Z buffer
         if (bed_host) GB_CUDA(cudaStreamWaitEvent(sd, up[c], 0));        // this chunk's packed rows have landed
+        if (!bed_host && c < (int64_t)p->chunk_ready.size() && p->chunk_ready[c])   // ... or were delivered by the caller
+            GB_CUDA(cudaStreamWaitEvent(sd, p->chunk_ready[c], 0));                  // (e.g. an NVLink all-gather per chunk)
         GB_CUDA(cudaEventRecord(EV(c, 0), sd));
         int rc = gcta_b200_bed_decode_ex(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
                                          p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,

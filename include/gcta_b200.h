@@ -122,6 +122,16 @@ int gcta_b200_plan_synth(gcta_b200_plan* plan, uint64_t seed, const uint32_t* th
  * pitch.  plan_upload_rows copies host rows [row_begin,row_end) into whichever buffer the plan currently uses. */
 int gcta_b200_plan_use_device_bed(gcta_b200_plan* plan, void* d_bed, int64_t* pitch, char* err, size_t errcap);
 int gcta_b200_plan_upload_rows(gcta_b200_plan* plan, const uint8_t* bed_host, int64_t row_begin, int64_t row_end, char* err, size_t errcap);
+/* The same per SNP chunk, so that the exchange of chunk c+1 overlaps the compute of chunk c: plan_num_chunks /
+ * plan_chunk_rows give the file rows each chunk reads; plan_upload_rows_async copies rows on the caller's stream without
+ * synchronising; plan_set_chunk_events hands the plan one caller-owned cudaEvent_t per chunk (recorded after that
+ * chunk's rows are complete in the genotype buffer, e.g. after its all-gather) - plan_run / plan_run_to_host with
+ * bed_host == NULL then wait on event c before standardising chunk c.  count == 0 clears them. */
+int64_t gcta_b200_plan_num_chunks(gcta_b200_plan* plan);
+int gcta_b200_plan_chunk_rows(gcta_b200_plan* plan, int64_t chunk, int64_t* row_begin, int64_t* row_end);
+int gcta_b200_plan_upload_rows_async(gcta_b200_plan* plan, const uint8_t* bed_host, int64_t row_begin, int64_t row_end,
+                                     void* stream, char* err, size_t errcap);
+int gcta_b200_plan_set_chunk_events(gcta_b200_plan* plan, void* const* events, int64_t count, char* err, size_t errcap);
 /* inverse of plan_upload: copy the plan's HBM genotype buffer to host memory in .bed payload layout
  * (bench/test use: obtain the host copy of a device-generated data set) */
 int gcta_b200_plan_download_bed(gcta_b200_plan* plan, uint8_t* bed_host, char* err, size_t errcap);

@@ -226,6 +226,44 @@ def test_pipelined_download_equals_plain_download(n, world):
     check_grm(A1[idx], N1[idx], Aref[ii, jj], Nref[ii, jj])
 
 
+def test_chunk_events_gate_each_chunk_on_its_rows():
+    """plan_set_chunk_events: the caller fills the genotype buffer chunk by chunk on its own stream (late on purpose -
+    a long spin kernel goes first) and records one event per chunk; the plan must wait on event c before reading
+    chunk c, so the result equals the plain upload + run + download bytes."""
+    import torch
+    n, m = 1500, 13000
+    bed = synth.make_bed_payload(5, n, m, miss_rate=0.02)
+    tri = n * (n + 1) // 2
+    A0 = np.empty(tri, dtype=np.float32); N0 = np.empty(tri, dtype=np.int32)
+    A1 = np.full(tri, np.nan, dtype=np.float32); N1 = np.full(tri, -1, dtype=np.int32)
+    with abi.Plan(n, m, chunk_snps=4096) as p:
+        p.upload(bed); p.run(); p.download(A0, N0)
+    with abi.Plan(n, m, chunk_snps=4096) as p:
+        chunks = p.chunk_rows()
+        assert len(chunks) == 4 and chunks[0][0] == 0 and chunks[-1][1] == m
+        assert all(a[1] == b[0] for a, b in zip(chunks, chunks[1:]))
+        pitch = p.use_device_bed(None)
+        d_bed = torch.zeros(m * pitch, dtype=torch.uint8, device="cuda")
+        p.use_device_bed(d_bed.data_ptr())
+        h = torch.from_numpy(bed).pin_memory()
+        side = torch.cuda.Stream()
+        events = [torch.cuda.Event() for _ in chunks]
+        torch.cuda.synchronize()
+        with torch.cuda.stream(side):
+            torch.cuda._sleep(400_000_000)   # ~0.2 s: the plan is launched long before the rows arrive
+            for ev, (c0, c1) in zip(events, chunks):
+                p.upload_rows_async(h.data_ptr(), c0, c1, side.cuda_stream)
+                ev.record(side)
+        p.set_chunk_events([ev.cuda_event for ev in events])
+        p.run_to_host(None, A1, N1)
+        p.set_chunk_events([])
+        side.synchronize()
+    assert np.array_equal(N0, N1) and np.array_equal(A0, A1)
+    with abi.Plan(n, m, chunk_snps=4096) as p:
+        with pytest.raises(abi.GctaB200Error):
+            p.set_chunk_events([0, 0])   # count must be 0 or the number of chunks
+
+
 def test_split_fp16_operand_mode_is_tighter():
     """GCTA_B200_FP16X2 (hi + lo planes, three tensor passes): agreement with the reference at FP32-accumulation
     level, an order of magnitude tighter than plain FP16 operands; several chunks and missing data."""
