@@ -192,6 +192,7 @@ def main_ours(a, rank, world, local_rank):
         A_ptr = h_A.data_ptr() - 4 * base  # the ABI indexes the whole packed triangle; only the band is touched
         N_ptr = h_N.ctypes.data - 4 * base
         e2e_steps = max(1, min(a.steps, a.e2e_steps))
+        ex = None
         if world == 1:
             def e2e_step():
                 # H2D of chunk c+1 overlaps the compute of chunk c; finalize + D2H overlap the last chunk's SYRK
@@ -199,27 +200,50 @@ def main_ours(a, rank, world, local_rank):
             api = "gcta_b200_plan_run_to_host (what gcta_b200_make_grm runs: upload, compute and download pipelined), pinned host buffers"
             h2d = stride * m
         else:
-            # every rank pulls 1/N of the SNP rows over its own PCIe link, the ranks all-gather the packed rows over
-            # NVLink (NCCL) into the buffer the plan reads, then each computes its row band
             import torch.distributed as tdist
-            # (A chunk-by-chunk version of this exchange - gcta_b200_plan_set_chunk_events, all-gather of chunk c+1 queued
-            # behind the compute of chunk c - hung twice on the 2-GPU box with NCCL 2.28.9 and is not used here; the event
-            # mechanism itself is covered on one GPU by tests/test_gpu_path.py.)
-            rows_per = -(-m // world)
-            pitch = plan.use_device_bed(None)
-            d_all = torch.zeros(rows_per * world * pitch, dtype=torch.uint8, device="cuda")
-            plan.use_device_bed(d_all.data_ptr())
-            r0, r1 = min(m, rank * rows_per), min(m, (rank + 1) * rows_per)
-            mine = d_all[rank * rows_per * pitch:(rank + 1) * rows_per * pitch]
+            if os.environ.get("GCTA_B200_E2E_EXCHANGE", "peer") == "nccl":
+                # every rank pulls 1/N of the SNP rows over its own PCIe link, one NCCL all-gather of the packed rows over
+                # NVLink into the buffer the plan reads, then each computes its row band (nothing overlaps the exchange)
+                rows_per = -(-m // world)
+                pitch = plan.use_device_bed(None)
+                d_all = torch.zeros(rows_per * world * pitch, dtype=torch.uint8, device="cuda")
+                plan.use_device_bed(d_all.data_ptr())
+                r0, r1 = min(m, rank * rows_per), min(m, (rank + 1) * rows_per)
+                mine = d_all[rank * rows_per * pitch:(rank + 1) * rows_per * pitch]
 
-            def e2e_step():
-                plan.upload_rows(h_bed.data_ptr(), r0, r1)
-                tdist.all_gather_into_tensor(d_all, mine)
-                torch.cuda.synchronize()
-                plan.run_to_host(None, A_ptr, N_ptr)   # genotypes resident after the all-gather; finalize + D2H pipelined
-            api = ("gcta_b200_plan_upload_rows (1/N of the rows per rank) + NCCL all-gather of the packed rows over NVLink + "
-                   "plan_run_to_host (finalize + download pipelined behind the last SYRK), pinned host buffers")
-            h2d = stride * (r1 - r0)
+                def e2e_step():
+                    plan.upload_rows(h_bed.data_ptr(), r0, r1)
+                    tdist.all_gather_into_tensor(d_all, mine)
+                    torch.cuda.synchronize()
+                    plan.run_to_host(None, A_ptr, N_ptr)   # genotypes resident after the all-gather; finalize + D2H pipelined
+                api = ("gcta_b200_plan_upload_rows (1/N of the rows per rank) + NCCL all-gather of the packed rows over NVLink + "
+                       "plan_run_to_host (finalize + download pipelined behind the last SYRK), pinned host buffers")
+                h2d = stride * (r1 - r0)
+            else:
+                # gcta_b200_exchange_*: the file rows travel in 32 segments; of each, a rank uploads 1/N over its own PCIe
+                # link and pulls the rest out of its peers' HBM with the copy engines over NVLink (CUDA IPC, no SM used), and
+                # the plan starts chunk c as soon as the segments it reads are in: the exchange hides behind the compute
+                host = tdist.new_group(backend="gloo")   # host barriers only; keeps NCCL kernels out of the timed region
+                ex = abi.Exchange(plan, rank, world)      # the plan now reads the exchange's (zeroed) gather buffer
+                blobs = [None] * world
+                tdist.all_gather_object(blobs, ex.blob, group=host)
+                ex.connect(b"".join(blobs))
+
+                def e2e_step():
+                    tdist.barrier(group=host)   # no peer still reads my buffer from the step before
+                    ex.post(h_bed.data_ptr())
+                    tdist.barrier(group=host)   # every rank has recorded this step's segment events
+                    ex.pull()
+                    plan.run_to_host(None, A_ptr, N_ptr)   # waits per chunk; finalize + D2H pipelined behind the last SYRK
+                    ex.finish()
+                api = ("gcta_b200_exchange_post/pull (per rank 1/N of the rows over PCIe, the rest peer-to-peer over NVLink by the copy "
+                       "engines, 32 segments, overlapped with the compute) + plan_run_to_host (finalize + download pipelined), pinned host buffers")
+                seg = max(1, -(-m // 32))
+                h2d = 0
+                for s0 in range(0, m, seg):
+                    s1 = min(m, s0 + seg)
+                    per = -(-(s1 - s0) // world)
+                    h2d += stride * (min(s1, s0 + (rank + 1) * per) - min(s1, s0 + rank * per))
         e2e_step()
         barrier()
         t0 = time.perf_counter()
@@ -227,7 +251,11 @@ def main_ours(a, rank, world, local_rank):
             e2e_step()
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
-        d2h = sum_over_ranks(cnt * 4 * (2 if o.total_missing > 0 else 1))
+        if ex is not None:
+            ex.disconnect()
+            barrier()     # no gather buffer is freed while a peer still maps it
+            ex.close()    # the plan goes back to its own buffer
+        d2h =sum_over_ranks(cnt * 4 * (2 if o.total_missing > 0 else 1))
         e2e = {"value": pairs_total * m * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(h2d)),
                "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps, "api": api}
         if rank == 0:

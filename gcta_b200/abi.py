@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(HERE, "libgcta_b200.so")
 FP16, BF16, FP16X2 = 0, 1, 2
 ERRCAP = 512
 TILE_M, TILE_N = 256, 256
+IPC_HANDLE_BYTES = 64   # GCTA_B200_IPC_HANDLE_BYTES
 
 EXPORTS = [
     "gcta_b200_make_grm", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth", "gcta_b200_plan_download_bed",
@@ -23,6 +24,10 @@ EXPORTS = [
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
     "gcta_b200_partition", "gcta_b200_tile_list", "gcta_b200_allele_counts", "gcta_b200_nonmiss_matrix", "gcta_b200_count_tiles",
     "gcta_b200_plan_use_device_bed", "gcta_b200_plan_upload_rows", "gcta_b200_plan_run_to_host",
+    "gcta_b200_plan_num_chunks", "gcta_b200_plan_chunk_rows", "gcta_b200_plan_upload_rows_async", "gcta_b200_plan_set_chunk_events",
+    "gcta_b200_plan_use_own_bed", "gcta_b200_plan_geometry",
+    "gcta_b200_exchange_blob_bytes", "gcta_b200_exchange_create", "gcta_b200_exchange_connect", "gcta_b200_exchange_post",
+    "gcta_b200_exchange_pull", "gcta_b200_exchange_finish", "gcta_b200_exchange_disconnect", "gcta_b200_exchange_destroy",
 ]
 
 
@@ -250,6 +255,59 @@ class Plan:
             self.close()
         except Exception:
             pass
+
+
+class Exchange:
+    """gcta_b200_exchange_*: peer exchange of the packed rows between the ranks' plans (copy engines over NVLink).
+
+    ex = Exchange(plan, rank, world); publish ex.blob to every rank; ex.connect(b"".join(blobs in rank order));
+    per step: <host barrier> ex.post(bed_host) <host barrier> ex.pull(); plan.run_to_host(None, ...); ex.finish()."""
+
+    def __init__(self, plan: "Plan", rank: int, world: int):
+        L = lib()
+        L.gcta_b200_exchange_blob_bytes.restype = C.c_int64
+        self.plan = plan   # keeps the plan alive as long as the exchange
+        self._h = C.c_void_p()
+        nbytes = L.gcta_b200_exchange_blob_bytes(plan._h)
+        blob = C.create_string_buffer(nbytes)
+        err = C.create_string_buffer(ERRCAP)
+        _check(L.gcta_b200_exchange_create(plan._h, C.c_int32(rank), C.c_int32(world), blob, C.byref(self._h), err, ERRCAP), err)
+        self.blob = blob.raw
+        self.world = world
+
+    def connect(self, all_blobs: bytes):
+        if len(all_blobs) != len(self.blob) * self.world:
+            raise GctaB200Error(1, "exchange.connect: need one blob per rank")
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_exchange_connect(self._h, all_blobs, err, ERRCAP), err)
+
+    def post(self, bed_host):
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_exchange_post(self._h, C.c_void_p(_ptr(bed_host)), err, ERRCAP), err)
+
+    def pull(self):
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_exchange_pull(self._h, err, ERRCAP), err)
+
+    def finish(self):
+        err = C.create_string_buffer(ERRCAP)
+        _check(lib().gcta_b200_exchange_finish(self._h, err, ERRCAP), err)
+
+    def disconnect(self):
+        """unmap the peers' buffers; every rank, then a host barrier, then close()"""
+        if self._h:
+            lib().gcta_b200_exchange_disconnect(self._h)
+
+    def close(self):
+        if self._h:
+            lib().gcta_b200_exchange_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
 
 
 def call(name, *args):

@@ -131,7 +131,7 @@ struct gcta_b200_plan {
     std::vector<int32_t> h_include, h_tiles;
     bool downloaded = false;   // the last run already streamed A (and filled N) into the caller's buffers
     int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
-    uint8_t* d_bed = nullptr;
+    uint8_t *d_bed = nullptr, *d_bed_own = nullptr;   // d_bed: the buffer the kernels read; d_bed_own: the plan's allocation
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
     int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr, *d_pairs = nullptr;   // d_pairs: CTA-pair work list of the cta_group::2 SYRK
@@ -243,6 +243,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
 
     // fixed-size buffers
     PLAN_TRY(dev_alloc(p, &p->d_bed, (size_t)p->pitch * a->m_file, err, errcap));
+    p->d_bed_own = p->d_bed;
     if (p->pitch != p->stride) PLAN_CUDA(cudaMemset(p->d_bed, 0, (size_t)p->pitch * a->m_file));
     PLAN_TRY(dev_alloc(p, &p->d_keepmask, (size_t)p->pitch / 4, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_mu, (size_t)m, err, errcap));
@@ -346,6 +347,23 @@ extern "C" int gcta_b200_plan_use_device_bed(gcta_b200_plan* p, void* d_bed, int
         GB_ARG(((uintptr_t)d_bed & 15) == 0, "plan_use_device_bed: buffer must be 16-byte aligned");
         p->d_bed = (uint8_t*)d_bed;   // the plan's own buffer stays allocated and is freed with the plan
     }
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_use_own_bed(gcta_b200_plan* p)
+{
+    if (!p) return GCTA_B200_ERR_ARG;
+    p->d_bed = p->d_bed_own;
+    return 0;
+}
+
+extern "C" int gcta_b200_plan_geometry(gcta_b200_plan* p, int32_t* device, int64_t* m_file, int64_t* stride, int64_t* pitch)
+{
+    if (!p) return GCTA_B200_ERR_ARG;
+    if (device) *device = p->device;
+    if (m_file) *m_file = p->m_file;
+    if (stride) *stride = p->stride;
+    if (pitch) *pitch = p->pitch;
     return 0;
 }
 

@@ -132,6 +132,36 @@ int gcta_b200_plan_chunk_rows(gcta_b200_plan* plan, int64_t chunk, int64_t* row_
 int gcta_b200_plan_upload_rows_async(gcta_b200_plan* plan, const uint8_t* bed_host, int64_t row_begin, int64_t row_end,
                                      void* stream, char* err, size_t errcap);
 int gcta_b200_plan_set_chunk_events(gcta_b200_plan* plan, void* const* events, int64_t count, char* err, size_t errcap);
+/* back to the plan's own genotype buffer after plan_use_device_bed; the plan's device, file rows, row stride, row pitch */
+int gcta_b200_plan_use_own_bed(gcta_b200_plan* plan);
+int gcta_b200_plan_geometry(gcta_b200_plan* plan, int32_t* device, int64_t* m_file, int64_t* stride, int64_t* pitch);
+
+/* ---- peer exchange of the packed rows between the ranks of a multi-GPU run (csrc/exchange.cu) ----
+ * One process per GPU.  Each rank uploads 1/world of every SNP chunk's rows over its own PCIe link and pulls the rest
+ * out of its peers' HBM with the copy engines over NVLink (CUDA IPC memory + inter-process events; no SM, no NCCL
+ * kernel next to the persistent SYRK grid).  The plan then waits per chunk, so the exchange of later chunks runs
+ * behind the compute of earlier ones.  No reference counterpart (the reference reads the .bed on one thread,
+ * data.cpp:140-194).  Protocol, every rank:
+ *   exchange_create(plan, rank, world, my_blob)        my_blob: exchange_blob_bytes(plan) bytes to publish
+ *   <all-gather the blobs between the processes by any host-side means, rank order>
+ *   exchange_connect(ex, all_blobs)
+ *   per step:  <host barrier>  exchange_post(ex, bed_host)  <host barrier>  exchange_pull(ex)
+ *              plan_run / plan_run_to_host with bed_host == NULL          exchange_finish(ex)
+ *   exchange_disconnect(ex) on every rank, <host barrier>, exchange_destroy(ex) (frees the buffer the peers had
+ *   mapped and puts the plan back on its own), then plan_destroy.
+ * The rows are exchanged in 32 fixed segments of the file (the same on every rank); the plans may chunk the SNP axis
+ * differently (a band's chunk length depends on its row_end).  All plans must have the same n_file and m_file. */
+#define GCTA_B200_IPC_HANDLE_BYTES 64
+typedef struct gcta_b200_exchange gcta_b200_exchange;
+int64_t gcta_b200_exchange_blob_bytes(gcta_b200_plan* plan);
+int gcta_b200_exchange_create(gcta_b200_plan* plan, int32_t rank, int32_t world, uint8_t* my_blob, gcta_b200_exchange** ex,
+                              char* err, size_t errcap);
+int gcta_b200_exchange_connect(gcta_b200_exchange* ex, const uint8_t* all_blobs, char* err, size_t errcap);
+int gcta_b200_exchange_post(gcta_b200_exchange* ex, const uint8_t* bed_host, char* err, size_t errcap);
+int gcta_b200_exchange_pull(gcta_b200_exchange* ex, char* err, size_t errcap);
+int gcta_b200_exchange_finish(gcta_b200_exchange* ex, char* err, size_t errcap);
+void gcta_b200_exchange_disconnect(gcta_b200_exchange* ex);
+void gcta_b200_exchange_destroy(gcta_b200_exchange* ex);
 /* inverse of plan_upload: copy the plan's HBM genotype buffer to host memory in .bed payload layout
  * (bench/test use: obtain the host copy of a device-generated data set) */
 int gcta_b200_plan_download_bed(gcta_b200_plan* plan, uint8_t* bed_host, char* err, size_t errcap);
