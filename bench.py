@@ -174,7 +174,7 @@ def main_ours(a, rank, world, local_rank):
     sust, burst, hbm, which = peaks()
     syrk_tflops = 2.0 * band_pairs * m * a.steps / (syrk_ms * 1e-3) / 1e12 if syrk_ms > 0 else 0.0
     syrk_tflops_min = -max_over_ranks(-syrk_tflops)
-    nchunks = -(-m // max(1, plan_chunk(plan, n, m)))
+    nchunks = len(plan.chunk_rows())   # K2 launches per step on this rank
     # K1 (HBM bound) for reference: packed read + 16-bit Z write (+ diag re-read), SURVEY.md 8d
     ldz = (n + 255) // 256 * 256
     k1_bytes = m * ((n + 3) // 4 * 2 + 2 * ldz)
@@ -229,13 +229,20 @@ def main_ours(a, rank, world, local_rank):
                 tdist.all_gather_object(blobs, ex.blob, group=host)
                 ex.connect(b"".join(blobs))
 
+                e2e_phases = {}
+
                 def e2e_step():
+                    t = [time.perf_counter()]
                     tdist.barrier(group=host)   # no peer still reads my buffer from the step before
                     ex.post(h_bed.data_ptr())
                     tdist.barrier(group=host)   # every rank has recorded this step's segment events
                     ex.pull()
-                    plan.run_to_host(None, A_ptr, N_ptr)   # waits per chunk; finalize + D2H pipelined behind the last SYRK
+                    t.append(time.perf_counter())
+                    oo = plan.run_to_host(None, A_ptr, N_ptr)   # waits per chunk; finalize + D2H pipelined behind the last SYRK
+                    t.append(time.perf_counter())
                     ex.finish()
+                    e2e_phases.update({"barriers+post+pull (host)": 1e3 * (t[1] - t[0]), "plan_run_to_host (host wall)": 1e3 * (t[2] - t[1]),
+                                       "device, first kernel to last": oo.ms_total, "device syrk": oo.ms_syrk, "device decode+diag": oo.ms_decode})
                 api = ("gcta_b200_exchange_post/pull (per rank 1/N of the rows over PCIe, the rest peer-to-peer over NVLink by the copy "
                        "engines, 32 segments, overlapped with the compute) + plan_run_to_host (finalize + download pipelined), pinned host buffers")
                 seg = max(1, -(-m // 32))
@@ -255,9 +262,12 @@ def main_ours(a, rank, world, local_rank):
             ex.disconnect()
             barrier()     # no gather buffer is freed while a peer still maps it
             ex.close()    # the plan goes back to its own buffer
-        d2h =sum_over_ranks(cnt * 4 * (2 if o.total_missing > 0 else 1))
+        d2h = sum_over_ranks(cnt * 4 * (2 if o.total_missing > 0 else 1))
         e2e = {"value": pairs_total * m * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(h2d)),
                "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps, "api": api}
+        if ex is not None:
+            ph = ranks.gather([e2e_phases[k] for k in sorted(e2e_phases)])
+            e2e["last_step_ms_per_rank"] = {k: [round(float(r[i]), 1) for r in ph] for i, k in enumerate(sorted(e2e_phases))}
         if rank == 0:
             diag_idx = np.arange(min(1000, row_end - row_begin))
             di = (diag_idx + row_begin) * (diag_idx + row_begin + 1) // 2 + diag_idx + row_begin - base
@@ -311,13 +321,6 @@ def k2_traffic(n, world):
     if d.get("n") != n:
         return None
     return d["dram_bytes_read"] + d["dram_bytes_write"]   # bytes per launch of 85,056 SNPs (profiles/k2_traffic.json)
-
-
-def plan_chunk(plan, n, m):
-    """SNPs per chunk the plan chose (mirrors plan.cu: <= 8 GiB of Z)."""
-    ldz = (n + 255) // 256 * 256
-    kc = (int(os.environ.get("GCTA_B200_ZCAP_GIB", "16")) << 30) // (ldz * 2) // 64 * 64
-    return max(64, min(kc, (m + 63) // 64 * 64))
 
 
 def main():

@@ -129,6 +129,8 @@ struct gcta_b200_plan {
     std::vector<cudaEvent_t> upload_events;
     std::vector<cudaEvent_t> chunk_ready;   // caller-owned events: chunk c's packed rows are in place (plan_set_chunk_events)
     std::vector<int32_t> h_include, h_tiles;
+    std::vector<int64_t> cstart;   // SNP chunk c = included SNPs [cstart[c], cstart[c+1]); every chunk <= `chunk` SNPs
+    int64_t nchunks() const { return (int64_t)cstart.size() - 1; }
     bool downloaded = false;   // the last run already streamed A (and filled N) into the caller's buffers
     int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
     uint8_t *d_bed = nullptr, *d_bed_own = nullptr;   // d_bed: the buffer the kernels read; d_bed_own: the plan's allocation
@@ -317,6 +319,16 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         kc = std::min<int64_t>(kc, round_up(m, 64));
         kc = std::min<int64_t>(kc, 1 << 23);   // counts of one chunk must stay exact in the FP32 accumulator
         p->chunk = kc;
+        // Chunk table.  When the plan picks the chunk length itself and there are many SNPs, a short head chunk (1/64 of
+        // them) goes first: a run that receives its packed rows while it computes (plan_run_streamed / plan_run_to_host,
+        // per-chunk events of an exchange) can only start once chunk 0's rows are in HBM, and a 16 GiB chunk of a narrow
+        // band is up to half of the file.
+        int64_t head = round_up((m + 63) / 64, 64);
+        if (const char* e = getenv("GCTA_B200_HEAD_CHUNK")) head = round_up(std::max<int64_t>(0, atoll(e)), 64);
+        if (a->chunk_snps > 0 || m < 65536 || head >= kc) head = 0;
+        p->cstart.assign(1, 0);
+        if (head > 0) p->cstart.push_back(head);
+        while (p->cstart.back() < m) p->cstart.push_back(std::min<int64_t>(m, p->cstart.back() + kc));
         PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz * planes, err, errcap));
         p->overlap = getenv("GCTA_B200_OVERLAP") && atoi(getenv("GCTA_B200_OVERLAP")) > 0;
         if (p->overlap && kc < round_up(m, 64)) PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[1], (size_t)kc * p->ldz * planes, err, errcap));
@@ -368,12 +380,12 @@ extern "C" int gcta_b200_plan_geometry(gcta_b200_plan* p, int32_t* device, int64
 }
 
 // ---- chunk-wise delivery of the packed rows by the caller (multi-GPU: upload 1/G + all-gather per chunk) ----
-extern "C" int64_t gcta_b200_plan_num_chunks(gcta_b200_plan* p) { return p ? (p->m + p->chunk - 1) / p->chunk : 0; }
+extern "C" int64_t gcta_b200_plan_num_chunks(gcta_b200_plan* p) { return p ? p->nchunks() : 0; }
 
 extern "C" int gcta_b200_plan_chunk_rows(gcta_b200_plan* p, int64_t c, int64_t* row_begin, int64_t* row_end)
 {
     if (!p || c < 0 || c >= gcta_b200_plan_num_chunks(p) || !row_begin || !row_end) return GCTA_B200_ERR_ARG;
-    const int64_t k0 = c * p->chunk, k1 = std::min<int64_t>(p->m, k0 + p->chunk);
+    const int64_t k0 = p->cstart[c], k1 = p->cstart[c + 1];
     *row_begin = k0;
     *row_end = k1;
     if (p->has_include) {
@@ -517,8 +529,9 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
     std::vector<cudaEvent_t> evs;
     int rc = 0;
     int gi = 0;
-    for (int s = 0; s < nseg && !rc; s++) {
-        // groups [gi, ge): about 1/nseg of the tiles each
+    for (int s = 0; s < nseg && !rc && gi < ngroups; s++) {
+        // groups [gi, ge): about 1/nseg of the tiles each (the first groups of a triangle are small, so early segments
+        // may swallow several groups and use them up before the last segment)
         const int64_t want = p->ntiles * (s + 1) / nseg;
         int ge = gi + 1;
         while (ge < ngroups && (s == nseg - 1 || gstart[ge] < want)) ge++;
@@ -559,7 +572,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     bool pipelined = false;
     GB_CUDA(cudaSetDevice(p->device));
     std::vector<cudaEvent_t>& up = p->upload_events;
-    const int64_t nch_up = (p->m + p->chunk - 1) / p->chunk;
+    const int64_t nch_up = p->nchunks();
     if (bed_host) {
         if (!p->stream_copy) GB_CUDA(cudaStreamCreateWithFlags(&p->stream_copy, cudaStreamNonBlocking));
         while ((int64_t)up.size() < nch_up) {
@@ -572,7 +585,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     // even when the host buffer is pageable (then the call blocks the host, but the GPU is already busy)
     auto issue_upload = [&](int64_t c) -> cudaError_t {
         if (!bed_host || c >= nch_up) return cudaSuccess;
-        const int64_t k0 = c * p->chunk, k1 = std::min<int64_t>(p->m, k0 + p->chunk);
+        const int64_t k0 = p->cstart[c], k1 = p->cstart[c + 1];
         int64_t r0 = k0, r1 = k1;
         if (p->has_include) {
             r0 = *std::min_element(p->h_include.begin() + k0, p->h_include.begin() + k1);
@@ -589,7 +602,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     // Measured on cfg3 (profiles/README.md): co-running the decode with the SYRK steals issue slots and power
     // from the tensor loop (K2 +30 %), so by default both run on one stream; GCTA_B200_OVERLAP=1 enables it.
     cudaStream_t st = p->stream, sd = p->overlap ? p->stream2 : p->stream;
-    const int64_t nchunks = (p->m + p->chunk - 1) / p->chunk;
+    const int64_t nchunks = p->nchunks();
     // events: [0] start, [1] buffers cleared, then 4 per chunk (decode start/end, syrk start/end), then 2
     const size_t need = (size_t)(4 * nchunks + 4);
     while (p->events.size() < need) {
@@ -614,7 +627,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     GB_CUDA(cudaEventRecord(p->events[1], st));
     GB_CUDA(cudaStreamWaitEvent(sd, p->events[1], 0));
     for (int64_t c = 0; c < nchunks; c++) {
-        const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
+        const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
         void* Z = (p->overlap && p->d_Zbuf[1]) ? p->d_Zbuf[c & 1] : p->d_Zbuf[0];
         if (c >= 2) GB_CUDA(cudaStreamWaitEvent(sd, EV(c - 2, 3), 0));   // the SYRK that last read this Z buffer
         if (bed_host) GB_CUDA(cudaStreamWaitEvent(sd, up[c], 0));        // this chunk's packed rows have landed
@@ -678,7 +691,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     if (tm > 0 && !use_popc) {
         GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
         for (int64_t c = 0; c < nchunks; c++) {   // the Z buffer is free again: reuse it for the indicator chunks
-            const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
+            const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
             // 8-bit E4M3 indicators (kind::f8f6f4: twice the MMA rate, half the bytes) unless the CTA-pair kernel or
             // GCTA_B200_N_MODE=tensor16 asks for the 16-bit route; both give the same integers
             const int opN = (p->d_pairs || (nmode && strcmp(nmode, "tensor16") == 0)) ? op16 : GCTA_B200_E4M3;
@@ -723,7 +736,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             }
             GB_CUDA(cudaMemsetAsync(p->d_Dtiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
             for (int64_t c = 0; c < nchunks; c++) {
-                const int64_t k0 = c * p->chunk, kc = std::min<int64_t>(p->chunk, p->m - k0);
+                const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
                 int rc = gcta_b200_nonmiss_matrix_ex(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16, p->d_dk,
                                                      p->d_Zbuf[0], p->ldz, st, err, errcap);
                 if (rc) return rc;

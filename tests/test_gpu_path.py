@@ -201,7 +201,7 @@ def test_randomised_shapes_against_the_oracle(seed):
     check_grm(A, N, pack_lower(Aref), pack_lower(Nref))
 
 
-@pytest.mark.parametrize("n,world", [(7000, 1), (9000, 2)])
+@pytest.mark.parametrize("n,world", [(7000, 1), (9000, 2), (9216, 1), (14000, 3)])
 def test_pipelined_download_equals_plain_download(n, world):
     """plan_run_to_host cuts the last chunk into segments (3-4 raster groups here) and streams each segment's rows to
     the host behind the remaining SYRK work; the result must be the very same bytes as run + download."""
