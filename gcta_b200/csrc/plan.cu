@@ -319,16 +319,18 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         kc = std::min<int64_t>(kc, round_up(m, 64));
         kc = std::min<int64_t>(kc, 1 << 23);   // counts of one chunk must stay exact in the FP32 accumulator
         p->chunk = kc;
-        // Chunk table.  When the plan picks the chunk length itself and there are many SNPs, a short head chunk (1/64 of
-        // them) goes first: a run that receives its packed rows while it computes (plan_run_streamed / plan_run_to_host,
-        // per-chunk events of an exchange) can only start once chunk 0's rows are in HBM, and a 16 GiB chunk of a narrow
-        // band is up to half of the file.
+        // Chunk table.  When the plan picks the chunk length itself and there are many SNPs, the chunks ramp up: 1/64 of
+        // the SNPs first, then twice the previous chunk until the Z buffer's length is reached.  A run that receives its
+        // packed rows while it computes (plan_run_streamed / plan_run_to_host, per-chunk events of an exchange) can only
+        // start chunk c once its rows are in HBM; with the ramp it waits for 1/64 of the file at the start and the
+        // transfer of each later chunk has the (at least half as long) compute of the one before to hide behind -
+        // a 16 GiB chunk of a narrow band would otherwise be up to half of the file.  Costs a few more launches.
         int64_t head = round_up((m + 63) / 64, 64);
         if (const char* e = getenv("GCTA_B200_HEAD_CHUNK")) head = round_up(std::max<int64_t>(0, atoll(e)), 64);
         if (a->chunk_snps > 0 || m < 65536 || head >= kc) head = 0;
         p->cstart.assign(1, 0);
-        if (head > 0) p->cstart.push_back(head);
-        while (p->cstart.back() < m) p->cstart.push_back(std::min<int64_t>(m, p->cstart.back() + kc));
+        for (int64_t len = head > 0 ? head : kc; p->cstart.back() < m; len = std::min<int64_t>(kc, 2 * len))
+            p->cstart.push_back(std::min<int64_t>(m, p->cstart.back() + len));
         PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz * planes, err, errcap));
         p->overlap = getenv("GCTA_B200_OVERLAP") && atoi(getenv("GCTA_B200_OVERLAP")) > 0;
         if (p->overlap && kc < round_up(m, 64)) PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[1], (size_t)kc * p->ldz * planes, err, errcap));
