@@ -41,6 +41,8 @@ public:
     void save_freq();                                     // data.cpp:930-945
     void make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd);   // grm.cpp:219-301 -> gcta_b200_make_grm
 
+    int selftest_writer(int64_t n, bool output_bin);      // times output_grm on a fabricated GRM (no GPU)
+
     // device options (not in the reference)
     int operand = 0;      // GCTA_B200_FP16
     int n_gpus = 1;       // row bands computed one after another on devices 0..n_gpus-1 of this process

@@ -9,10 +9,13 @@
 #include <iomanip>
 #include <iostream>
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 
 #include "../../include/gcta_b200.h"
 #include "gcta_host.h"
+#include "grm_text_gz.h"
 
 using std::cout;
 using std::endl;
@@ -240,51 +243,7 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
 // ---------------------------------------------------------------------------------------------
 // writers (grm.cpp:303-341)
 // ---------------------------------------------------------------------------------------------
-// Fast formatters for the n(n+1)/2 text lines.  put_e6 writes exactly what printf("%.6e") writes (the reference's
-// `setf(scientific); precision(6)`, grm.cpp:326-327): the value is scaled by an exact power of ten to 7 significant
-// digits; whenever the scaled value is close enough to a rounding boundary for the one floating-point rounding of the
-// scaling to matter (or the exponent is outside the exact-power range) it falls back to snprintf itself.
-static inline char* put_uint(char* q, uint64_t v)
-{
-    char tmp[24];
-    int k = 0;
-    do { tmp[k++] = (char)('0' + v % 10); v /= 10; } while (v);
-    while (k) *q++ = tmp[--k];
-    return q;
-}
-
-static int put_e6(char* q, double v)
-{
-    static const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
-    char* const q0 = q;
-    double a = std::fabs(v);
-    if (!(a >= 1e-15 && a < 1e15)) {
-        if (v == 0.0 && !std::signbit(v)) { memcpy(q, "0.000000e+00", 12); return 12; }
-        return snprintf(q, 32, "%.6e", v);
-    }
-    int e = (int)std::floor(std::log10(a));
-    for (int attempt = 0; attempt < 3; attempt++) {
-        const int k = 6 - e;   // a * 10^k should lie in [1e6, 1e7)
-        const double scaled = k >= 0 ? a * P10[k] : a / P10[-k];
-        if (scaled < 1e6) { e--; continue; }
-        if (scaled >= 1e7) { e++; continue; }
-        const double fl = std::floor(scaled), frac = scaled - fl;
-        if (std::fabs(frac - 0.5) < 1e-5) return snprintf(q0, 32, "%.6e", v);   // too close to a tie to decide here
-        uint64_t d = (uint64_t)fl + (frac > 0.5 ? 1 : 0);
-        int ee = e;
-        if (d >= 10000000ull) { d = 1000000ull; ee++; }
-        if (std::signbit(v)) *q++ = '-';
-        char dig[7];
-        for (int t = 6; t >= 0; t--) { dig[t] = (char)('0' + d % 10); d /= 10; }
-        *q++ = dig[0]; *q++ = '.';
-        for (int t = 1; t < 7; t++) *q++ = dig[t];
-        *q++ = 'e';
-        if (ee < 0) { *q++ = '-'; ee = -ee; } else *q++ = '+';
-        *q++ = (char)('0' + ee / 10); *q++ = (char)('0' + ee % 10);
-        return (int)(q - q0);
-    }
-    return snprintf(q0, 32, "%.6e", v);
-}
+using grm_text_gz::put_e6;   // exact "%.6e" formatter (grm_text_gz.cpp)
 
 // `gcta64_b200 --selftest-format`: put_e6 against snprintf on many values (tests/test_host_cli.py runs it)
 int gcta_host_selftest_format()
@@ -315,6 +274,57 @@ int gcta_host_selftest_format()
     return bad ? 1 : 0;
 }
 
+// `gcta64_b200 --selftest-gz`: the structured encoder against zlib's inflate on awkward inputs (one line, constant
+// fields that merge into long runs, NaN / inf / zero / huge values, negative and extreme N, row ranges that start
+// mid-triangle); every member must inflate - CRC and length checked by zlib - to the formatter's text.
+int gcta_host_selftest_gz()
+{
+    auto inflate_all = [](const string& gz, string& text) -> bool {
+        z_stream s;
+        memset(&s, 0, sizeof s);
+        if (inflateInit2(&s, 15 + 16) != Z_OK) return false;
+        s.next_in = (Bytef*)gz.data();
+        s.avail_in = (uInt)gz.size();
+        vector<char> buf(1 << 16);
+        int rc = Z_OK;
+        while (rc == Z_OK) {
+            s.next_out = (Bytef*)buf.data();
+            s.avail_out = (uInt)buf.size();
+            rc = inflate(&s, Z_NO_FLUSH);
+            text.append(buf.data(), buf.size() - s.avail_out);
+        }
+        const bool ok = rc == Z_STREAM_END && s.avail_in == 0;
+        inflateEnd(&s);
+        return ok;
+    };
+    uint64_t st = 0x2545F4914F6CDD1Dull;
+    auto next = [&]() { st ^= st << 13; st ^= st >> 7; st ^= st << 17; return st; };
+    int bad = 0, cases = 0;
+    auto run = [&](const char* name, const vector<float>& A, const vector<int32_t>& N, int64_t r0, int64_t r1) {
+        string text, gz, back;
+        grm_text_gz::format_rows(A.data(), N.data(), r0, r1, text);
+        grm_text_gz::encode_rows(A.data(), N.data(), r0, r1, gz);
+        cases++;
+        if (!inflate_all(gz, back) || back != text) { bad++; fprintf(stderr, "gz selftest: case %s rows [%lld,%lld) failed\n", name, (long long)r0, (long long)r1); }
+    };
+    const float specials[] = {0.0f, -0.0f, 1.0f, -1.0f, NAN, INFINITY, -INFINITY, 1e30f, -1e-30f, 1.17549435e-38f, 1e-45f, 3.4028235e38f, 9.9999995e-1f, 0.5f};
+    const int32_t nspecial[] = {0, 1, -1, 9, 10, 99, 100, 2147483647, -2147483647 - 1, 1000000, 999999};
+    for (int64_t n : {1, 2, 3, 17, 60, 300}) {
+        const size_t tri = (size_t)(n * (n + 1) / 2);
+        vector<float> A(tri);
+        vector<int32_t> N(tri);
+        std::fill(A.begin(), A.end(), 0.0f); std::fill(N.begin(), N.end(), 1000000);
+        run("constant", A, N, 0, n);
+        for (size_t o = 0; o < tri; o++) { A[o] = specials[next() % (sizeof specials / sizeof specials[0])]; N[o] = nspecial[next() % (sizeof nspecial / sizeof nspecial[0])]; }
+        run("specials", A, N, 0, n);
+        for (size_t o = 0; o < tri; o++) { A[o] = (float)((double)(int64_t)(next() % 2000001 - 1000000) * 1e-9); N[o] = 500000 - (int32_t)(next() % 3); }
+        run("grm-like", A, N, 0, n);
+        if (n >= 17) { run("mid-triangle", A, N, n / 2, n / 2 + 1); run("tail", A, N, n - 3, n); run("empty", A, N, 5, 5); }
+    }
+    printf("gz selftest: %d cases, %d failures\n", cases, bad);
+    return bad ? 1 : 0;
+}
+
 static void gz_member(const string& text, string& out)
 {
     z_stream s;
@@ -322,7 +332,7 @@ static void gz_member(const string& text, string& out)
     // Level 1 by default: deflate is ~75 % of the writer's time at zlib's default level 6 (what the reference's
     // gzopen(name, "w") uses, zfstream.cpp:51-76) and 3.4x faster at level 1 for ~23 % larger files; the decompressed text is the
     // same.  GCTA_B200_GZ_LEVEL=6 restores the reference's level.
-    static const int level = getenv("GCTA_B200_GZ_LEVEL") ? std::max(1, std::min(9, atoi(getenv("GCTA_B200_GZ_LEVEL")))) : 1;
+    static const int level = getenv("GCTA_B200_GZ_LEVEL") ? std::max(0, std::min(9, atoi(getenv("GCTA_B200_GZ_LEVEL")))) : 1;
     if (deflateInit2(&s, level, Z_DEFLATED, 15 + 16 /* gzip wrapper */, 8, Z_DEFAULT_STRATEGY) != Z_OK)
         throw string("Error: zlib deflateInit2 failed.");
     out.resize(deflateBound(&s, (uLong)text.size()) + 64);
@@ -370,38 +380,72 @@ void gcta_host::output_grm(const vector<float>& A, const vector<int32_t>& N, boo
             blocks.emplace_back(i0, i1);
             i0 = i1;
         }
-        for (size_t b0 = 0; b0 < blocks.size(); b0 += T) {
-            const size_t b1 = std::min(blocks.size(), b0 + T);
-            vector<string> gz(b1 - b0);
-            vector<string> errs(b1 - b0);
-            vector<std::thread> th;
-            for (size_t b = b0; b < b1; b++)
-                th.emplace_back([&, b]() {
+        // T workers take blocks off a shared counter and compress them; this thread writes the members in order as
+        // they complete, so compression, formatting and file I/O overlap.  At most `window` blocks are in flight.
+        // Default codec: the structure-aware encoder of grm_text_gz.cpp; GCTA_B200_GZ_LEVEL=<0..9> formats the text and
+        // runs zlib's deflate at that level instead (6 = what the reference's gzopen(name, "w") uses).
+        const bool use_zlib = getenv("GCTA_B200_GZ_LEVEL") != nullptr;
+        const size_t nb = blocks.size(), window = (size_t)(2 * T);
+        vector<string> gz(nb);
+        vector<char> done(nb, 0);
+        string first_error;
+        std::mutex mu;
+        std::condition_variable cv_done, cv_room;
+        size_t next_block = 0, next_write = 0;
+        vector<std::thread> th;
+        for (int t = 0; t < T && (size_t)t < nb; t++)
+            th.emplace_back([&]() {
+                for (;;) {
+                    size_t b;
+                    {
+                        std::unique_lock<std::mutex> lk(mu);
+                        cv_room.wait(lk, [&] { return next_block >= nb || next_block < next_write + window || !first_error.empty(); });
+                        if (next_block >= nb || !first_error.empty()) return;
+                        b = next_block++;
+                    }
+                    string member, err;
                     try {
-                        string text;
-                        char buf[96];
-                        for (int64_t i = blocks[b].first; i < blocks[b].second; i++)
-                            for (int64_t j = 0; j <= i; j++) {
-                                const size_t o = (size_t)(i * (i + 1) / 2 + j);
-                                char* q = buf;
-                                q = put_uint(q, (uint64_t)(i + 1)); *q++ = '\t';
-                                q = put_uint(q, (uint64_t)(j + 1)); *q++ = '\t';
-                                if (N[o] < 0) { *q++ = '-'; q = put_uint(q, (uint64_t)(-(int64_t)N[o])); } else q = put_uint(q, (uint64_t)N[o]);
-                                *q++ = '\t';
-                                q += put_e6(q, (double)A[o]);
-                                *q++ = '\n';
-                                text.append(buf, (size_t)(q - buf));
-                            }
-                        gz_member(text, gz[b - b0]);
-                    } catch (const string& e) { errs[b - b0] = e; }
-                });
-            for (auto& t : th) t.join();
-            for (size_t k = 0; k < gz.size(); k++) {
-                if (!errs[k].empty()) { fclose(f); throw errs[k]; }
-                fwrite(gz[k].data(), 1, gz[k].size(), f);
+                        if (use_zlib) {
+                            string text;
+                            grm_text_gz::format_rows(A.data(), N.data(), blocks[b].first, blocks[b].second, text);
+                            gz_member(text, member);
+                        } else
+                            grm_text_gz::encode_rows(A.data(), N.data(), blocks[b].first, blocks[b].second, member);
+                    } catch (const string& e) { err = e; }
+                    catch (const std::exception& e) { err = string("Error: ") + e.what(); }
+                    {
+                        std::lock_guard<std::mutex> lk(mu);
+                        gz[b].swap(member);
+                        done[b] = 1;
+                        if (!err.empty() && first_error.empty()) first_error = err;
+                    }
+                    cv_done.notify_all();
+                    if (!err.empty()) { cv_room.notify_all(); return; }
+                }
+            });
+        bool write_failed = false;
+        for (; next_write < nb;) {
+            string member;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv_done.wait(lk, [&] { return done[next_write] || !first_error.empty(); });
+                if (!first_error.empty()) break;
+                member.swap(gz[next_write]);
+                next_write++;
+            }
+            cv_room.notify_all();
+            if (fwrite(member.data(), 1, member.size(), f) != member.size()) {
+                std::lock_guard<std::mutex> lk(mu);
+                write_failed = true;
+                first_error = "Error: can not write to the file [" + grm_file + "].";
+                break;
             }
         }
+        cv_room.notify_all();
+        for (auto& t : th) t.join();
         fclose(f);
+        if (!first_error.empty()) throw first_error;
+        (void)write_failed;
         cout << "The genetic relationship matrix has been saved in the file [" + grm_file + "] (in compressed text format)." << endl;
     }
     const string famfile = _out + ".grm.id";
@@ -410,4 +454,33 @@ void gcta_host::output_grm(const vector<float>& A, const vector<int32_t>& N, boo
     for (int i : _keep) fam << _fid[i] + "\t" + _pid[i] << endl;
     fam.close();
     cout << "IDs for the GRM file [" + grm_file + "] have been saved in the file [" + famfile + "]." << endl;
+}
+
+// `gcta64_b200 --selftest-writer n --out prefix [--make-grm-bin]`: time output_grm on a fabricated GRM of n individuals
+// (values shaped like a real one: diagonal near 1, off-diagonal ~ N(0, 1e-3), N a little below a constant).  Needs no GPU.
+int gcta_host::selftest_writer(int64_t n, bool output_bin)
+{
+    _keep.resize((size_t)n);
+    _fid.resize((size_t)n);
+    _pid.resize((size_t)n);
+    for (int64_t i = 0; i < n; i++) { _keep[(size_t)i] = (int)i; _fid[(size_t)i] = "F" + std::to_string(i); _pid[(size_t)i] = "I" + std::to_string(i); }
+    const size_t tri = (size_t)(n * (n + 1) / 2);
+    vector<float> A(tri);
+    vector<int32_t> N(tri);
+    uint64_t s = 0x9E3779B97F4A7C15ull;
+    auto next = [&]() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return s; };
+    size_t o = 0;
+    for (int64_t i = 0; i < n; i++)
+        for (int64_t j = 0; j <= i; j++, o++) {
+            const uint64_t r = next();
+            // sum of four uniforms, centred: close enough to a normal for the digit statistics
+            const double u = ((double)(r & 0xFFFF) + (double)((r >> 16) & 0xFFFF) + (double)((r >> 32) & 0xFFFF) + (double)(r >> 48)) / 65536.0 - 2.0;
+            A[o] = (float)(i == j ? 1.0 + 0.02 * u : 1.7e-3 * u);
+            N[o] = 500000 - (int32_t)(next() % 20000);
+        }
+    const auto t0 = std::chrono::steady_clock::now();
+    output_grm(A, N, output_bin);
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    printf("writer selftest: n=%lld, %zu pairs, %.3f s, %.1f M pairs/s\n", (long long)n, tri, sec, tri / sec / 1e6);
+    return 0;
 }

@@ -1,0 +1,420 @@
+// grm_text_gz.cpp - structure-aware gzip encoder for the .grm.gz text (see grm_text_gz.h).
+#include "grm_text_gz.h"
+
+#include <zlib.h>   // crc32 only
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <queue>
+
+namespace grm_text_gz {
+
+// ---------------------------------------------------------------------------------------------
+// number formatting
+// ---------------------------------------------------------------------------------------------
+static inline char* put_uint(char* q, uint64_t v)
+{
+    char tmp[24];
+    int k = 0;
+    do { tmp[k++] = (char)('0' + v % 10); v /= 10; } while (v);
+    while (k) *q++ = tmp[--k];
+    return q;
+}
+
+// printf("%.6e") (the reference's `setf(scientific); precision(6)`, grm.cpp:326-327): the value is scaled by an exact
+// power of ten to 7 significant digits; whenever the scaled value is close enough to a rounding boundary for the one
+// floating-point rounding of the scaling to matter (or the exponent is outside the exact-power range) snprintf decides.
+int put_e6(char* q, double v)
+{
+    static const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    char* const q0 = q;
+    const double a = std::fabs(v);
+    if (!(a >= 1e-15 && a < 1e15)) {
+        if (v == 0.0 && !std::signbit(v)) { memcpy(q, "0.000000e+00", 12); return 12; }
+        return snprintf(q, 32, "%.6e", v);
+    }
+    int e2;
+    std::frexp(a, &e2);                                    // a = f * 2^e2, f in [0.5, 1)
+    int e = (int)std::floor((e2 - 1) * 0.30102999566398);  // decimal exponent, possibly one too small
+    for (int attempt = 0; attempt < 3; attempt++) {
+        const int k = 6 - e;   // a * 10^k should lie in [1e6, 1e7)
+        const double scaled = k >= 0 ? a * P10[k] : a / P10[-k];
+        if (scaled < 1e6) { e--; continue; }
+        if (scaled >= 1e7) { e++; continue; }
+        const double fl = std::floor(scaled), frac = scaled - fl;
+        if (std::fabs(frac - 0.5) < 1e-5) return snprintf(q0, 32, "%.6e", v);   // too close to a tie to decide here
+        uint64_t d = (uint64_t)fl + (frac > 0.5 ? 1 : 0);
+        int ee = e;
+        if (d >= 10000000ull) { d = 1000000ull; ee++; }
+        if (std::signbit(v)) *q++ = '-';
+        char dig[7];
+        for (int t = 6; t >= 0; t--) { dig[t] = (char)('0' + d % 10); d /= 10; }
+        *q++ = dig[0]; *q++ = '.';
+        for (int t = 1; t < 7; t++) *q++ = dig[t];
+        *q++ = 'e';
+        if (ee < 0) { *q++ = '-'; ee = -ee; } else *q++ = '+';
+        *q++ = (char)('0' + ee / 10); *q++ = (char)('0' + ee % 10);
+        return (int)(q - q0);
+    }
+    return snprintf(q0, 32, "%.6e", v);
+}
+
+namespace {
+
+// One formatted line and where its four fields start; a field includes the separator that ends it.
+struct Line {
+    char s[96];
+    int fs[5] = {0, 0, 0, 0, 0};   // fs[4] = length of the line
+};
+
+// Formats the lines of one row after another: the row index is formatted once, the column index counts up in place.
+struct RowFormatter {
+    char ipre[24]; int ilen = 0;
+    char jdec[24]; int jlen = 0;   // decimal digits of j + 1, most significant first
+    void start_row(int64_t i)
+    {
+        char* q = put_uint(ipre, (uint64_t)(i + 1));
+        *q++ = '\t';
+        ilen = (int)(q - ipre);
+        jdec[0] = '0'; jlen = 1;   // incremented to "1" by the first next()
+    }
+    inline void bump_j()
+    {
+        int k = jlen - 1;
+        while (k >= 0 && jdec[k] == '9') jdec[k--] = '0';
+        if (k >= 0) jdec[k]++;
+        else { memmove(jdec + 1, jdec, (size_t)jlen); jdec[0] = '1'; jlen++; }
+    }
+    inline void next(Line& L, int32_t Nv, float Av)
+    {
+        bump_j();
+        char* q = L.s;
+        memcpy(q, ipre, (size_t)ilen); q += ilen;
+        L.fs[0] = 0; L.fs[1] = ilen;
+        memcpy(q, jdec, (size_t)jlen); q += jlen; *q++ = '\t';
+        L.fs[2] = (int)(q - L.s);
+        if (Nv < 0) { *q++ = '-'; q = put_uint(q, (uint64_t)(-(int64_t)Nv)); } else q = put_uint(q, (uint64_t)Nv);
+        *q++ = '\t';
+        L.fs[3] = (int)(q - L.s);
+        q += put_e6(q, (double)Av);
+        *q++ = '\n';
+        L.fs[4] = (int)(q - L.s);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// deflate pieces (RFC 1951)
+// ---------------------------------------------------------------------------------------------
+constexpr int NLIT = 286, NDIST = 30, MIN_MATCH = 4, MAX_MATCH = 258;
+const uint16_t LEN_BASE[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
+const uint8_t LEN_EXTRA[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+const uint16_t DIST_BASE[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
+const uint8_t DIST_EXTRA[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
+
+inline int len_symbol(int len)   // index into LEN_BASE
+{
+    int k = 28;
+    while (LEN_BASE[k] > len) k--;
+    return k;
+}
+inline int dist_symbol(int dist)
+{
+    int k = 29;
+    while (DIST_BASE[k] > dist) k--;
+    return k;
+}
+
+// Huffman code lengths (<= limit) for freq[0..n); symbols with freq 0 get length 0.
+void huffman_lengths(const uint32_t* freq, int n, int limit, uint8_t* len)
+{
+    std::vector<uint64_t> f(freq, freq + n);
+    for (;;) {
+        struct Node { uint64_t w; int a, b; };
+        std::vector<Node> nodes;
+        typedef std::pair<uint64_t, int> QE;
+        std::priority_queue<QE, std::vector<QE>, std::greater<QE>> pq;
+        for (int i = 0; i < n; i++)
+            if (f[i]) { nodes.push_back({f[i], -1 - i, 0}); pq.push({f[i], (int)nodes.size() - 1}); }
+        std::fill(len, len + n, 0);
+        if (nodes.empty()) return;
+        if (nodes.size() == 1) { len[-1 - nodes[0].a] = 1; return; }
+        while (pq.size() > 1) {
+            QE x = pq.top(); pq.pop();
+            QE y = pq.top(); pq.pop();
+            nodes.push_back({x.first + y.first, x.second, y.second});
+            pq.push({x.first + y.first, (int)nodes.size() - 1});
+        }
+        // depths, root = last node
+        std::vector<int> depth(nodes.size(), 0);
+        int maxd = 0;
+        for (int k = (int)nodes.size() - 1; k >= 0; k--) {
+            if (nodes[k].a < 0) { len[-1 - nodes[k].a] = (uint8_t)std::min(depth[k], 255); maxd = std::max(maxd, depth[k]); }
+            else { depth[nodes[k].a] = depth[k] + 1; depth[nodes[k].b] = depth[k] + 1; }
+        }
+        if (maxd <= limit) return;
+        for (int i = 0; i < n; i++)
+            if (f[i]) f[i] = (f[i] + 1) / 2;   // flatten and retry
+    }
+}
+
+// canonical codes, bit-reversed for the LSB-first bit stream
+void canonical_codes(const uint8_t* len, int n, uint16_t* code)
+{
+    int bl_count[16] = {0};
+    for (int i = 0; i < n; i++) bl_count[len[i]]++;
+    bl_count[0] = 0;
+    int next_code[16] = {0}, c = 0;
+    for (int b = 1; b <= 15; b++) { c = (c + bl_count[b - 1]) << 1; next_code[b] = c; }
+    for (int i = 0; i < n; i++) {
+        if (!len[i]) { code[i] = 0; continue; }
+        int v = next_code[len[i]]++, r = 0;
+        for (int b = 0; b < len[i]; b++) { r = (r << 1) | (v & 1); v >>= 1; }
+        code[i] = (uint16_t)r;
+    }
+}
+
+// LSB-first bit stream into a 1 MiB staging buffer that is appended to `out` whenever it runs low (the caller calls
+// room() once per line; a line never needs more than a few hundred bytes).
+struct BitWriter {
+    std::string& out;
+    std::vector<unsigned char> buf;
+    unsigned char* p;
+    uint64_t acc = 0;
+    int nbits = 0;
+    explicit BitWriter(std::string& o) : out(o), buf(1 << 20), p(buf.data()) {}
+    inline void put(uint32_t v, int n)
+    {
+        acc |= (uint64_t)v << nbits;
+        nbits += n;
+        if (nbits >= 32) {
+            const uint32_t w = (uint32_t)acc;
+            p[0] = (unsigned char)w; p[1] = (unsigned char)(w >> 8); p[2] = (unsigned char)(w >> 16); p[3] = (unsigned char)(w >> 24);
+            p += 4;
+            acc >>= 32;
+            nbits -= 32;
+        }
+    }
+    inline void room()
+    {
+        if ((size_t)(p - buf.data()) + 4096 > buf.size()) { out.append((const char*)buf.data(), (size_t)(p - buf.data())); p = buf.data(); }
+    }
+    void finish()
+    {
+        while (nbits > 0) { *p++ = (unsigned char)(acc & 255); acc >>= 8; nbits -= 8; }
+        nbits = 0;
+        out.append((const char*)buf.data(), (size_t)(p - buf.data()));
+        p = buf.data();
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// the tokeniser: line -> shared runs with the previous line + literals
+// ---------------------------------------------------------------------------------------------
+struct CountSink {
+    uint32_t lit[NLIT] = {0}, dist[NDIST] = {0};
+    inline void literal(uint8_t b) { lit[b]++; }
+    inline void match(int len, int d) { lit[257 + len_symbol(len)]++; dist[dist_symbol(d)]++; }
+};
+
+struct EmitSink {
+    BitWriter& bw;
+    const uint16_t* lcode; const uint8_t* llen; const uint16_t* dcode; const uint8_t* dlen;
+    // per match length / small distance: symbol + extra bits folded into one (value, nbits) pair
+    uint32_t mlen_bits[MAX_MATCH + 1]; uint8_t mlen_n[MAX_MATCH + 1];
+    uint32_t mdist_bits[513]; uint8_t mdist_n[513];
+    EmitSink(BitWriter& b, const uint16_t* lc, const uint8_t* ll, const uint16_t* dc, const uint8_t* dl) : bw(b), lcode(lc), llen(ll), dcode(dc), dlen(dl)
+    {
+        for (int len = 3; len <= MAX_MATCH; len++) {
+            const int k = len_symbol(len);
+            mlen_bits[len] = lcode[257 + k] | ((uint32_t)(len - LEN_BASE[k]) << llen[257 + k]);
+            mlen_n[len] = (uint8_t)(llen[257 + k] + LEN_EXTRA[k]);
+        }
+        for (int d = 1; d <= 512; d++) {
+            const int k = dist_symbol(d);
+            mdist_bits[d] = dcode[k] | ((uint32_t)(d - DIST_BASE[k]) << dlen[k]);
+            mdist_n[d] = (uint8_t)(dlen[k] + DIST_EXTRA[k]);
+        }
+    }
+    inline void literal(uint8_t b) { bw.put(lcode[b], llen[b]); }
+    inline void match(int len, int d)
+    {
+        bw.put(mlen_bits[len], mlen_n[len]);
+        if (d <= 512) bw.put(mdist_bits[d], mdist_n[d]);
+        else {
+            const int k = dist_symbol(d);
+            bw.put(dcode[k], dlen[k]);
+            bw.put((uint32_t)(d - DIST_BASE[k]), DIST_EXTRA[k]);
+        }
+    }
+};
+
+template <class Sink>
+struct Tokeniser {
+    Sink& sink;
+    int run_len = 0, run_dist = 0;
+    uint8_t run_head[MIN_MATCH];   // first bytes of the pending run, in case it ends up too short for a match
+    explicit Tokeniser(Sink& s) : sink(s) {}
+
+    inline void flush_run()
+    {
+        if (run_len >= MIN_MATCH) sink.match(run_len, run_dist);
+        else for (int k = 0; k < run_len; k++) sink.literal(run_head[k]);
+        run_len = 0;
+    }
+    inline void add_run(const char* bytes, int len, int dist)
+    {
+        if (len <= 0) return;
+        if (run_len > 0 && (run_dist != dist || run_len + len > MAX_MATCH)) flush_run();
+        for (int k = 0; k < len && run_len + k < MIN_MATCH; k++) run_head[run_len + k] = (uint8_t)bytes[k];
+        run_len += len;
+        run_dist = dist;
+    }
+    inline void add_literals(const char* bytes, int len)
+    {
+        if (len <= 0) return;
+        flush_run();
+        for (int k = 0; k < len; k++) sink.literal((uint8_t)bytes[k]);
+    }
+    // `prev` == nullptr: first line of a member (nothing to refer to)
+    inline void line(const Line& cur, const Line* prev)
+    {
+        if (!prev) { add_literals(cur.s, cur.fs[4]); return; }
+        const int pl = prev->fs[4];
+        for (int f = 0; f < 4; f++) {
+            const int cs = cur.fs[f], ce = cur.fs[f + 1], ps = prev->fs[f], pe = prev->fs[f + 1];
+            const int clen = ce - cs, plen = pe - ps, mn = std::min(clen, plen);
+            int c = 0;
+            while (c < mn && cur.s[cs + c] == prev->s[ps + c]) c++;
+            add_run(cur.s + cs, c, pl + cs - ps);
+            if (c == clen && c == plen) continue;   // the field repeats as a whole
+            int t = 0;
+            while (t < mn - c && cur.s[ce - 1 - t] == prev->s[pe - 1 - t]) t++;
+            add_literals(cur.s + cs + c, clen - c - t);
+            add_run(cur.s + ce - t, t, pl + ce - pe);
+        }
+    }
+};
+
+inline void put_le32(std::string& out, uint32_t v)
+{
+    char b[4] = {(char)(v & 255), (char)((v >> 8) & 255), (char)((v >> 16) & 255), (char)(v >> 24)};
+    out.append(b, 4);
+}
+
+}  // namespace
+
+void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& text)
+{
+    RowFormatter rf;
+    Line L;
+    for (int64_t i = row_begin; i < row_end; i++) {
+        rf.start_row(i);
+        const size_t base = (size_t)(i * (i + 1) / 2);
+        for (int64_t j = 0; j <= i; j++) {
+            rf.next(L, N[base + j], A[base + j]);
+            text.append(L.s, (size_t)L.fs[4]);
+        }
+    }
+}
+
+void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& out)
+{
+    // ---- pass 1: symbol statistics from a sample of the member's lines (runs of consecutive lines from 16 rows) ----
+    CountSink cs;
+    {
+        Tokeniser<CountSink> tk(cs);
+        RowFormatter rf;
+        Line buf[2];
+        const int64_t rows = row_end - row_begin;
+        const int64_t nsample = std::min<int64_t>(16, rows);
+        for (int64_t s = 0; s < nsample; s++) {
+            const int64_t i = row_begin + (nsample > 1 ? s * (rows - 1) / (nsample - 1) : 0);
+            rf.start_row(i);
+            const size_t base = (size_t)(i * (i + 1) / 2);
+            const int64_t cnt = std::min<int64_t>(i + 1, 512);
+            const Line* prev = nullptr;
+            // the last `cnt` lines of the row (the widest column indices) would be as good; the first are simplest
+            for (int64_t j = 0; j < cnt; j++) {
+                Line& cur = buf[j & 1];
+                rf.next(cur, N[base + j], A[base + j]);
+                tk.line(cur, prev);
+                prev = &cur;
+            }
+            tk.flush_run();
+        }
+    }
+    // every symbol keeps a code: the sample need not have seen everything the member holds
+    for (int k = 0; k < NLIT; k++) cs.lit[k] = cs.lit[k] * 16 + 1;
+    for (int k = 0; k < NDIST; k++) cs.dist[k] = cs.dist[k] * 16 + 1;
+    uint8_t llen[NLIT], dlen[NDIST];
+    uint16_t lcode[NLIT], dcode[NDIST];
+    huffman_lengths(cs.lit, NLIT, 15, llen);
+    huffman_lengths(cs.dist, NDIST, 15, dlen);
+    canonical_codes(llen, NLIT, lcode);
+    canonical_codes(dlen, NDIST, dcode);
+
+    // ---- gzip member header (RFC 1952) and the dynamic-Huffman block header (RFC 1951, 3.2.7) ----
+    static const char GZ_HEADER[10] = {(char)0x1f, (char)0x8b, 8, 0, 0, 0, 0, 0, 0, 3};
+    out.append(GZ_HEADER, 10);
+    BitWriter bw(out);
+    bw.put(1, 1);   // BFINAL
+    bw.put(2, 2);   // BTYPE = dynamic Huffman
+    bw.put(NLIT - 257, 5);
+    bw.put(NDIST - 1, 5);
+    bw.put(19 - 4, 4);
+    uint32_t clfreq[19] = {0};
+    for (int k = 0; k < NLIT; k++) clfreq[llen[k]]++;
+    for (int k = 0; k < NDIST; k++) clfreq[dlen[k]]++;
+    uint8_t cllen[19];
+    uint16_t clcode[19];
+    huffman_lengths(clfreq, 19, 7, cllen);
+    canonical_codes(cllen, 19, clcode);
+    static const int CL_ORDER[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+    for (int k = 0; k < 19; k++) bw.put(cllen[CL_ORDER[k]], 3);
+    for (int k = 0; k < NLIT; k++) bw.put(clcode[llen[k]], cllen[llen[k]]);     // plain lengths, no repeat codes:
+    for (int k = 0; k < NDIST; k++) bw.put(clcode[dlen[k]], cllen[dlen[k]]);    // ~250 bytes per member
+
+    // ---- pass 2: format, tokenise and emit every line; CRC of the text in 32 KiB pieces ----
+    EmitSink es(bw, lcode, llen, dcode, dlen);
+    Tokeniser<EmitSink> tk(es);
+    RowFormatter rf;
+    Line buf[2];
+    int which = 0;
+    const Line* prev = nullptr;
+    constexpr size_t STAGE = 1 << 15;
+    std::vector<char> stage(STAGE + sizeof(Line::s));
+    size_t staged = 0;
+    uLong crc = crc32(0L, Z_NULL, 0);
+    uint64_t isize = 0;
+    for (int64_t i = row_begin; i < row_end; i++) {
+        rf.start_row(i);
+        const size_t base = (size_t)(i * (i + 1) / 2);
+        for (int64_t j = 0; j <= i; j++) {
+            Line& cur = buf[which];
+            which ^= 1;
+            rf.next(cur, N[base + j], A[base + j]);
+            bw.room();
+            tk.line(cur, prev);
+            prev = &cur;
+            memcpy(stage.data() + staged, cur.s, (size_t)cur.fs[4]);
+            staged += (size_t)cur.fs[4];
+            if (staged >= STAGE) {
+                crc = crc32(crc, (const Bytef*)stage.data(), (uInt)staged);
+                isize += staged;
+                staged = 0;
+            }
+        }
+    }
+    tk.flush_run();
+    crc = crc32(crc, (const Bytef*)stage.data(), (uInt)staged);
+    isize += staged;
+    bw.put(lcode[256], llen[256]);   // end of block
+    bw.finish();
+    put_le32(out, (uint32_t)crc);
+    put_le32(out, (uint32_t)(isize & 0xFFFFFFFFull));
+}
+
+}  // namespace grm_text_gz

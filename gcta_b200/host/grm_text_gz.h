@@ -1,0 +1,33 @@
+// grm_text_gz.h - the ".grm.gz" text of output_grm_vec (grm.cpp:321-331) written as gzip members by an encoder that knows
+// the line structure, instead of formatting into a buffer and handing that to zlib's deflate.
+//
+// A line is "i \t j \t N \t A \n".  Against the line before it, every field either repeats, shares a prefix (i, the
+// leading digits of j and N) or a suffix (the exponent of A), and the rest is close to random digits.  A general LZ77
+// match search spends nearly all of its time discovering exactly that, line after line.  The encoder below compares
+// each field with the same field of the previous line (a handful of byte compares), emits the shared runs as deflate
+// <length, distance> pairs - the distance follows from the two lines' field offsets, no hash chains - and the rest as
+// literals, all through one dynamic Huffman code per member built from a sample of the member's own lines.
+// The output is plain RFC 1951/1952: gzread, zcat and the reference's reader (read_grm_gz, grm.cpp:381-448, through
+// zfstream.cpp's gzifstream) decode it like any other gzip file.
+#ifndef GCTA_B200_GRM_TEXT_GZ_H
+#define GCTA_B200_GRM_TEXT_GZ_H
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace grm_text_gz {
+
+// Formats "%.6e" exactly like printf (falls back to snprintf near rounding ties); returns the length.
+int put_e6(char* q, double v);
+
+// One gzip member holding the lines of rows [row_begin, row_end) of the packed lower triangle (1-based indices in the
+// text, j <= i; A and N indexed by i(i+1)/2 + j).  Appends to `out`.
+void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& out);
+
+// The same text, uncompressed (tests; the zlib route of the writer).
+void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& text);
+
+}  // namespace grm_text_gz
+
+#endif

@@ -131,10 +131,19 @@ static void option(int argc, char* argv_in[])
 }
 
 int gcta_host_selftest_format();   // gcta_host_grm.cpp
+int gcta_host_selftest_gz();
 
 int main(int argc, char* argv[])
 {
     if (argc == 2 && strcmp(argv[1], "--selftest-format") == 0) return gcta_host_selftest_format();
+    if (argc == 2 && strcmp(argv[1], "--selftest-gz") == 0) return gcta_host_selftest_gz();
+    if (argc >= 5 && strcmp(argv[1], "--selftest-writer") == 0 && strcmp(argv[3], "--out") == 0) {
+        // gcta64_b200 --selftest-writer n --out prefix [--make-grm-bin]
+        try {
+            gcta_host g(22, -1.0, argv[4]);
+            return g.selftest_writer(atoll(argv[2]), argc >= 6 && strcmp(argv[5], "--make-grm-bin") == 0);
+        } catch (const string& err_msg) { cerr << err_msg << endl; return 1; }
+    }
     cout << "*******************************************************************" << endl;
     cout << "* Genome-wide Complex Trait Analysis (GCTA)" << endl;
     cout << "* version 0.93.9 - B200 build of the --make-grm path (" << gcta_b200_version() << ")" << endl;

@@ -50,6 +50,53 @@ def test_fast_number_formatter_equals_printf():
     assert r.returncode == 0 and "0 mismatches" in r.stdout, r.stdout + r.stderr
 
 
+def test_structured_gz_encoder_on_awkward_inputs():
+    """--selftest-gz: single lines, constant fields (runs merged across lines), NaN/inf/denormal A, extreme N, row
+    ranges from the middle of the triangle, an empty range - each member inflated by zlib and compared with the text."""
+    r = subprocess.run([BIN, "--selftest-gz"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=120)
+    assert r.returncode == 0 and " 0 failures" in r.stdout, r.stdout + r.stderr
+
+
+def _selftest_writer(n, prefix, cwd, env=None, extra=()):
+    e = dict(os.environ)
+    e.pop("GCTA_B200_GZ_LEVEL", None)
+    e.update(env or {})
+    r = subprocess.run([BIN, "--selftest-writer", str(n), "--out", prefix, *extra], cwd=cwd, env=e, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True, timeout=300)
+    assert r.returncode == 0 and "writer selftest" in r.stdout, r.stdout + r.stderr
+    return r
+
+
+def test_structured_gz_encoder_writes_the_same_text_as_zlib(tmp_path):
+    """The default .grm.gz codec (host/grm_text_gz.cpp: shared runs with the previous line as deflate matches, one
+    dynamic Huffman code per member) must decode - with a stock gzip reader, CRC and length checked - to exactly the
+    text the formatter + zlib route gives; several members (n = 1600: 1.28 M lines), first rows included."""
+    import gzip
+    _selftest_writer(1600, "a", tmp_path)
+    _selftest_writer(1600, "b", tmp_path, env={"GCTA_B200_GZ_LEVEL": "6"})
+    raw = open(tmp_path / "a.grm.gz", "rb").read()
+    assert raw[:4] == b"\x1f\x8b\x08\x00" and raw.count(b"\x1f\x8b\x08\x00") >= 2
+    ta, tb = gzip.decompress(raw), gzip.decompress(open(tmp_path / "b.grm.gz", "rb").read())
+    assert ta == tb
+    lines = ta.split(b"\n")
+    assert len(lines) == 1600 * 1601 // 2 + 1 and lines[-1] == b""
+    assert lines[0].split(b"\t")[:2] == [b"1", b"1"] and lines[-2].split(b"\t")[:2] == [b"1600", b"1600"]
+    assert len(raw) < 0.45 * len(ta)   # random 7-digit mantissas cap any deflate stream near 2.6-2.9x
+    assert open(tmp_path / "a.grm.id").read().splitlines()[:2] == ["F0\tI0", "F1\tI1"]
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
+def test_reference_reader_accepts_the_structured_gz(tmp_path):
+    """SURVEY.md 8f-1 without a GPU: the reference's read_grm_gz (grm.cpp:381-448, gzifstream of zfstream.cpp) reads the
+    encoder's members and re-saves the same matrix."""
+    _selftest_writer(1500, "mine", tmp_path)
+    rr = oracle.run_ref(["--grm", "mine", "--make-grm", "--out", "re"], cwd=tmp_path)
+    assert "Analysis finished" in rr.stdout and rr.stderr.strip() == "", rr.stderr
+    A, N, _ = grmio.read_grm_gz(str(tmp_path / "mine.grm.gz"))
+    A2, N2, _ = grmio.read_grm_gz(str(tmp_path / "re.grm.gz"))
+    assert np.array_equal(N, N2) and np.abs(A - A2).max() <= 1e-6 * max(1.0, np.abs(A).max())
+
+
 @pytest.mark.parametrize("case,args,log", [
     ("g8_errors", ["--bfile", "t", "--make-grm", "--out", "o"], "ref_stdout_o.txt"),                # chr 23 without --autosome
     ("g8_errors", ["--bfile", "missing_prefix", "--make-grm", "--out", "o2"], "ref_stdout_o2.txt"),  # cannot open .fam
