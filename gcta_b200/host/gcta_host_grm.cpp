@@ -270,6 +270,26 @@ int gcta_host_selftest_format()
         check(v);
         if ((i & 7) == 0) check((double)(int64_t)(next() % 20000000) / 1e7 * ((r & 2) ? 1e-3 : 1.0));   // near 7-digit decimals
     }
+    // put_g15 (the re-save path's "%.15g"): decimals of up to 7 digits parsed by strtod (what a .grm.gz holds), full
+    // doubles (merged GRMs), and the notation switches at 1e-5 and 1e15
+    auto check15 = [&](double v) {
+        const int la = grm_text_gz::put_g15(a, v);
+        a[la] = 0;
+        snprintf(b, sizeof b, "%.15g", v);
+        total++;
+        if (strcmp(a, b) != 0 && bad++ < 5) fprintf(stderr, "mismatch (%%.15g): %s vs %s\n", a, b);
+    };
+    const double specials15[] = {0.0, -0.0, 1.0, -1.0, 10.0, 100.0, 1e14, 9.999999e14, 1e15, 1e-4, 1e-5, 9.999999e-5, 1.5, 0.1, 0.3, 1234567.0, 12345670.0,
+                                 1.234567e-3, 123456.7, 1e-15, 1e-16, 1.0 / 3.0, 2.0 / 3.0, 1e22, 123456789012345.0, 1234567890123456.0};
+    for (double v : specials15) check15(v);
+    for (int i = 0; i < 2000000; i++) {
+        char txt[40];
+        const uint64_t r = next();
+        snprintf(txt, sizeof txt, "%s%d.%06de%+03d", (r & 1) ? "-" : "", (int)(1 + next() % 9), (int)(next() % 1000000), (int)(next() % 30) - 15);
+        check15(strtod(txt, nullptr));                                             // a value as read from a .grm.gz
+        if ((i & 3) == 0) check15(std::ldexp((double)(next() >> 11), (int)(next() % 100) - 103));   // arbitrary doubles
+        if ((i & 15) == 0) check15((double)(int64_t)(next() % 20000000) * 1e-3);   // short decimals in fixed notation
+    }
     printf("format selftest: %ld values, %ld mismatches\n", total, bad);
     return bad ? 1 : 0;
 }

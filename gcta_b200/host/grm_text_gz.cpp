@@ -62,6 +62,57 @@ int put_e6(char* q, double v)
     return snprintf(q0, 32, "%.6e", v);
 }
 
+// printf("%.15g") (iostream's default float format at precision 15, which is what the reference's GRM re-save prints,
+// grm.cpp:367).  Fast path for the common case there - a double that was itself read from a decimal of at most seven
+// significant digits: such a value prints as that decimal (the double is within 1.2e-16 relative of it, far less than
+// half a unit of the 15th digit), so the digits are recovered by one exact scaling and checked by scaling back.
+// Everything else goes to snprintf.
+int put_g15(char* q, double v)
+{
+    static const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    char* const q0 = q;
+    const double a = std::fabs(v);
+    if (v == 0.0 && !std::signbit(v)) { *q = '0'; return 1; }
+    if (!(a >= 1e-15 && a < 1e15)) return snprintf(q, 40, "%.15g", v);
+    int e2;
+    std::frexp(a, &e2);
+    int e = (int)std::floor((e2 - 1) * 0.30102999566398);
+    for (int attempt = 0; attempt < 3; attempt++) {
+        const int k = 6 - e;
+        const double scaled = k >= 0 ? a * P10[k] : a / P10[-k];
+        if (scaled < 1e6) { e--; continue; }
+        if (scaled >= 1e7) { e++; continue; }
+        uint64_t m = (uint64_t)(scaled + 0.5);
+        int X = e;
+        if (m >= 10000000ull) { m = 1000000ull; X++; }
+        const int kk = 6 - X;
+        const double back = kk >= 0 ? (double)m / P10[kk] : (double)m * P10[-kk];
+        if (back != a) break;   // not a short decimal: let snprintf do it
+        char dig[7];
+        for (int t = 6; t >= 0; t--) { dig[t] = (char)('0' + m % 10); m /= 10; }
+        int nd = 7;
+        while (nd > 1 && dig[nd - 1] == '0') nd--;
+        if (std::signbit(v)) *q++ = '-';
+        if (X < -4 || X >= 15) {
+            *q++ = dig[0];
+            if (nd > 1) { *q++ = '.'; for (int t = 1; t < nd; t++) *q++ = dig[t]; }
+            *q++ = 'e';
+            int ee = X;
+            if (ee < 0) { *q++ = '-'; ee = -ee; } else *q++ = '+';
+            *q++ = (char)('0' + ee / 10); *q++ = (char)('0' + ee % 10);
+        } else if (X >= 0) {
+            for (int t = 0; t <= X; t++) *q++ = t < nd ? dig[t] : '0';
+            if (nd > X + 1) { *q++ = '.'; for (int t = X + 1; t < nd; t++) *q++ = dig[t]; }
+        } else {
+            *q++ = '0'; *q++ = '.';
+            for (int t = 0; t < -X - 1; t++) *q++ = '0';
+            for (int t = 0; t < nd; t++) *q++ = dig[t];
+        }
+        return (int)(q - q0);
+    }
+    return snprintf(q0, 40, "%.15g", v);
+}
+
 namespace {
 
 // One formatted line and where its four fields start; a field includes the separator that ends it.
@@ -88,7 +139,8 @@ struct RowFormatter {
         if (k >= 0) jdec[k]++;
         else { memmove(jdec + 1, jdec, (size_t)jlen); jdec[0] = '1'; jlen++; }
     }
-    inline void next(Line& L, int32_t Nv, float Av)
+    // fields 0..2 ("i \t", "j \t", "N \t"); returns where the value field starts
+    inline char* head(Line& L, int32_t Nv)
     {
         bump_j();
         char* q = L.s;
@@ -99,10 +151,35 @@ struct RowFormatter {
         if (Nv < 0) { *q++ = '-'; q = put_uint(q, (uint64_t)(-(int64_t)Nv)); } else q = put_uint(q, (uint64_t)Nv);
         *q++ = '\t';
         L.fs[3] = (int)(q - L.s);
+        return q;
+    }
+    // output_grm_vec's line (grm.cpp:328-330): A in scientific notation, 6 decimals
+    inline void next(Line& L, int32_t Nv, float Av)
+    {
+        char* q = head(L, Nv);
         q += put_e6(q, (double)Av);
         *q++ = '\n';
         L.fs[4] = (int)(q - L.s);
     }
+    // output_grm_MatrixXf's line (grm.cpp:367): `setprecision(15) << double`, i.e. printf("%.15g")
+    inline void next15(Line& L, int32_t Nv, double Av)
+    {
+        char* q = head(L, Nv);
+        q += put_g15(q, Av);
+        *q++ = '\n';
+        L.fs[4] = (int)(q - L.s);
+    }
+};
+
+// the two sources of lines: the packed float/int32 triangle of make_grm, and the packed double/double one of the
+// GRM re-save path (N is printed as `(int)N`, grm.cpp:367)
+struct SrcE6 {
+    const float* A; const int32_t* N;
+    inline void fill(RowFormatter& rf, Line& L, size_t o) const { rf.next(L, N[o], A[o]); }
+};
+struct SrcG15 {
+    const double* A; const double* N;
+    inline void fill(RowFormatter& rf, Line& L, size_t o) const { rf.next15(L, (int32_t)N[o], A[o]); }
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -306,7 +383,8 @@ inline void put_le32(std::string& out, uint32_t v)
 
 }  // namespace
 
-void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& text)
+template <class Src>
+static void format_impl(const Src& src, int64_t row_begin, int64_t row_end, std::string& text)
 {
     RowFormatter rf;
     Line L;
@@ -314,13 +392,14 @@ void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t ro
         rf.start_row(i);
         const size_t base = (size_t)(i * (i + 1) / 2);
         for (int64_t j = 0; j <= i; j++) {
-            rf.next(L, N[base + j], A[base + j]);
+            src.fill(rf, L, base + j);
             text.append(L.s, (size_t)L.fs[4]);
         }
     }
 }
 
-void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& out)
+template <class Src>
+static void encode_impl(const Src& src, int64_t row_begin, int64_t row_end, std::string& out)
 {
     // ---- pass 1: symbol statistics from a sample of the member's lines (runs of consecutive lines from 16 rows) ----
     CountSink cs;
@@ -339,7 +418,7 @@ void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t ro
             // the last `cnt` lines of the row (the widest column indices) would be as good; the first are simplest
             for (int64_t j = 0; j < cnt; j++) {
                 Line& cur = buf[j & 1];
-                rf.next(cur, N[base + j], A[base + j]);
+                src.fill(rf, cur, base + j);
                 tk.line(cur, prev);
                 prev = &cur;
             }
@@ -395,7 +474,7 @@ void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t ro
         for (int64_t j = 0; j <= i; j++) {
             Line& cur = buf[which];
             which ^= 1;
-            rf.next(cur, N[base + j], A[base + j]);
+            src.fill(rf, cur, base + j);
             bw.room();
             tk.line(cur, prev);
             prev = &cur;
@@ -415,6 +494,23 @@ void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t ro
     bw.finish();
     put_le32(out, (uint32_t)crc);
     put_le32(out, (uint32_t)(isize & 0xFFFFFFFFull));
+}
+
+void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& text)
+{
+    format_impl(SrcE6{A, N}, row_begin, row_end, text);
+}
+void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& out)
+{
+    encode_impl(SrcE6{A, N}, row_begin, row_end, out);
+}
+void format_rows_g15(const double* A, const double* N, int64_t row_begin, int64_t row_end, std::string& text)
+{
+    format_impl(SrcG15{A, N}, row_begin, row_end, text);
+}
+void encode_rows_g15(const double* A, const double* N, int64_t row_begin, int64_t row_end, std::string& out)
+{
+    encode_impl(SrcG15{A, N}, row_begin, row_end, out);
 }
 
 }  // namespace grm_text_gz

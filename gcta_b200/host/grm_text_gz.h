@@ -28,6 +28,12 @@ void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t ro
 // The same text, uncompressed (tests; the zlib route of the writer).
 void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& text);
 
+// The GRM re-save path (output_grm_MatrixXf, grm.cpp:343-380): matrices held in double, line "i \t j \t (int)N \t A"
+// with A printed like `setprecision(15) << double`, i.e. printf("%.15g").
+int put_g15(char* q, double v);
+void encode_rows_g15(const double* A, const double* N, int64_t row_begin, int64_t row_end, std::string& out);
+void format_rows_g15(const double* A, const double* N, int64_t row_begin, int64_t row_end, std::string& text);
+
 }  // namespace grm_text_gz
 
 #endif
