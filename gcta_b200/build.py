@@ -52,7 +52,7 @@ def build(verbose: bool = False, force: bool = False) -> str:
 
 
 HOST_BIN = os.path.join(HERE, "gcta64_b200")
-HOST_SOURCES = ["main.cpp", "gcta_host.cpp", "gcta_host_grm.cpp", "grm_text_gz.cpp"]
+HOST_SOURCES = ["main.cpp", "gcta_host.cpp", "gcta_host_grm.cpp", "gcta_host_grmio.cpp", "grm_text_gz.cpp"]
 
 
 def build_host(force: bool = False) -> str:

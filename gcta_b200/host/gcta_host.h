@@ -43,6 +43,12 @@ public:
 
     int selftest_writer(int64_t n, bool output_bin);      // times output_grm on a fabricated GRM (no GPU)
 
+    // consumer side of the .grm.gz: --grm / --mgrm with --make-grm[-bin], grm.cpp:343-654.  Host only,
+    // like the reference (O(n^2) text and arithmetic); gcta_host_grmio.cpp
+    void save_grm(const std::string& grm_file, const std::string& keep_indi_file, const std::string& remove_indi_file,
+                  const std::string& sex_file, double grm_cutoff, double adj_grm_fac, int dosage_compen, bool merge_grm_flag,
+                  bool output_grm_bin);                    // grm.cpp:572-577
+
     // device options (not in the reference)
     int operand = 0;      // GCTA_B200_FP16
     int n_gpus = 1;       // row bands computed one after another on devices 0..n_gpus-1 of this process
@@ -57,6 +63,19 @@ private:
     void check_sex() const;                               // grm.cpp:29-34
     void rm_high_ld();                                    // data.cpp:1194-1196 (default: no-op)
     void output_grm(const std::vector<float>& A, const std::vector<int32_t>& N, bool output_bin);   // grm.cpp:303-341
+    void read_grm_gz(const std::string& grm_file, std::vector<std::string>& grm_id, bool out_id_log = true, bool read_id_only = false);   // grm.cpp:381-448
+    void merge_grm(const std::string& merge_grm_file);    // grm.cpp:608-654
+    void rm_cor_indi(double grm_cutoff);                  // grm.cpp:450-493
+    void adj_grm(double adj_grm_fac);                     // grm.cpp:495-522
+    void dc(int dosage_compen);                           // grm.cpp:524-541
+    void manipulate_grm(const std::string& grm_file, const std::string& keep_indi_file, const std::string& remove_indi_file,
+                        const std::string& sex_file, double grm_cutoff, double adj_grm_fac, int dosage_compen, bool merge_grm_flag);   // grm.cpp:544-570
+    void output_grm_g15(bool output_grm_bin);             // output_grm_MatrixXf, grm.cpp:343-380
+    // the GRM as read back: packed lower triangle of dimension _grm_dim, doubles like the reference's default build
+    // (gcta.h:43 eigenMatrix = MatrixXd); element (i, j), i >= j, at i(i+1)/2 + j
+    std::vector<double> _grm, _grm_N;
+    int64_t _grm_dim = 0;
+    double& grm_at(std::vector<double>& M, int64_t i, int64_t j);
     static void read_snplist(const std::string& file, std::vector<std::string>& list, const std::string& msg = "SNPs");
     static void read_indi_list(const std::string& file, std::vector<std::string>& list);
     static void update_id_map_kp(const std::vector<std::string>& ids, std::map<std::string, int>& id_map, std::vector<int>& keep);

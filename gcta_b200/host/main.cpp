@@ -25,7 +25,10 @@ static void option(int argc, char* argv_in[])
     string bfile, update_sex_file, update_freq_file, update_refA_file, kp_indi_file, rm_indi_file, extract_snp_file,
         exclude_snp_file, extract_snp_name, exclude_snp_name, out = "gcta";
     bool bfile_flag = false, out_freq_flag = false, autosome_flag = false, make_grm_flag = false, make_grm_xchr_flag = false,
-         grm_out_bin_flag = false;
+         grm_out_bin_flag = false, grm_flag = false, m_grm_flag = false, pca_flag = false;
+    string grm_file;
+    double grm_adj_fac = -2.0, grm_cutoff = -2.0;
+    int dosage_compen = -2;
     int autosome_num = 22, extract_chr_start = 0, extract_chr_end = 0, grm_mtd = 0, n_gpus = 1, operand = GCTA_B200_FP16;
     long long chunk_snps = 0;
     double maf = 0.0, max_maf = 0.0, rm_high_ld_cutoff = -1.0;
@@ -81,6 +84,33 @@ static void option(int argc, char* argv_in[])
             cout << "--rm-high-ld " << rm_high_ld_cutoff << endl;
             if (rm_high_ld_cutoff <= 0 || rm_high_ld_cutoff >= 1) throw("\nError: the value to be specified after --rm-high-ld should be within the range from 0 to 1.\n");
         }
+        // ---- consumer side of the GRM files (option.cpp:267-276, 305-327) ----
+        else if (is("--mgrm")) { m_grm_flag = true; grm_file = argv[++i]; cout << "--mgrm " << grm_file << endl; }
+        else if (is("--grm")) { grm_flag = true; grm_file = argv[++i]; cout << "--grm " << grm_file << endl; }
+        else if (is("--grm-adj")) {
+            grm_adj_fac = atof(argv[++i]);
+            cout << "--grm-adj " << grm_adj_fac << endl;
+            if (grm_adj_fac < 0 || grm_adj_fac > 1) throw("\nError: the value to be specified after --grm-adj should be within the range from 0 to 1.\n");
+        }
+        else if (is("--dc")) {
+            dosage_compen = atoi(argv[++i]);
+            cout << "--dc " << dosage_compen << endl;
+            if (dosage_compen != 0 && dosage_compen != 1) throw("\nError: the value to be specified after --dc should be 0 or 1.\n");
+        }
+        else if (is("--grm-cutoff")) {
+            grm_cutoff = atof(argv[++i]);
+            cout << "--grm-cutoff " << grm_cutoff << endl;
+            if (grm_cutoff < 0 || grm_cutoff > 1) throw("\nError: the value to be specified after --grm-cutoff should be within the range from 0 to 1.\n");
+        }
+        else if (is("--pca")) {   // optional count (option.cpp:320-327); the analysis itself is not part of this build
+            pca_flag = true;
+            int out_pc_num = 20;
+            i++;
+            if (strcmp(argv[i], "gcta") == 0 || strncmp(argv[i], "--", 2) == 0) i--;
+            else out_pc_num = atoi(argv[i]);
+            cout << "--pca " << out_pc_num << endl;
+            if (out_pc_num < 1) throw("\nError: the value to be specified after --pca should be positive.\n");
+        }
         else if (is("--make-grm")) { make_grm_flag = true; cout << "--make-grm" << endl; }
         else if (is("--make-grm-xchr")) { make_grm_xchr_flag = true; cout << "--make-grm-xchr" << endl; }
         else if (is("--make-grm-bin")) { make_grm_flag = true; grm_out_bin_flag = true; cout << "--make-grm-bin" << endl; }
@@ -100,6 +130,14 @@ static void option(int argc, char* argv_in[])
         else { std::stringstream e; e << "\nError: invalid option \"" << o << "\".\n"; throw(e.str()); }
     }
     cout << endl;
+    // conflicted options (option.cpp:547-563)
+    if (m_grm_flag) {
+        if (grm_flag) { grm_flag = false; cout << "Warning: --grm option suppressed by the --mgrm option." << endl; }
+        if (grm_cutoff > -1.0) { grm_cutoff = -2.0; cout << "Warning: --grm-cutoff option suppressed by the --mgrm option." << endl; }
+    }
+    if (pca_flag) throw("Error: --pca is not available in gcta64_b200 (outside the accelerated --make-grm path).");
+    if (dosage_compen > -1 && update_sex_file.empty())
+        throw("Error: you need to specify the sex information for the individuals by the option --update-sex because of the option --dc.");
     // set autosome (option.cpp:566-571)
     if (autosome_flag) { extract_chr_start = 1; extract_chr_end = autosome_num; }
     if (make_grm_xchr_flag) extract_chr_start = extract_chr_end = autosome_num + 1;
@@ -126,6 +164,10 @@ static void option(int argc, char* argv_in[])
         if (out_freq_flag) g.save_freq();
         else if (make_grm_flag) g.make_grm(false, grm_out_bin_flag, grm_mtd);
         else if (make_grm_xchr_flag) g.make_grm(true, grm_out_bin_flag, grm_mtd);
+    }
+    else if (grm_flag || m_grm_flag) {   // option.cpp:657-660
+        if (make_grm_flag)
+            g.save_grm(grm_file, kp_indi_file, rm_indi_file, update_sex_file, grm_cutoff, grm_adj_fac, dosage_compen, m_grm_flag, grm_out_bin_flag);
     }
     else throw("Error: no analysis has been launched by the option(s).\n");
 }

@@ -1,0 +1,103 @@
+"""Consumer side of the .grm.gz (grm.cpp:343-654): `--grm` / `--mgrm` with `--make-grm[-bin]`, and
+--keep / --remove / --grm-cutoff / --grm-adj / --dc on the way, run through gcta64_b200 and through the compiled
+reference on the same files.  Everything is host code in both, so the bar is byte identity: the decompressed text,
+the .grm.bin, the .grm.id and the log lines.  No GPU needed.
+"""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from tests.helpers import ROOT
+
+BIN = os.path.join(ROOT, "gcta_b200", "gcta64_b200")
+pytestmark = pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
+
+
+def _write_grm(d, prefix, ids, seed, nbase, zero_n_at=None):
+    r = np.random.default_rng(seed)
+    n = len(ids)
+    with gzip.open(d / (prefix + ".grm.gz"), "wt") as f:
+        for i in range(n):
+            for j in range(i + 1):
+                a = 1.0 + 0.05 * r.standard_normal() if i == j else 0.03 * r.standard_normal()
+                N = nbase - int(r.integers(0, 50))
+                if zero_n_at == (i, j):
+                    N, a = 0, 0.0
+                f.write("%d\t%d\t%d\t%.6e\n" % (i + 1, j + 1, N, np.float32(a)))
+    with open(d / (prefix + ".grm.id"), "w") as f:
+        f.write("".join("%s\t%s\n" % t for t in ids))
+
+
+@pytest.fixture(scope="module")
+def data(tmp_path_factory):
+    d = tmp_path_factory.mktemp("grmio")
+    ids = [("F%d" % i, "I%d" % i) for i in range(60)]
+    _write_grm(d, "a", ids, 1, 5000)
+    _write_grm(d, "b", ids, 2, 3000, zero_n_at=(7, 3))   # one pair never observed: "Warning:" line, N = 0 in the merge
+    perm = [ids[i] for i in np.random.default_rng(5).permutation(60)][:45]
+    _write_grm(d, "c", perm, 3, 2000)                      # other order, fewer individuals
+    (d / "list.txt").write_text("a\nb\n")
+    (d / "list3.txt").write_text("a\nb\n\nc\nnot a single token\n")
+    (d / "keep.txt").write_text("".join("%s %s\n" % t for t in ids[5:50:2]))
+    (d / "sex.txt").write_text("".join("%s %s %d\n" % (t[0], t[1], 1 + (k % 2)) for k, t in enumerate(ids)))
+    (d / "bad.grm.gz").write_bytes(gzip.compress(b"1\t1\t100\t1.0\n2\t1\t100\tabc\n2\t2\t100\t1.0\n"))
+    (d / "bad.grm.id").write_text("F0\tI0\nF1\tI1\n")
+    (d / "short.grm.gz").write_bytes(gzip.compress(b"1\t1\t100\t1.0\n2\t1\t100\t0.1\n"))
+    (d / "short.grm.id").write_text("F0\tI0\nF1\tI1\n")
+    return d
+
+
+def _body(txt, prefix):
+    lines = [ln for ln in txt.split("\n") if ln.strip()]
+    i = lines.index("Options:")
+    return [ln.replace(prefix, "X") for ln in lines[i:] if not ln.startswith(("Analysis started", "Analysis finished", "Computational time"))]
+
+
+CASES = [
+    ("resave", ["--grm", "a", "--make-grm"]),
+    ("bin", ["--grm", "a", "--make-grm-bin"]),
+    ("warn", ["--grm", "b", "--make-grm"]),
+    ("cut", ["--grm", "a", "--grm-cutoff", "0.05", "--make-grm"]),
+    ("keep", ["--grm", "a", "--keep", "keep.txt", "--make-grm"]),
+    ("rm", ["--grm", "a", "--remove", "keep.txt", "--make-grm"]),
+    ("adj", ["--grm", "a", "--grm-adj", "0", "--make-grm"]),
+    ("dc1", ["--grm", "a", "--dc", "1", "--update-sex", "sex.txt", "--make-grm"]),
+    ("dc0", ["--grm", "a", "--dc", "0", "--update-sex", "sex.txt", "--make-grm"]),
+    ("mg", ["--mgrm", "list.txt", "--make-grm"]),
+    ("mg3", ["--mgrm", "list3.txt", "--make-grm"]),
+    ("mgbin", ["--mgrm", "list.txt", "--make-grm-bin"]),
+    ("mgsup", ["--grm", "a", "--mgrm", "list.txt", "--grm-cutoff", "0.05", "--make-grm"]),   # both suppressed with warnings
+    ("mgsup2", ["--mgrm", "list.txt", "--grm", "a", "--make-grm"]),   # the later name wins and is then read as a list: error
+    ("all", ["--grm", "a", "--keep", "keep.txt", "--grm-cutoff", "0.04", "--grm-adj", "0.1", "--make-grm"]),
+    ("dcnosex", ["--grm", "a", "--dc", "1", "--make-grm"]),            # error: --update-sex required
+    ("adjrange", ["--grm", "a", "--grm-adj", "1.5", "--make-grm"]),    # error: range
+    ("missing", ["--grm", "nothere", "--make-grm"]),                   # error: cannot open .grm.id
+    ("badline", ["--grm", "bad", "--make-grm"]),                       # error: format, line echoed
+    ("short", ["--grm", "short", "--make-grm"]),                       # error: incorrect number of lines
+]
+
+
+@pytest.mark.parametrize("name,args", CASES, ids=[c[0] for c in CASES])
+def test_grm_manipulation_is_byte_identical_to_the_reference(data, name, args):
+    rp, mp = "r_" + name, "m_" + name
+    r = oracle.run_ref(args + ["--out", rp], cwd=data, timeout=300)
+    m = subprocess.run([BIN] + args + ["--out", mp], cwd=data, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert m.returncode == 0 and r.returncode == 0
+    assert _body(m.stdout, mp) == _body(r.stdout, rp)
+    assert m.stderr.replace(mp, "X") == r.stderr.replace(rp, "X")
+    produced = False
+    for ext in (".grm.gz", ".grm.bin", ".grm.id"):
+        rf, mf = data / (rp + ext), data / (mp + ext)
+        assert rf.exists() == mf.exists(), ext
+        if not rf.exists():
+            continue
+        produced = True
+        if ext == ".grm.gz":
+            assert gzip.decompress(mf.read_bytes()) == gzip.decompress(rf.read_bytes())
+        else:
+            assert mf.read_bytes() == rf.read_bytes()
+    assert produced == (name not in ("mgsup2", "dcnosex", "adjrange", "missing", "badline", "short"))
