@@ -355,6 +355,14 @@ static void gz_member(const string& text, string& out)
     static const int level = getenv("GCTA_B200_GZ_LEVEL") ? std::max(0, std::min(9, atoi(getenv("GCTA_B200_GZ_LEVEL")))) : 1;
     if (deflateInit2(&s, level, Z_DEFLATED, 15 + 16 /* gzip wrapper */, 8, Z_DEFAULT_STRATEGY) != Z_OK)
         throw string("Error: zlib deflateInit2 failed.");
+    // the same member-length subfield the built-in encoder writes (grm_text_gz.h), so these files are read in parallel too
+    gz_header head;
+    memset(&head, 0, sizeof head);
+    Bytef extra[8] = {'G', 'M', 4, 0, 0, 0, 0, 0};
+    head.extra = extra;
+    head.extra_len = 8;
+    head.os = 3;
+    deflateSetHeader(&s, &head);
     out.resize(deflateBound(&s, (uLong)text.size()) + 64);
     s.next_in = (Bytef*)text.data();
     s.avail_in = (uInt)text.size();
@@ -364,6 +372,8 @@ static void gz_member(const string& text, string& out)
     out.resize(s.total_out);
     deflateEnd(&s);
     if (rc != Z_STREAM_END) throw string("Error: zlib deflate failed.");
+    if (grm_text_gz::member_size_from_header((const unsigned char*)out.data(), out.size()) == 0 && out.size() >= 20 && (unsigned char)out[3] == 4)
+        grm_text_gz::patch_member_size(out, 0);
 }
 
 void gcta_host::output_grm(const vector<float>& A, const vector<int32_t>& N, bool output_bin)

@@ -8,6 +8,7 @@
 #include <zlib.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <condition_variable>
 #include <cstdio>
@@ -109,6 +110,52 @@ inline bool parse_grm_line(const char* p, const char* e, ParsedLine& L)
     return p == e;
 }
 
+struct BlockResult {
+    int64_t nline = 0;
+    string err;                 // first bad line of the block (message as the reference throws it)
+    vector<string> warnings;    // lines with N == 0 seen before it, in order
+};
+
+// Parses the complete lines of [p, end) into the packed triangles; `last` = nothing follows, so a final line without
+// a newline counts too.  Returns where the unconsumed rest begins.  Stops at the first bad line (R.err).
+const char* parse_block(const char* p, const char* end, bool last, int64_t n, double* grm, double* grm_N, const string& errmsg, BlockResult& R)
+{
+    for (;;) {
+        const char* nl = (const char*)memchr(p, '\n', (size_t)(end - p));
+        if (!nl) {
+            if (!last || p == end) break;
+            nl = end;
+        }
+        ParsedLine L;
+        if (!parse_grm_line(p, nl, L) || L.i1 < L.i2 || L.i1 > n || L.i2 > n || L.i2 < 1) { R.err = errmsg + string(p, nl); return p; }
+        if (L.N == 0) R.warnings.emplace_back(p, nl);
+        const size_t o = (size_t)((L.i1 - 1) * L.i1 / 2 + (L.i2 - 1));
+        grm_N[o] = L.N;
+        grm[o] = L.A;
+        R.nline++;
+        p = nl < end ? nl + 1 : end;
+    }
+    return p;
+}
+
+// Member table of a file whose every gzip member announces its length (grm_text_gz.h); false for any other file.
+bool scan_members(FILE* f, vector<std::pair<uint64_t, uint32_t>>& members)
+{
+    members.clear();
+    if (fseeko(f, 0, SEEK_END) != 0) return false;
+    const uint64_t total = (uint64_t)ftello(f);
+    uint64_t pos = 0;
+    unsigned char h[grm_text_gz::MEMBER_HEADER_BYTES];
+    while (pos < total) {
+        if (fseeko(f, (off_t)pos, SEEK_SET) != 0 || fread(h, 1, sizeof h, f) != sizeof h) { members.clear(); return false; }
+        const uint32_t size = grm_text_gz::member_size_from_header(h, sizeof h);
+        if (size < (uint32_t)sizeof h + 8 || pos + size > total) { members.clear(); return false; }
+        members.emplace_back(pos, size);
+        pos += size;
+    }
+    return !members.empty();
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -143,9 +190,8 @@ void gcta_host::read_grm_gz(const string& grm_file, vector<string>& grm_id, bool
     if (read_id_only) return;
 
     const string grm_gzfile = grm_file + ".grm.gz";
-    gzFile zf = gzopen(grm_gzfile.c_str(), "rb");
-    if (!zf) throw("Error: can not open the file [" + grm_gzfile + "] to read.");
-    gzbuffer(zf, 1u << 20);
+    FILE* raw = fopen(grm_gzfile.c_str(), "rb");
+    if (!raw) throw("Error: can not open the file [" + grm_gzfile + "] to read.");
     const string errmsg = "Error: failed to read [" + grm_gzfile + "]. The format of the GRM file has been changed?\nError occurs in line:\n";
     cout << "Reading the GRM from [" + grm_gzfile + "]." << endl;
     _grm_dim = n;
@@ -153,37 +199,79 @@ void gcta_host::read_grm_gz(const string& grm_file, vector<string>& grm_id, bool
     _grm.assign(tri, 0.0);
     _grm_N.assign(tri, 0.0);
     int64_t nline = 0;
-    vector<char> buf(8u << 20);
-    size_t have = 0;
-    bool eof = false;
-    while (!eof) {
-        const int got = gzread(zf, buf.data() + have, (unsigned)(buf.size() - have));
-        if (got < 0) { gzclose(zf); throw("Error: failed to read [" + grm_gzfile + "] (corrupt gzip stream)."); }
-        if (got == 0) eof = true;
-        have += (size_t)got;
-        const char* p = buf.data();
-        const char* const end = buf.data() + have;
-        for (;;) {
-            const char* nl = (const char*)memchr(p, '\n', (size_t)(end - p));
-            if (!nl) {
-                if (!eof || p == end) break;
-                nl = end;   // last line without a newline
+    // Files written by gcta64_b200 carry each gzip member's length in its header: then the members are inflated and
+    // parsed by all cores.  Any other .grm.gz (the reference's single stream) is decoded sequentially.
+    vector<std::pair<uint64_t, uint32_t>> members;
+    const bool indexed = scan_members(raw, members);
+    fclose(raw);
+    if (indexed) {
+        const int fd_T = (int)std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+        vector<BlockResult> res(members.size());
+        std::atomic<size_t> next(0);
+        std::atomic<bool> not_line_aligned(false);
+        vector<std::thread> th;
+        for (int t = 0; t < fd_T && (size_t)t < members.size(); t++)
+            th.emplace_back([&]() {
+                FILE* f = fopen(grm_gzfile.c_str(), "rb");
+                vector<unsigned char> comp;
+                vector<char> text;
+                for (size_t b = next++; f && b < members.size(); b = next++) {
+                    BlockResult& R = res[b];
+                    comp.resize(members[b].second);
+                    if (fseeko(f, (off_t)members[b].first, SEEK_SET) != 0 || fread(comp.data(), 1, comp.size(), f) != comp.size()) { R.err = "Error: failed to read [" + grm_gzfile + "]."; continue; }
+                    const unsigned char* tail = comp.data() + comp.size() - 4;
+                    const size_t isize = (size_t)tail[0] | ((size_t)tail[1] << 8) | ((size_t)tail[2] << 16) | ((size_t)tail[3] << 24);
+                    text.resize(isize + 1);
+                    z_stream s;
+                    memset(&s, 0, sizeof s);
+                    if (inflateInit2(&s, 15 + 16) != Z_OK) { R.err = "Error: zlib inflateInit2 failed."; continue; }
+                    s.next_in = comp.data(); s.avail_in = (uInt)comp.size();
+                    s.next_out = (Bytef*)text.data(); s.avail_out = (uInt)text.size();
+                    const int rc = inflate(&s, Z_FINISH);
+                    const size_t got = (size_t)s.total_out;
+                    inflateEnd(&s);
+                    if (rc != Z_STREAM_END || got != isize) { R.err = "Error: failed to read [" + grm_gzfile + "] (corrupt gzip stream)."; continue; }
+                    if (got > 0 && text[got - 1] != '\n') { not_line_aligned = true; continue; }
+                    parse_block(text.data(), text.data() + got, true, n, _grm.data(), _grm_N.data(), errmsg, R);
+                }
+                if (f) fclose(f);
+            });
+        for (auto& x : th) x.join();
+        if (!not_line_aligned) {
+            for (const BlockResult& R : res) {
+                for (const string& w : R.warnings) cout << "Warning: " << w << endl;
+                if (!R.err.empty()) throw R.err;
+                nline += R.nline;
             }
-            ParsedLine L;
-            if (!parse_grm_line(p, nl, L)) { gzclose(zf); throw(errmsg + string(p, nl)); }
-            if (L.i1 < L.i2 || L.i1 > n || L.i2 > n || L.i2 < 1) { gzclose(zf); throw(errmsg + string(p, nl)); }
-            if (L.N == 0) cout << "Warning: " << string(p, nl) << endl;
-            const size_t o = (size_t)((L.i1 - 1) * L.i1 / 2 + (L.i2 - 1));
-            _grm_N[o] = L.N;
-            _grm[o] = L.A;
-            nline++;
-            p = nl < end ? nl + 1 : end;
+        } else {
+            members.clear();   // members that split a line: start over, sequentially
+            std::fill(_grm.begin(), _grm.end(), 0.0);
+            std::fill(_grm_N.begin(), _grm_N.end(), 0.0);
         }
-        have = (size_t)(end - p);
-        if (have == buf.size()) { gzclose(zf); throw(errmsg + string(p, p + 200)); }   // a "line" longer than the buffer
-        memmove(buf.data(), p, have);
     }
-    gzclose(zf);
+    if (members.empty()) {
+        gzFile zf = gzopen(grm_gzfile.c_str(), "rb");
+        if (!zf) throw("Error: can not open the file [" + grm_gzfile + "] to read.");
+        gzbuffer(zf, 1u << 20);
+        vector<char> buf(8u << 20);
+        size_t have = 0;
+        bool eof = false;
+        while (!eof) {
+            const int got = gzread(zf, buf.data() + have, (unsigned)(buf.size() - have));
+            if (got < 0) { gzclose(zf); throw("Error: failed to read [" + grm_gzfile + "] (corrupt gzip stream)."); }
+            if (got == 0) eof = true;
+            have += (size_t)got;
+            BlockResult R;
+            const char* p = parse_block(buf.data(), buf.data() + have, eof, n, _grm.data(), _grm_N.data(), errmsg, R);
+            for (const string& w : R.warnings) cout << "Warning: " << w << endl;
+            if (!R.err.empty()) { gzclose(zf); throw R.err; }
+            nline += R.nline;
+            have = (size_t)(buf.data() + have - p);
+            if (have == buf.size()) { gzclose(zf); throw(errmsg + string(p, p + 200)); }   // a "line" longer than the buffer
+            memmove(buf.data(), p, have);
+        }
+        gzclose(zf);
+    }
     if (nline != (int64_t)tri) throw("Error: incorrect number of lines in the grm file. *.grm.gz file and *.grm.id file are mismatched?");
     cout << "Pairwise genetic relationships between " << n << " individuals are included from [" + grm_gzfile + "]." << endl;
 }

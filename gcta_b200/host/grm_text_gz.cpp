@@ -113,6 +113,28 @@ int put_g15(char* q, double v)
     return snprintf(q0, 40, "%.15g", v);
 }
 
+// ---------------------------------------------------------------------------------------------
+// member header with the member's own length (RFC 1952 FEXTRA subfield 'G','M', 4 bytes little endian)
+// ---------------------------------------------------------------------------------------------
+const char MEMBER_HEADER[MEMBER_HEADER_BYTES] = {(char)0x1f, (char)0x8b, 8, 4 /* FEXTRA */, 0, 0, 0, 0, 0, 3,
+                                                 8, 0 /* XLEN */, 'G', 'M', 4, 0 /* LEN */, 0, 0, 0, 0};
+
+void patch_member_size(std::string& out, size_t member_start)
+{
+    const uint64_t size = out.size() - member_start;
+    // a member that does not fit 32 bits keeps 0 = "unknown": readers then fall back to sequential decoding
+    const uint32_t v = size <= 0xFFFFFFFFull ? (uint32_t)size : 0;
+    for (int k = 0; k < 4; k++) out[member_start + 16 + k] = (char)((v >> (8 * k)) & 255);
+}
+
+uint32_t member_size_from_header(const unsigned char* h, size_t avail)
+{
+    if (avail < (size_t)MEMBER_HEADER_BYTES) return 0;
+    if (h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || h[3] != 4) return 0;
+    if (h[10] != 8 || h[11] != 0 || h[12] != 'G' || h[13] != 'M' || h[14] != 4 || h[15] != 0) return 0;
+    return (uint32_t)h[16] | ((uint32_t)h[17] << 8) | ((uint32_t)h[18] << 16) | ((uint32_t)h[19] << 24);
+}
+
 namespace {
 
 // One formatted line and where its four fields start; a field includes the separator that ends it.
@@ -436,8 +458,11 @@ static void encode_impl(const Src& src, int64_t row_begin, int64_t row_end, std:
     canonical_codes(dlen, NDIST, dcode);
 
     // ---- gzip member header (RFC 1952) and the dynamic-Huffman block header (RFC 1951, 3.2.7) ----
-    static const char GZ_HEADER[10] = {(char)0x1f, (char)0x8b, 8, 0, 0, 0, 0, 0, 0, 3};
-    out.append(GZ_HEADER, 10);
+    // FEXTRA carries one subfield 'G','M' = the byte length of this member (patched in below), the way BGZF does it:
+    // a reader that knows it can hop from member to member and inflate them in parallel; every other gzip reader
+    // skips the field.
+    const size_t member_start = out.size();
+    out.append(MEMBER_HEADER, MEMBER_HEADER_BYTES);
     BitWriter bw(out);
     bw.put(1, 1);   // BFINAL
     bw.put(2, 2);   // BTYPE = dynamic Huffman
@@ -494,6 +519,7 @@ static void encode_impl(const Src& src, int64_t row_begin, int64_t row_end, std:
     bw.finish();
     put_le32(out, (uint32_t)crc);
     put_le32(out, (uint32_t)(isize & 0xFFFFFFFFull));
+    patch_member_size(out, member_start);
 }
 
 void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& text)

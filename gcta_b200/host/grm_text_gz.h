@@ -28,6 +28,14 @@ void encode_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t ro
 // The same text, uncompressed (tests; the zlib route of the writer).
 void format_rows(const float* A, const int32_t* N, int64_t row_begin, int64_t row_end, std::string& text);
 
+// Every member starts with this 20-byte gzip header: FEXTRA with one subfield 'G','M' holding the member's byte length
+// (BGZF's idea with a 32-bit size).  patch_member_size fills it in once the member is complete;
+// member_size_from_header returns it, or 0 when the bytes are not such a header (then: decode sequentially).
+constexpr int MEMBER_HEADER_BYTES = 20;
+extern const char MEMBER_HEADER[MEMBER_HEADER_BYTES];
+void patch_member_size(std::string& out, size_t member_start);
+uint32_t member_size_from_header(const unsigned char* h, size_t avail);
+
 // The GRM re-save path (output_grm_MatrixXf, grm.cpp:343-380): matrices held in double, line "i \t j \t (int)N \t A"
 // with A printed like `setprecision(15) << double`, i.e. printf("%.15g").
 int put_g15(char* q, double v);

@@ -48,7 +48,36 @@ def data(tmp_path_factory):
     (d / "bad.grm.id").write_text("F0\tI0\nF1\tI1\n")
     (d / "short.grm.gz").write_bytes(gzip.compress(b"1\t1\t100\t1.0\n2\t1\t100\t0.1\n"))
     (d / "short.grm.id").write_text("F0\tI0\nF1\tI1\n")
+    # files in gcta64_b200's own layout (every gzip member announces its length, read by all cores): N == 0 warnings
+    # spread over members, a bad line in a later member, members that cut a line in two (sequential fallback)
+    text = gzip.decompress((d / "b.grm.gz").read_bytes())
+    lines = text.split(b"\n")[:-1]
+    lines[40] = lines[40].split(b"\t")[0] + b"\t" + lines[40].split(b"\t")[1] + b"\t0\t0.000000e+00"
+    lines[1500] = lines[1500].split(b"\t")[0] + b"\t" + lines[1500].split(b"\t")[1] + b"\t0\t0.000000e+00"
+    cuts = [0, 300, 900, 1400, len(lines)]
+    chunks = [b"".join(ln + b"\n" for ln in lines[a:b]) for a, b in zip(cuts, cuts[1:])]
+    (d / "idxwarn.grm.gz").write_bytes(b"".join(_member(c) for c in chunks))
+    bad = list(lines)
+    bad[1000] = b"47\t12\tx\t1.0"
+    bad[1600] = b"nonsense"
+    (d / "idxbad.grm.gz").write_bytes(b"".join(_member(b"".join(ln + b"\n" for ln in bad[a:b])) for a, b in zip(cuts, cuts[1:])))
+    whole = b"".join(chunks)
+    assert whole[7000:7001] != b"\n" and whole[20010:20011] != b"\n"
+    (d / "idxsplit.grm.gz").write_bytes(_member(whole[:7001]) + _member(whole[7001:20011]) + _member(whole[20011:]))
+    for name in ("idxwarn", "idxbad", "idxsplit"):
+        (d / (name + ".grm.id")).write_text((d / "b.grm.id").read_text())
     return d
+
+
+def _member(text: bytes) -> bytes:
+    """one gzip member with the FEXTRA 'GM' subfield = its own length (host/grm_text_gz.h)"""
+    import struct
+    import zlib
+    c = zlib.compressobj(6, zlib.DEFLATED, -15)
+    body = c.compress(text) + c.flush()
+    size = 20 + len(body) + 8
+    head = bytes([0x1f, 0x8b, 8, 4, 0, 0, 0, 0, 0, 3, 8, 0]) + b"GM" + bytes([4, 0]) + struct.pack("<I", size)
+    return head + body + struct.pack("<II", zlib.crc32(text), len(text) & 0xFFFFFFFF)
 
 
 def _body(txt, prefix):
@@ -78,6 +107,9 @@ CASES = [
     ("missing", ["--grm", "nothere", "--make-grm"]),                   # error: cannot open .grm.id
     ("badline", ["--grm", "bad", "--make-grm"]),                       # error: format, line echoed
     ("short", ["--grm", "short", "--make-grm"]),                       # error: incorrect number of lines
+    ("idxwarn", ["--grm", "idxwarn", "--make-grm"]),                   # member-indexed file: warnings stay in file order
+    ("idxbad", ["--grm", "idxbad", "--make-grm"]),                     # ... the first bad line in file order is reported
+    ("idxsplit", ["--grm", "idxsplit", "--make-grm"]),                 # ... members that cut lines: sequential fallback
 ]
 
 
@@ -100,4 +132,4 @@ def test_grm_manipulation_is_byte_identical_to_the_reference(data, name, args):
             assert gzip.decompress(mf.read_bytes()) == gzip.decompress(rf.read_bytes())
         else:
             assert mf.read_bytes() == rf.read_bytes()
-    assert produced == (name not in ("mgsup2", "dcnosex", "adjrange", "missing", "badline", "short"))
+    assert produced == (name not in ("mgsup2", "dcnosex", "adjrange", "missing", "badline", "short", "idxbad"))
