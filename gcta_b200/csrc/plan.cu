@@ -507,15 +507,6 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
     using namespace gb;
     if (!p->stream_copy) GB_CUDA(cudaStreamCreateWithFlags(&p->stream_copy, cudaStreamNonBlocking));
     const int64_t band_base = p->row_begin * (p->row_begin + 1) / 2;
-    std::vector<std::thread> fill;
-    if (out->N_lower) {
-        const int nt = (int)std::min<int64_t>(16, std::max<int64_t>(1, p->band_count >> 22));
-        int32_t* dst = out->N_lower + band_base;
-        const int32_t mval = (int32_t)p->m;
-        const int64_t cnt = p->band_count;
-        for (int t = 0; t < nt; t++)
-            fill.emplace_back([=]() { std::fill(dst + cnt * t / nt, dst + cnt * (t + 1) / nt, mval); });
-    }
     // segment boundaries: tile indices where a new raster group of row blocks starts
     const int R = raster_rows();
     const int64_t b0 = p->row_begin / TILE_M;
@@ -556,6 +547,17 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
         if (e == cudaSuccess)
             e = cudaMemcpyAsync(out->A_lower + seg_base, p->d_A_lower + (seg_base - band_base), (size_t)seg_cnt * 4, cudaMemcpyDeviceToHost, p->stream_copy);
         if (e != cudaSuccess) rc = set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed in the pipelined download: ") + cudaGetErrorString(e));
+    }
+    // every launch of the chunk is queued: only now start the host threads that fill N (== m everywhere), so that
+    // nothing competes with the launching thread for cores while the GPU waits for its next kernel
+    std::vector<std::thread> fill;
+    if (out->N_lower) {
+        const int nt = (int)std::min<int64_t>(16, std::max<int64_t>(1, p->band_count >> 22));
+        int32_t* dst = out->N_lower + band_base;
+        const int32_t mval = (int32_t)p->m;
+        const int64_t cnt = p->band_count;
+        for (int t = 0; t < nt; t++)
+            fill.emplace_back([=]() { std::fill(dst + cnt * t / nt, dst + cnt * (t + 1) / nt, mval); });
     }
     cudaError_t e2 = cudaStreamSynchronize(p->stream_copy);
     for (auto& t : fill) t.join();
