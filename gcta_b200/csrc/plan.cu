@@ -62,33 +62,53 @@ extern "C" int gcta_b200_partition(int64_t n, int32_t part_rank, int32_t part_wo
     if (part_rank < 0 || part_rank >= part_world) return GCTA_B200_ERR_ARG;
     const int64_t nrb = (n + TILE_M - 1) / TILE_M;
     // Cost of a band of row blocks [b0, b1), in units of one 256x256 tile of SYRK work:
-    //   tiles(b0, b1)            the tensor work
-    // + ALPHA * b1               K1 standardises columns [0, 256*b1) for this band (HBM-bound, replicated per GPU)
-    // + BETA * (b1 - b0)         K1d sums the diagonal of the band's own individuals
-    // ALPHA and BETA are measured ratios on B200 (one column block of K1 costs ~2.1 tiles, of K1d ~1; both
-    // scale with M like the tiles do, so the ratios do not depend on M).  Boundaries minimise the largest band.
-    const double ALPHA = 2.1, BETA = 1.0;
+    //   SMS * ceil(tiles(b0, b1) / SMS)   the tensor work: K2 runs one persistent CTA per SM and all CTAs start each wave
+    //                                     of SMS tiles together, so a launch takes whole waves
+    // + ALPHA * b1                        K1 standardises columns [0, 256*b1) for this band (HBM-bound, replicated per GPU)
+    // + BETA * (b1 - b0)                  K1d sums the diagonal of the band's own individuals
+    // ALPHA and BETA are measured ratios on B200 (8-GPU run of the headline workload with the wave-barrier kernel: a
+    // wave of 148 tiles 12.2 ms, K1 0.110 ms and K1d 0.069 ms per block of 256 individuals; all three scale with M, so
+    // the ratios do not depend on M).  Boundaries minimise the largest band.  The model reproduces the measured
+    // per-rank times of that run within 3 %; counting whole waves instead of tiles moves the 8-GPU bands so that no
+    // rank needs an 18th wave (predicted step 236 ms against 241 ms).
+    const double ALPHA = 1.33, BETA = 0.83;
+    const int64_t SMS = 148;
     std::vector<int64_t> pref(nrb + 1, 0);
     for (int64_t b = 0; b < nrb; b++) pref[b + 1] = pref[b] + tiles_in_row_block(b, n);
-    auto cost = [&](int64_t b0, int64_t b1) { return (double)(pref[b1] - pref[b0]) + ALPHA * b1 + BETA * (b1 - b0); };
-    auto cut = [&](double cap, std::vector<int64_t>& bounds) {   // greedy: longest band within `cap`, G bands at most
+    auto cost = [&](int64_t b0, int64_t b1) {
+        const int64_t t = pref[b1] - pref[b0];
+        return (double)((t + SMS - 1) / SMS * SMS) + ALPHA * b1 + BETA * (b1 - b0);
+    };
+    // the same with tiles counted one by one: used to break ties, so that among the partitions that reach the smallest
+    // wave-counted maximum the bands are also as even as possible in plain work
+    auto cost_lin = [&](int64_t b0, int64_t b1) { return (double)(pref[b1] - pref[b0]) + ALPHA * b1 + BETA * (b1 - b0); };
+    auto cut = [&](double cap, double cap_lin, std::vector<int64_t>& bounds) {   // greedy: longest band within the caps, G bands at most
         bounds.assign(part_world + 1, nrb);
         bounds[0] = 0;
         int64_t b = 0;
         for (int g = 0; g < part_world; g++) {
             int64_t e = b;
-            while (e < nrb && cost(b, e + 1) <= cap) e++;
+            while (e < nrb && cost(b, e + 1) <= cap && cost_lin(b, e + 1) <= cap_lin) e++;
             bounds[g + 1] = e;
             b = e;
         }
         return b >= nrb;
     };
+    const double INF = 1e300;
     double lo = 0.0, hi = cost(0, nrb);
     std::vector<int64_t> bounds, best;
-    cut(hi, best);
+    cut(hi, INF, best);
     for (int it = 0; it < 60; it++) {
         const double mid = 0.5 * (lo + hi);
-        if (cut(mid, bounds)) { hi = mid; best = bounds; }
+        if (cut(mid, INF, bounds)) { hi = mid; best = bounds; }
+        else lo = mid;
+    }
+    const double cap_wave = hi * 1.02;   // within 2 % of the best wave-counted maximum (less than one wave for any real size)
+    lo = 0.0;
+    hi = cost_lin(0, nrb);
+    for (int it = 0; it < 60; it++) {
+        const double mid = 0.5 * (lo + hi);
+        if (cut(cap_wave, mid, bounds)) { hi = mid; best = bounds; }
         else lo = mid;
     }
     *row_begin = std::min<int64_t>(best[part_rank] * TILE_M, n);
