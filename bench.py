@@ -245,12 +245,7 @@ def main_ours(a, rank, world, local_rank):
                                        "device, first kernel to last": oo.ms_total, "device syrk": oo.ms_syrk, "device decode+diag": oo.ms_decode})
                 api = ("gcta_b200_exchange_post/pull (per rank 1/N of the rows over PCIe, the rest peer-to-peer over NVLink by the copy "
                        "engines, 32 segments, overlapped with the compute) + plan_run_to_host (finalize + download pipelined), pinned host buffers")
-                seg = max(1, -(-m // 32))
-                h2d = 0
-                for s0 in range(0, m, seg):
-                    s1 = min(m, s0 + seg)
-                    per = -(-(s1 - s0) // world)
-                    h2d += stride * (min(s1, s0 + (rank + 1) * per) - min(s1, s0 + rank * per))
+                h2d = stride * sum(e - b for b, e in abi.exchange_slices(m, world, rank))
         e2e_step()
         barrier()
         t0 = time.perf_counter()

@@ -26,7 +26,7 @@ EXPORTS = [
     "gcta_b200_plan_use_device_bed", "gcta_b200_plan_upload_rows", "gcta_b200_plan_run_to_host",
     "gcta_b200_plan_num_chunks", "gcta_b200_plan_chunk_rows", "gcta_b200_plan_upload_rows_async", "gcta_b200_plan_set_chunk_events",
     "gcta_b200_plan_use_own_bed", "gcta_b200_plan_geometry",
-    "gcta_b200_exchange_blob_bytes", "gcta_b200_exchange_create", "gcta_b200_exchange_connect", "gcta_b200_exchange_post",
+    "gcta_b200_exchange_slice", "gcta_b200_exchange_blob_bytes", "gcta_b200_exchange_create", "gcta_b200_exchange_connect", "gcta_b200_exchange_post",
     "gcta_b200_exchange_pull", "gcta_b200_exchange_finish", "gcta_b200_exchange_disconnect", "gcta_b200_exchange_destroy",
 ]
 
@@ -255,6 +255,19 @@ class Plan:
             self.close()
         except Exception:
             pass
+
+
+def exchange_slices(m_file: int, world: int, rank: int):
+    """[(row_begin, row_end)] per segment: the file rows `rank` uploads in gcta_b200_exchange_post (no device needed)"""
+    L = lib()
+    L.gcta_b200_exchange_slice.restype = C.c_int64
+    nseg = L.gcta_b200_exchange_slice(C.c_int64(m_file), C.c_int32(world), C.c_int32(rank), C.c_int64(0), None, None)
+    out = []
+    for s in range(nseg):
+        b, e = C.c_int64(), C.c_int64()
+        L.gcta_b200_exchange_slice(C.c_int64(m_file), C.c_int32(world), C.c_int32(rank), C.c_int64(s), C.byref(b), C.byref(e))
+        out.append((b.value, e.value))
+    return out
 
 
 class Exchange:

@@ -49,14 +49,25 @@ struct gcta_b200_exchange {
     bool connected = false;
 
     // rows of segment s that rank q uploads
-    void slice(int64_t s, int q, int64_t* r0, int64_t* r1) const
-    {
-        const int64_t s0 = s * seg_rows, s1 = std::min(m_file, s0 + seg_rows);
-        const int64_t per = (s1 - s0 + world - 1) / world;
-        *r0 = std::min(s1, s0 + q * per);
-        *r1 = std::min(s1, s0 + (q + 1) * per);
-    }
+    void slice(int64_t s, int q, int64_t* r0, int64_t* r1) const { gcta_b200_exchange_slice(m_file, world, q, s, r0, r1); }
 };
+
+// Pure geometry (no device needed): the file rows are cut into at most 32 equal segments, each segment into `world`
+// equal slices; returns the rows of segment `seg` that `rank` uploads and the number of segments.
+extern "C" int64_t gcta_b200_exchange_slice(int64_t m_file, int32_t world, int32_t rank, int64_t seg, int64_t* row_begin, int64_t* row_end)
+{
+    if (m_file <= 0 || world < 1 || rank < 0 || rank >= world) return 0;
+    int64_t seg_rows, nseg;
+    seg_geometry(m_file, &seg_rows, &nseg);
+    if (row_begin && row_end) {
+        if (seg < 0 || seg >= nseg) { *row_begin = *row_end = m_file; return nseg; }
+        const int64_t s0 = seg * seg_rows, s1 = std::min(m_file, s0 + seg_rows);
+        const int64_t per = (s1 - s0 + world - 1) / world;
+        *row_begin = std::min(s1, s0 + rank * per);
+        *row_end = std::min(s1, s0 + (rank + 1) * per);
+    }
+    return nseg;
+}
 
 extern "C" int64_t gcta_b200_exchange_blob_bytes(gcta_b200_plan* plan)
 {

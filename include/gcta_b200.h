@@ -153,6 +153,9 @@ int gcta_b200_plan_geometry(gcta_b200_plan* plan, int32_t* device, int64_t* m_fi
  * differently (a band's chunk length depends on its row_end).  All plans must have the same n_file and m_file. */
 #define GCTA_B200_IPC_HANDLE_BYTES 64
 typedef struct gcta_b200_exchange gcta_b200_exchange;
+/* geometry only (no device): number of segments for a file of m_file rows, and the rows of segment `seg` that `rank`
+ * of `world` uploads (row_begin/row_end may be NULL) */
+int64_t gcta_b200_exchange_slice(int64_t m_file, int32_t world, int32_t rank, int64_t seg, int64_t* row_begin, int64_t* row_end);
 int64_t gcta_b200_exchange_blob_bytes(gcta_b200_plan* plan);
 int gcta_b200_exchange_create(gcta_b200_plan* plan, int32_t rank, int32_t world, uint8_t* my_blob, gcta_b200_exchange** ex,
                               char* err, size_t errcap);

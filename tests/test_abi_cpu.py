@@ -58,6 +58,34 @@ def test_partition_bands_are_contiguous_and_balanced(n, world):
     assert all(b % 256 == 0 for b, e in bands if e > b)
 
 
+def test_partition_counts_whole_waves_on_the_headline_workload():
+    """K2 takes whole waves of 148 tiles per launch: with 8 GPUs on n = 50,000 no band may need more than 17 waves
+    (19,306 tiles cannot be done in fewer: 8 x 16 waves hold only 18,944)."""
+    bands = [abi.partition(50000, r, 8) for r in range(8)]
+    waves = [-(-len(abi.tile_list(50000, b, e)) // 148) for b, e in bands]
+    assert max(waves) == 17 and sum(w * 148 for w in waves) >= 19306
+    # later bands standardise more columns, so they never get more tensor work than earlier ones
+    assert waves == sorted(waves, reverse=True)
+
+
+@pytest.mark.parametrize("m,world", [(1000000, 8), (13000, 2), (31, 4), (1, 3), (64, 64), (100003, 7)])
+def test_exchange_slices_cover_every_file_row_once(m, world):
+    """gcta_b200_exchange_slice: per segment the ranks' slices are disjoint, ascending and together the whole segment;
+    the segments follow each other and end at the last row - what exchange_post uploads and exchange_pull fetches."""
+    per_rank = [abi.exchange_slices(m, world, r) for r in range(world)]
+    nseg = len(per_rank[0])
+    assert 1 <= nseg <= 32 and all(len(p) == nseg for p in per_rank)
+    pos = 0
+    for s in range(nseg):
+        for r in range(world):
+            b, e = per_rank[r][s]
+            assert b == pos and e >= b
+            pos = e
+    assert pos == m
+    sizes = [sum(e - b for b, e in p) for p in per_rank]
+    assert sum(sizes) == m and (m < 32 * world or max(sizes) - min(sizes) <= 32 + m // (world * 16))
+
+
 def test_no_cpu_fallback():
     if abi.lib().gcta_b200_device_count() > 0:
         pytest.skip("a CUDA device is present")
