@@ -86,6 +86,32 @@ def test_exchange_slices_cover_every_file_row_once(m, world):
     assert sum(sizes) == m and (m < 32 * world or max(sizes) - min(sizes) <= 32 + m // (world * 16))
 
 
+def test_header_is_plain_c_and_links_from_c(tmp_path):
+    """The boundary is a C ABI: the header must compile as strict C99, and a C program must link against the library
+    and call it (device-free entry points only: there is no GPU here)."""
+    import subprocess
+    hdr = os.path.join(ROOT, "include", "gcta_b200.h")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", hdr], check=True)
+    src = tmp_path / "t.c"
+    src.write_text('#include <stdio.h>\n#include "gcta_b200.h"\n'
+                   "int main(void) {\n"
+                   "    int64_t b = -1, e = -1, r0 = -1, r1 = -1;\n"
+                   "    if (gcta_b200_partition(50000, 1, 2, &b, &e)) return 1;\n"
+                   "    int64_t nseg = gcta_b200_exchange_slice(1000000, 8, 3, 5, &r0, &r1);\n"
+                   '    printf("%s|%lld|%lld|%lld|%lld|%lld|%lld\\n", gcta_b200_version(), (long long)b, (long long)e, (long long)nseg,\n'
+                   "           (long long)r0, (long long)r1, (long long)gcta_b200_s_tile_index(5, 7));\n"
+                   "    return 0;\n}\n")
+    exe = tmp_path / "t"
+    libdir = os.path.join(ROOT, "gcta_b200")
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe), "-L", libdir, "-lgcta_b200",
+                    "-Wl,-rpath," + libdir], check=True)
+    out = subprocess.run([str(exe)], check=True, stdout=subprocess.PIPE, text=True).stdout.strip().split("|")
+    assert out[0].startswith("gcta_b200 ")
+    assert (int(out[1]), int(out[2])) == abi.partition(50000, 1, 2)
+    assert int(out[3]) == 32 and (int(out[4]), int(out[5])) == abi.exchange_slices(1000000, 8, 3)[5]
+    assert int(out[6]) == ((7 >> 2) * 256 + 5) * 4 + (7 & 3)
+
+
 def test_no_cpu_fallback():
     if abi.lib().gcta_b200_device_count() > 0:
         pytest.skip("a CUDA device is present")
