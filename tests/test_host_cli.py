@@ -266,6 +266,37 @@ FLAG_SETS = [
 ]
 
 
+HOST_ONLY_FLAG_SETS = FLAG_SETS + [
+    ["--keep", "nosuchfile.txt", "--make-grm"],                        # cannot open the list
+    ["--autosome", "--extract-snp", "rs_unknown", "--make-grm"],       # SNP not found
+    ["--autosome", "--exclude-snp", "rs_unknown", "--make-grm"],
+    ["--chr", "24", "--make-grm"],                                     # no SNP left
+    ["--update-sex", "remove.txt", "--make-grm-xchr"],                 # malformed sex file
+    ["--autosome", "--rm-high-ld", "1.5", "--make-grm"],               # range error while parsing
+    ["--autosome", "--save-ram", "--make-grm-bin"],
+]
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
+@pytest.mark.parametrize("flags", HOST_ONLY_FLAG_SETS, ids=[" ".join(f) for f in HOST_ONLY_FLAG_SETS])
+def test_host_side_of_the_flags_matches_the_reference_without_a_gpu(flags, tmp_path):
+    """Everything the front end does before it needs the device - option echo, .fam/.bim/.bed reading, the selection
+    lists, the guards and their error strings - must produce the reference's log line for line; where the reference
+    fails before any arithmetic, stderr must be the same too.  Runs on the CPU box."""
+    _flag_dataset(tmp_path)
+    rr = oracle.run_ref(["--bfile", "t"] + flags + ["--out", "ref"], cwd=tmp_path)
+    rm = run_cli(["--bfile", "t"] + flags + ["--out", "mine"], tmp_path)
+    ours = [ln.replace("[mine.", "[X.") for ln in body(rm.stdout) if not ln.startswith("--out")]
+    theirs = [ln.replace("[ref.", "[X.") for ln in body(rr.stdout) if not ln.startswith("--out")]
+    device_lines = ("Calculating allele frequencies", "Recoding genotypes", "Pruning SNPs", "Writing allele frequencies",
+                    "Calculating the genetic relationship")
+    stop = next((i for i, ln in enumerate(theirs) if ln.startswith(device_lines)), len(theirs))
+    assert stop > 0 and ours[:stop] == theirs[:stop]
+    if stop == len(theirs):     # the reference never reached the arithmetic: same error, same place
+        assert rm.stderr.strip() == rr.stderr.strip() and rr.stderr.strip() != ""
+        assert ours == theirs
+
+
 @pytest.mark.gpu
 @pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
 @pytest.mark.parametrize("flags", FLAG_SETS, ids=[" ".join(f) for f in FLAG_SETS])
