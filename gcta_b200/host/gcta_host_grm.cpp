@@ -15,6 +15,7 @@
 
 #include "../../include/gcta_b200.h"
 #include "gcta_host.h"
+#include "grm_bin_writer.h"
 #include "grm_text_gz.h"
 
 using std::cout;
@@ -383,15 +384,7 @@ void gcta_host::output_grm(const vector<float>& A, const vector<int32_t>& N, boo
     if (output_bin) {
         // full n x n float64, row-major, symmetric fill, no header, no N (grm.cpp:309-317)
         grm_file = _out + ".grm.bin";
-        FILE* f = fopen(grm_file.c_str(), "wb");
-        if (!f) throw("Error: can not open the file [" + grm_file + "] to write.");
-        vector<double> row(n);
-        for (int64_t i = 0; i < n; i++) {
-            for (int64_t j = 0; j <= i; j++) row[j] = A[(size_t)(i * (i + 1) / 2 + j)];
-            for (int64_t j = i + 1; j < n; j++) row[j] = A[(size_t)(j * (j + 1) / 2 + i)];
-            fwrite(row.data(), sizeof(double), (size_t)n, f);
-        }
-        fclose(f);
+        if (!write_grm_bin_square(grm_file, A.data(), n)) throw("Error: can not open the file [" + grm_file + "] to write.");
         cout << "GRM of " << n << " individuals has been saved in the file [" + grm_file + "] (in binary format)." << endl;
     } else {
         // gzip text "i \t j \t N \t A" (scientific, 6 digits), 1-based, j <= i (grm.cpp:321-331).  Written as

@@ -20,6 +20,7 @@
 #include <unordered_map>
 
 #include "gcta_host.h"
+#include "grm_bin_writer.h"
 #include "grm_text_gz.h"
 
 using std::cout;
@@ -477,15 +478,7 @@ void gcta_host::output_grm_g15(bool output_grm_bin)
     string grm_file;
     if (output_grm_bin) {
         grm_file = _out + ".grm.bin";
-        FILE* f = fopen(grm_file.c_str(), "wb");
-        if (!f) throw("Error: can not open the file [" + grm_file + "] to write.");
-        vector<double> row((size_t)n);
-        for (int64_t i = 0; i < n; i++) {
-            for (int64_t j = 0; j <= i; j++) row[(size_t)j] = _grm[(size_t)(i * (i + 1) / 2 + j)];
-            for (int64_t j = i + 1; j < n; j++) row[(size_t)j] = _grm[(size_t)(j * (j + 1) / 2 + i)];
-            fwrite(row.data(), sizeof(double), (size_t)n, f);
-        }
-        fclose(f);
+        if (!write_grm_bin_square(grm_file, _grm.data(), n)) throw("Error: can not open the file [" + grm_file + "] to write.");
         cout << "GRM of " << n << " individuals has been saved in the file [" + grm_file + "] (in binary format)." << endl;
     } else {
         grm_file = _out + ".grm.gz";

@@ -93,6 +93,20 @@ def test_structured_gz_encoder_writes_the_same_text_as_zlib(tmp_path):
     assert gzip.decompress(open(tmp_path / "re_a.grm.gz", "rb").read()) == gzip.decompress(open(tmp_path / "re_b.grm.gz", "rb").read())
 
 
+def test_parallel_bin_writer_lays_out_the_full_square(tmp_path):
+    """.grm.bin is written by a pool of threads in 16-row bands with pwrite (host/grm_bin_writer.h): n x n float64,
+    symmetric, and element for element the matrix the text writer prints (n = 333: 21 bands, the last one ragged)."""
+    n = 333
+    _selftest_writer(n, "t", tmp_path)
+    _selftest_writer(n, "b", tmp_path, extra=["--make-grm-bin"])
+    A, _, _ = grmio.read_grm_gz(str(tmp_path / "t.grm.gz"))
+    B = grmio.read_grm_bin(str(tmp_path / "b.grm.bin"))
+    assert B.shape == (n, n) and np.array_equal(B, B.T)
+    low = B[np.tril_indices(n)]
+    assert np.abs(low - A).max() <= 5.1e-7 * np.abs(low).max()
+    assert np.array_equal(low.astype(np.float32).astype(np.float64), low)   # float32 values widened, nothing else
+
+
 @pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
 def test_reference_reader_accepts_the_structured_gz(tmp_path):
     """SURVEY.md 8f-1 without a GPU: the reference's read_grm_gz (grm.cpp:381-448, gzifstream of zfstream.cpp) reads the
