@@ -3,8 +3,13 @@
 // pipelines grep them; the code itself is new.
 #include "gcta_host.h"
 
+#include <fcntl.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <thread>
 #include <fstream>
 #include <iomanip>
 #include <iostream>
@@ -94,23 +99,53 @@ void gcta_host::read_bedfile(const string& bedfile)
     vector<int> keep;
     for (int i = 0; i < _indi_num; i++)
         if (_id_map.find(_fid[i] + ":" + _pid[i]) != _id_map.end()) keep.push_back(i);
-    std::ifstream bit(bedfile.c_str(), std::ios::in | std::ios::binary);
-    if (!bit) throw("Error: can not open the file [" + bedfile + "] to read.");
+    const int fd = open(bedfile.c_str(), O_RDONLY);
+    if (fd < 0) throw("Error: can not open the file [" + bedfile + "] to read.");
     cout << "Reading PLINK BED file from [" + bedfile + "] in SNP-major format ..." << endl;
-    char magic[3];
-    bit.read(magic, 3);   // skipped unchecked, data.cpp:164
+    // the 3 magic bytes are skipped unchecked (data.cpp:164); the rows wanted are read straight into the packed buffer,
+    // runs of consecutive rows with one pread each, by a few threads (the file is 12.5 GB at the headline size)
     _bed_stride = ((int64_t)_indi_num + 3) / 4;
+    vector<std::pair<int64_t, int64_t>> runs;   // (first file row, rows) of consecutive wanted rows
     int64_t m_read = 0;
-    for (int j = 0; j < _snp_num; j++) m_read += rsnp[j];
-    _bed.assign((size_t)(m_read * _bed_stride), 0);
-    int64_t row = 0;
-    for (int j = 0; j < _snp_num && row < m_read; j++) {
-        if (!rsnp[j]) { bit.seekg(_bed_stride, std::ios::cur); continue; }
-        bit.read(reinterpret_cast<char*>(&_bed[(size_t)(row * _bed_stride)]), _bed_stride);
-        if (!bit) throw("Error: problem with the BED file...has the FAM/BIM file been changed?");   // data.cpp:173
-        row++;
+    for (int j = 0; j < _snp_num; j++) {
+        if (!rsnp[j]) continue;
+        if (!runs.empty() && runs.back().first + runs.back().second == j) runs.back().second++;
+        else runs.emplace_back(j, 1);
+        m_read++;
     }
-    bit.close();
+    _bed.resize((size_t)(m_read * _bed_stride));   // not zero-filled: every byte comes from the file
+    // split long runs so that every thread gets work
+    const int64_t piece = std::max<int64_t>(1, (64ll << 20) / std::max<int64_t>(1, _bed_stride));
+    struct Piece { int64_t file_row, dst_row, rows; };
+    vector<Piece> pieces;
+    int64_t dst = 0;
+    for (const auto& r : runs)
+        for (int64_t o = 0; o < r.second; o += piece) {
+            const int64_t k = std::min(piece, r.second - o);
+            pieces.push_back({r.first + o, dst, k});
+            dst += k;
+        }
+    std::atomic<size_t> next(0);
+    std::atomic<bool> bad(false);
+    auto work = [&]() {
+        for (size_t p = next++; p < pieces.size() && !bad; p = next++) {
+            char* out = reinterpret_cast<char*>(&_bed[(size_t)(pieces[p].dst_row * _bed_stride)]);
+            size_t left = (size_t)(pieces[p].rows * _bed_stride);
+            off_t off = (off_t)3 + (off_t)pieces[p].file_row * (off_t)_bed_stride;
+            while (left > 0) {
+                const ssize_t g = pread(fd, out, left, off);
+                if (g <= 0) { bad = true; break; }   // short file
+                out += g; left -= (size_t)g; off += g;
+            }
+        }
+    };
+    const int T = (int)std::max<size_t>(1, std::min<size_t>({(size_t)8, (size_t)std::thread::hardware_concurrency(), pieces.size()}));
+    vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(work);
+    work();
+    for (auto& x : th) x.join();
+    close(fd);
+    if (bad) throw("Error: problem with the BED file...has the FAM/BIM file been changed?");   // data.cpp:173
     _keep = keep;
     cout << "Genotype data for " << _keep.size() << " individuals and " << m_read << " SNPs to be included from [" + bedfile + "]." << endl;
 

@@ -9,8 +9,19 @@
 #pragma once
 #include <cstdint>
 #include <map>
+#include <memory>
 #include <string>
+#include <utility>
 #include <vector>
+
+// std::allocator that leaves trivially constructible elements uninitialised: the .bed payload (12.5 GB at the headline
+// size) is filled completely by the reader, zeroing it first would cost seconds
+template <typename T>
+struct default_init_allocator : std::allocator<T> {
+    template <typename U> struct rebind { typedef default_init_allocator<U> other; };
+    template <typename U> void construct(U* p) noexcept { ::new (static_cast<void*>(p)) U; }
+    template <typename U, typename... Args> void construct(U* p, Args&&... args) { ::new (static_cast<void*>(p)) U(std::forward<Args>(args)...); }
+};
 
 class gcta_host {
 public:
@@ -62,7 +73,7 @@ private:
     void check_chrX() const;                              // grm.cpp:22-27
     void check_sex() const;                               // grm.cpp:29-34
     void rm_high_ld();                                    // data.cpp:1194-1196 (default: no-op)
-    void output_grm(const std::vector<float>& A, const std::vector<int32_t>& N, bool output_bin);   // grm.cpp:303-341
+    void output_grm(const float* A, const int32_t* N, bool output_bin);   // N == NULL with output_bin   // grm.cpp:303-341
     void read_grm_gz(const std::string& grm_file, std::vector<std::string>& grm_id, bool out_id_log = true, bool read_id_only = false);   // grm.cpp:381-448
     void merge_grm(const std::string& merge_grm_file);    // grm.cpp:608-654
     void rm_cor_indi(double grm_cutoff);                  // grm.cpp:450-493
@@ -94,7 +105,7 @@ private:
     std::vector<char> _allele1, _allele2, _ref_A;
     std::map<std::string, int> _snp_name_map;
     // genotypes: payload rows of the SNPs read (compact SNP index), all file individuals
-    std::vector<uint8_t> _bed;
+    std::vector<uint8_t, default_init_allocator<uint8_t>> _bed;
     int64_t _bed_stride = 0;
     std::vector<double> _mu;   // 2p in the _ref_A orientation, indexed by compact SNP id (gcta.h:273)
     bool _mu_from_file = false; // set by update_freq: only then is 2p passed down instead of recomputed

@@ -10,6 +10,7 @@
 #include <iostream>
 #include <chrono>
 #include <condition_variable>
+#include <memory>
 #include <mutex>
 #include <thread>
 
@@ -195,8 +196,10 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
     else cout << "\nCalculating the genetic relationship matrix ... (NOTE: default speed-optimized mode, may use huge RAM)" << endl;
 
     const size_t tri = (size_t)n * (size_t)(n + 1) / 2;
-    vector<float> A(tri);
-    vector<int32_t> N(output_bin ? 0 : tri);   // --make-grm-bin drops N (grm.cpp:307-318)
+    // not value-initialised: at n = 50,000 zero-filling these 10 GB would cost seconds before the first kernel starts,
+    // and every element of the band(s) is written by the library
+    std::unique_ptr<float[]> A(new float[tri]);
+    std::unique_ptr<int32_t[]> N(output_bin ? nullptr : new int32_t[tri]);   // --make-grm-bin drops N (grm.cpp:307-318)
     const int G = std::max(1, std::min(n_gpus, gcta_b200_device_count() > 0 ? gcta_b200_device_count() : 1));
     vector<string> errs(G);
     vector<int> rcs(G, 0);
@@ -212,8 +215,8 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
         a.device = g; a.part_rank = g; a.part_world = G; a.chunk_snps = chunk_snps;
         gcta_b200_out& o = outs[g];
         memset(&o, 0, sizeof o);
-        o.A_lower = A.data();
-        o.N_lower = N.empty() ? nullptr : N.data();
+        o.A_lower = A.get();
+        o.N_lower = N.get();
         char err[512] = {0};
         rcs[g] = gcta_b200_make_grm(&a, &o, err, sizeof err);
         errs[g] = err;
@@ -236,7 +239,7 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
                       << ", \"ms_finalize\": " << outs[g].ms_finalize << ", \"ms_d2h\": " << outs[g].ms_d2h << ", \"launches\": " << outs[g].launches << "}" << endl;
     }
     const auto t_w0 = std::chrono::steady_clock::now();
-    output_grm(A, N, output_bin);
+    output_grm(A.get(), N.get(), output_bin);
     if (getenv("GCTA_B200_TIMING"))
         std::cerr << "{\"write_s\": " << std::chrono::duration<double>(std::chrono::steady_clock::now() - t_w0).count() << "}" << endl;
 }
@@ -377,14 +380,14 @@ static void gz_member(const string& text, string& out)
         grm_text_gz::patch_member_size(out, 0);
 }
 
-void gcta_host::output_grm(const vector<float>& A, const vector<int32_t>& N, bool output_bin)
+void gcta_host::output_grm(const float* A, const int32_t* N, bool output_bin)
 {
     const int64_t n = (int64_t)_keep.size();
     string grm_file;
     if (output_bin) {
         // full n x n float64, row-major, symmetric fill, no header, no N (grm.cpp:309-317)
         grm_file = _out + ".grm.bin";
-        if (!write_grm_bin_square(grm_file, A.data(), n)) throw("Error: can not open the file [" + grm_file + "] to write.");
+        if (!write_grm_bin_square(grm_file, A, n)) throw("Error: can not open the file [" + grm_file + "] to write.");
         cout << "GRM of " << n << " individuals has been saved in the file [" + grm_file + "] (in binary format)." << endl;
     } else {
         // gzip text "i \t j \t N \t A" (scientific, 6 digits), 1-based, j <= i (grm.cpp:321-331).  Written as
@@ -430,10 +433,10 @@ void gcta_host::output_grm(const vector<float>& A, const vector<int32_t>& N, boo
                     try {
                         if (use_zlib) {
                             string text;
-                            grm_text_gz::format_rows(A.data(), N.data(), blocks[b].first, blocks[b].second, text);
+                            grm_text_gz::format_rows(A, N, blocks[b].first, blocks[b].second, text);
                             gz_member(text, member);
                         } else
-                            grm_text_gz::encode_rows(A.data(), N.data(), blocks[b].first, blocks[b].second, member);
+                            grm_text_gz::encode_rows(A, N, blocks[b].first, blocks[b].second, member);
                     } catch (const string& e) { err = e; }
                     catch (const std::exception& e) { err = string("Error: ") + e.what(); }
                     {
@@ -502,7 +505,7 @@ int gcta_host::selftest_writer(int64_t n, bool output_bin)
             N[o] = 500000 - (int32_t)(next() % 20000);
         }
     const auto t0 = std::chrono::steady_clock::now();
-    output_grm(A, N, output_bin);
+    output_grm(A.data(), N.data(), output_bin);
     const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     printf("writer selftest: n=%lld, %zu pairs, %.3f s, %.1f M pairs/s\n", (long long)n, tri, sec, tri / sec / 1e6);
     return 0;

@@ -311,6 +311,22 @@ def test_host_side_of_the_flags_matches_the_reference_without_a_gpu(flags, tmp_p
         assert ours == theirs
 
 
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
+@pytest.mark.parametrize("cut", [1, 23 * 17, 23 * 399 + 5])
+def test_truncated_bed_is_reported_like_the_reference(tmp_path, cut):
+    """The .bed reader uses pread from several threads; a file that ends early (mid-row, or rows missing) must give the
+    reference's message (data.cpp:173) - also when only some rows are wanted (--exclude)."""
+    n, m = _flag_dataset(tmp_path)
+    raw = open(tmp_path / "t.bed", "rb").read()
+    assert len(raw) == 3 + m * 23
+    open(tmp_path / "t.bed", "wb").write(raw[:len(raw) - cut])
+    for extra in ([], ["--exclude", "exclude.txt"]):
+        rr = oracle.run_ref(["--bfile", "t", "--autosome"] + extra + ["--make-grm", "--out", "ref"], cwd=tmp_path)
+        rm = run_cli(["--bfile", "t", "--autosome"] + extra + ["--make-grm", "--out", "mine"], tmp_path)
+        assert rr.stderr.strip() == "Error: problem with the BED file...has the FAM/BIM file been changed?"
+        assert rm.stderr.strip() == rr.stderr.strip()
+
+
 @pytest.mark.gpu
 @pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/gcta_ref not built")
 @pytest.mark.parametrize("flags", FLAG_SETS, ids=[" ".join(f) for f in FLAG_SETS])
