@@ -227,7 +227,33 @@ def main_ours(a, rank, world, local_rank):
             h2d = stride * m
         else:
             import torch.distributed as tdist
-            if os.environ.get("GCTA_B200_E2E_EXCHANGE", "peer") == "nccl":
+            host = tdist.new_group(backend="gloo")   # host barriers only; keeps NCCL kernels out of the timed region
+            peer_err = ""
+            if os.environ.get("GCTA_B200_E2E_EXCHANGE", "peer") != "nccl":
+                # set the peer exchange up; if CUDA IPC is not available on this box (any rank), every rank falls back to
+                # the NCCL all-gather below instead of losing the run
+                try:
+                    ex = abi.Exchange(plan, rank, world)      # the plan now reads the exchange's (zeroed) gather buffer
+                except Exception as e:   # noqa: BLE001
+                    peer_err = str(e)
+                blobs = [None] * world
+                tdist.all_gather_object(blobs, ex.blob if ex is not None else b"", group=host)
+                if ex is not None and all(len(b) == len(ex.blob) for b in blobs):
+                    try:
+                        ex.connect(b"".join(blobs))
+                    except Exception as e:   # noqa: BLE001
+                        peer_err = str(e)
+                elif ex is not None:
+                    peer_err = "a peer could not create its exchange"
+                if ranks.min(0.0 if peer_err else 1.0) < 1.0:
+                    peer_err = peer_err or "a peer could not connect"
+                    if ex is not None:
+                        ex.disconnect()
+                    barrier()
+                    if ex is not None:
+                        ex.close()
+                    ex = None
+            if ex is None:
                 # every rank pulls 1/N of the SNP rows over its own PCIe link, one NCCL all-gather of the packed rows over
                 # NVLink into the buffer the plan reads, then each computes its row band (nothing overlaps the exchange)
                 rows_per = -(-m // world)
@@ -249,12 +275,6 @@ def main_ours(a, rank, world, local_rank):
                 # gcta_b200_exchange_*: the file rows travel in 32 segments; of each, a rank uploads 1/N over its own PCIe
                 # link and pulls the rest out of its peers' HBM with the copy engines over NVLink (CUDA IPC, no SM used), and
                 # the plan starts chunk c as soon as the segments it reads are in: the exchange hides behind the compute
-                host = tdist.new_group(backend="gloo")   # host barriers only; keeps NCCL kernels out of the timed region
-                ex = abi.Exchange(plan, rank, world)      # the plan now reads the exchange's (zeroed) gather buffer
-                blobs = [None] * world
-                tdist.all_gather_object(blobs, ex.blob, group=host)
-                ex.connect(b"".join(blobs))
-
                 e2e_phases = {}
 
                 def e2e_step():
@@ -286,6 +306,8 @@ def main_ours(a, rank, world, local_rank):
         d2h = sum_over_ranks(cnt * 4 * (2 if o.total_missing > 0 else 1))
         e2e = {"value": pairs_total * m * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(h2d)),
                "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps, "api": api}
+        if world > 1 and peer_err:
+            e2e["peer_exchange_unavailable"] = peer_err[:300]
         if ex is not None:
             ph = ranks.gather([e2e_phases[k] for k in sorted(e2e_phases)])
             e2e["last_step_ms_per_rank"] = {k: [round(float(r[i]), 1) for r in ph] for i, k in enumerate(sorted(e2e_phases))}
