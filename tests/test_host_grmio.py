@@ -113,6 +113,55 @@ CASES = [
 ]
 
 
+@pytest.mark.parametrize("seed", range(16))
+def test_randomised_grm_manipulation(tmp_path, seed):
+    """Random GRMs with many related pairs (so that --grm-cutoff has ties to break), random sizes down to n = 1, random
+    keep lists, cutoffs, adjustment factors and merges of two or three files with shuffled / partial ID lists."""
+    rng = np.random.default_rng(900 + seed)
+    n = int(rng.integers(1, 45))
+    ids = [("F%d" % i, "I%d" % i) for i in range(n)]
+
+    def write(prefix, idl, scale):
+        k = len(idl)
+        with gzip.open(tmp_path / (prefix + ".grm.gz"), "wt") as f:
+            for i in range(k):
+                for j in range(i + 1):
+                    a = 1.0 + 0.1 * rng.standard_normal() if i == j else scale * rng.standard_normal()
+                    f.write("%d\t%d\t%d\t%.6e\n" % (i + 1, j + 1, int(rng.integers(0 if seed % 5 == 0 else 1, 4000)), np.float32(a)))
+        (tmp_path / (prefix + ".grm.id")).write_text("".join("%s\t%s\n" % t for t in idl))
+
+    write("a", ids, 0.2)
+    args = ["--grm", "a"]
+    if seed % 4 == 3 and n > 1:
+        perm = [ids[i] for i in rng.permutation(n)]
+        write("b", perm, 0.05)
+        write("c", perm[: max(1, n - int(rng.integers(0, 3)))], 0.05)
+        (tmp_path / "list.txt").write_text("a\nb\n" + ("c\n" if seed % 8 == 7 else ""))
+        args = ["--mgrm", "list.txt"]
+    else:
+        if seed % 2 == 1 and n > 2:
+            keep = sorted(rng.choice(n, size=int(rng.integers(1, n)), replace=False))
+            (tmp_path / "k.txt").write_text("".join("F%d I%d\n" % (i, i) for i in keep))
+            args += ["--keep" if seed % 3 else "--remove", "k.txt"]
+        if seed % 3 != 1:
+            args += ["--grm-cutoff", "%.3f" % float(rng.choice([0.0, 0.05, 0.15, 0.3]))]
+        if seed % 4 == 2 and n > 3:
+            args += ["--grm-adj", "%.2f" % float(rng.choice([0.0, 0.2, 1.0]))]
+    args += ["--make-grm-bin" if seed % 6 == 4 else "--make-grm"]
+    r = oracle.run_ref(args + ["--out", "zzr"], cwd=tmp_path, timeout=300)
+    m = subprocess.run([BIN] + args + ["--out", "zzm"], cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert _body(m.stdout, "zzm") == _body(r.stdout, "zzr"), " ".join(args)
+    assert m.stderr.replace("zzm", "X") == r.stderr.replace("zzr", "X")
+    for ext in (".grm.gz", ".grm.bin", ".grm.id"):
+        rf, mf = tmp_path / ("zzr" + ext), tmp_path / ("zzm" + ext)
+        assert rf.exists() == mf.exists(), ext
+        if rf.exists():
+            if ext == ".grm.gz":
+                assert gzip.decompress(mf.read_bytes()) == gzip.decompress(rf.read_bytes()), " ".join(args)
+            else:
+                assert mf.read_bytes() == rf.read_bytes(), " ".join(args)
+
+
 @pytest.mark.parametrize("name,args", CASES, ids=[c[0] for c in CASES])
 def test_grm_manipulation_is_byte_identical_to_the_reference(data, name, args):
     rp, mp = "r_" + name, "m_" + name
