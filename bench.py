@@ -283,6 +283,8 @@ def main_ours(a, rank, world, local_rank):
                     ex.post(h_bed.data_ptr())
                     tdist.barrier(group=host)   # every rank has recorded this step's segment events
                     ex.pull()
+                    if os.environ.get("GCTA_B200_E2E_PREFETCH") == "1":
+                        ex.finish()   # diagnosis only: the whole exchange first, then the compute (nothing concurrent)
                     t.append(time.perf_counter())
                     oo = plan.run_to_host(None, A_ptr, N_ptr)   # waits per chunk; finalize + D2H pipelined behind the last SYRK
                     t.append(time.perf_counter())
