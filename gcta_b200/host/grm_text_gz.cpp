@@ -15,13 +15,24 @@ namespace grm_text_gz {
 // ---------------------------------------------------------------------------------------------
 // number formatting
 // ---------------------------------------------------------------------------------------------
+static const char DIGIT_PAIRS[201] =
+    "00010203040506070809101112131415161718192021222324252627282930313233343536373839404142434445464748495051525354555657585960616263646566676869"
+    "707172737475767778798081828384858687888990919293949596979899";
+
 static inline char* put_uint(char* q, uint64_t v)
 {
     char tmp[24];
-    int k = 0;
-    do { tmp[k++] = (char)('0' + v % 10); v /= 10; } while (v);
-    while (k) *q++ = tmp[--k];
-    return q;
+    int k = 24;
+    while (v >= 100) {   // two digits at a time, from the right
+        const uint64_t r = v % 100;
+        v /= 100;
+        k -= 2;
+        memcpy(tmp + k, DIGIT_PAIRS + 2 * r, 2);
+    }
+    if (v >= 10) { k -= 2; memcpy(tmp + k, DIGIT_PAIRS + 2 * v, 2); }
+    else tmp[--k] = (char)('0' + v);
+    memcpy(q, tmp + k, (size_t)(24 - k));
+    return q + (24 - k);
 }
 
 // printf("%.6e") (the reference's `setf(scientific); precision(6)`, grm.cpp:326-327): the value is scaled by an exact
@@ -36,22 +47,30 @@ int put_e6(char* q, double v)
         if (v == 0.0 && !std::signbit(v)) { memcpy(q, "0.000000e+00", 12); return 12; }
         return snprintf(q, 32, "%.6e", v);
     }
-    int e2;
-    std::frexp(a, &e2);                                    // a = f * 2^e2, f in [0.5, 1)
-    int e = (int)std::floor((e2 - 1) * 0.30102999566398);  // decimal exponent, possibly one too small
+    uint64_t bits;
+    memcpy(&bits, &a, 8);
+    const int e2 = (int)((bits >> 52) & 0x7ff) - 1022;     // a = f * 2^e2, f in [0.5, 1) (a is normal in this range)
+    int e = ((e2 - 1) * 1233) >> 12;                       // floor((e2 - 1) * log10(2)), possibly one off: fixed below
     for (int attempt = 0; attempt < 3; attempt++) {
         const int k = 6 - e;   // a * 10^k should lie in [1e6, 1e7)
         const double scaled = k >= 0 ? a * P10[k] : a / P10[-k];
         if (scaled < 1e6) { e--; continue; }
         if (scaled >= 1e7) { e++; continue; }
-        const double fl = std::floor(scaled), frac = scaled - fl;
+        const uint64_t fl = (uint64_t)scaled;
+        const double frac = scaled - (double)fl;
         if (std::fabs(frac - 0.5) < 1e-5) return snprintf(q0, 32, "%.6e", v);   // too close to a tie to decide here
-        uint64_t d = (uint64_t)fl + (frac > 0.5 ? 1 : 0);
+        uint32_t d = (uint32_t)fl + (frac > 0.5 ? 1u : 0u);
         int ee = e;
-        if (d >= 10000000ull) { d = 1000000ull; ee++; }
+        if (d >= 10000000u) { d = 1000000u; ee++; }
         if (std::signbit(v)) *q++ = '-';
+        // 7 digits: the leading one, then three pairs out of a 2-digit table
+        const uint32_t hi = d / 10000u, lo = d - hi * 10000u;      // hi: 3 digits, lo: 4 digits
+        const uint32_t h0 = hi / 100u, h12 = hi - h0 * 100u, l01 = lo / 100u, l23 = lo - l01 * 100u;
         char dig[7];
-        for (int t = 6; t >= 0; t--) { dig[t] = (char)('0' + d % 10); d /= 10; }
+        dig[0] = (char)('0' + h0);
+        memcpy(dig + 1, DIGIT_PAIRS + 2 * h12, 2);
+        memcpy(dig + 3, DIGIT_PAIRS + 2 * l01, 2);
+        memcpy(dig + 5, DIGIT_PAIRS + 2 * l23, 2);
         *q++ = dig[0]; *q++ = '.';
         for (int t = 1; t < 7; t++) *q++ = dig[t];
         *q++ = 'e';
@@ -315,6 +334,7 @@ struct BitWriter {
 struct CountSink {
     uint32_t lit[NLIT] = {0}, dist[NDIST] = {0};
     inline void literal(uint8_t b) { lit[b]++; }
+    inline void literal2(uint8_t b0, uint8_t b1) { lit[b0]++; lit[b1]++; }
     inline void match(int len, int d) { lit[257 + len_symbol(len)]++; dist[dist_symbol(d)]++; }
 };
 
@@ -338,6 +358,10 @@ struct EmitSink {
         }
     }
     inline void literal(uint8_t b) { bw.put(lcode[b], llen[b]); }
+    inline void literal2(uint8_t b0, uint8_t b1)   // two codes (<= 15 bits each) in one go
+    {
+        bw.put((uint32_t)lcode[b0] | ((uint32_t)lcode[b1] << llen[b0]), llen[b0] + llen[b1]);
+    }
     inline void match(int len, int d)
     {
         bw.put(mlen_bits[len], mlen_n[len]);
@@ -375,7 +399,9 @@ struct Tokeniser {
     {
         if (len <= 0) return;
         flush_run();
-        for (int k = 0; k < len; k++) sink.literal((uint8_t)bytes[k]);
+        int k = 0;
+        for (; k + 1 < len; k += 2) sink.literal2((uint8_t)bytes[k], (uint8_t)bytes[k + 1]);
+        if (k < len) sink.literal((uint8_t)bytes[k]);
     }
     // `prev` == nullptr: first line of a member (nothing to refer to)
     inline void line(const Line& cur, const Line* prev)
