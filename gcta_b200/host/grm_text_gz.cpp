@@ -93,9 +93,10 @@ int put_g15(char* q, double v)
     const double a = std::fabs(v);
     if (v == 0.0 && !std::signbit(v)) { *q = '0'; return 1; }
     if (!(a >= 1e-15 && a < 1e15)) return snprintf(q, 40, "%.15g", v);
-    int e2;
-    std::frexp(a, &e2);
-    int e = (int)std::floor((e2 - 1) * 0.30102999566398);
+    uint64_t bits;
+    memcpy(&bits, &a, 8);
+    const int e2 = (int)((bits >> 52) & 0x7ff) - 1022;
+    int e = ((e2 - 1) * 1233) >> 12;
     for (int attempt = 0; attempt < 3; attempt++) {
         const int k = 6 - e;
         const double scaled = k >= 0 ? a * P10[k] : a / P10[-k];
