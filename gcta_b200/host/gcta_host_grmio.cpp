@@ -13,8 +13,10 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <fstream>
 #include <iostream>
+#include <memory>
 #include <mutex>
 #include <thread>
 #include <unordered_map>
@@ -254,24 +256,90 @@ void gcta_host::read_grm_gz(const string& grm_file, vector<string>& grm_id, bool
         gzFile zf = gzopen(grm_gzfile.c_str(), "rb");
         if (!zf) throw("Error: can not open the file [" + grm_gzfile + "] to read.");
         gzbuffer(zf, 1u << 20);
-        vector<char> buf(8u << 20);
-        size_t have = 0;
+        // One stream can only be inflated by one thread; this thread does that and cuts the text into blocks at line
+        // ends, a few workers parse the blocks.  Results are kept per block so that warnings and the first error come
+        // out in file order.
+        constexpr size_t BLOCK = 8u << 20;
+        struct Blk { vector<char> data; size_t len = 0; int64_t idx = 0; bool last = false; BlockResult R; };
+        std::deque<std::unique_ptr<Blk>> all;   // every block in file order (results live here)
+        std::deque<Blk*> todo;
+        std::mutex mu;
+        std::condition_variable cv_todo, cv_room;
+        bool done_reading = false;
+        std::atomic<int64_t> first_bad(INT64_MAX);   // index of the earliest block with a bad line: later blocks are skipped
+        size_t in_flight = 0;
+        const int W = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+        vector<std::thread> workers;
+        for (int t = 0; t < W; t++)
+            workers.emplace_back([&]() {
+                for (;;) {
+                    Blk* b;
+                    {
+                        std::unique_lock<std::mutex> lk(mu);
+                        cv_todo.wait(lk, [&] { return !todo.empty() || done_reading; });
+                        if (todo.empty()) return;
+                        b = todo.front();
+                        todo.pop_front();
+                    }
+                    if (b->idx < first_bad.load()) {
+                        parse_block(b->data.data(), b->data.data() + b->len, b->last, n, _grm.data(), _grm_N.data(), errmsg, b->R);
+                        if (!b->R.err.empty()) {
+                            int64_t cur = first_bad.load();
+                            while (b->idx < cur && !first_bad.compare_exchange_weak(cur, b->idx)) {}
+                        }
+                    }
+                    vector<char>().swap(b->data);
+                    { std::lock_guard<std::mutex> lk(mu); in_flight--; }
+                    cv_room.notify_one();
+                }
+            });
+        string read_error;
+        vector<char> carry;
         bool eof = false;
-        while (!eof) {
-            const int got = gzread(zf, buf.data() + have, (unsigned)(buf.size() - have));
-            if (got < 0) { gzclose(zf); throw("Error: failed to read [" + grm_gzfile + "] (corrupt gzip stream)."); }
-            if (got == 0) eof = true;
-            have += (size_t)got;
-            BlockResult R;
-            const char* p = parse_block(buf.data(), buf.data() + have, eof, n, _grm.data(), _grm_N.data(), errmsg, R);
-            for (const string& w : R.warnings) cout << "Warning: " << w << endl;
-            if (!R.err.empty()) { gzclose(zf); throw R.err; }
-            nline += R.nline;
-            have = (size_t)(buf.data() + have - p);
-            if (have == buf.size()) { gzclose(zf); throw(errmsg + string(p, p + 200)); }   // a "line" longer than the buffer
-            memmove(buf.data(), p, have);
+        while (!eof && first_bad.load() == INT64_MAX) {
+            std::unique_ptr<Blk> b(new Blk());
+            b->data.resize(BLOCK + carry.size());
+            memcpy(b->data.data(), carry.data(), carry.size());
+            size_t have = carry.size();
+            carry.clear();
+            while (have < b->data.size()) {
+                const int got = gzread(zf, b->data.data() + have, (unsigned)(b->data.size() - have));
+                if (got < 0) { read_error = "Error: failed to read [" + grm_gzfile + "] (corrupt gzip stream)."; eof = true; break; }
+                if (got == 0) { eof = true; break; }
+                have += (size_t)got;
+            }
+            if (!read_error.empty()) break;
+            size_t cutpos = have;
+            if (!eof) {   // keep the unfinished last line for the next block
+                while (cutpos > 0 && b->data[cutpos - 1] != '\n') cutpos--;
+                if (cutpos == 0) { read_error = errmsg + string(b->data.data(), b->data.data() + 200); break; }   // a "line" longer than a block
+                carry.assign(b->data.begin() + (std::ptrdiff_t)cutpos, b->data.begin() + (std::ptrdiff_t)have);
+            }
+            b->len = cutpos;
+            b->last = eof;
+            b->idx = (int64_t)all.size();
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv_room.wait(lk, [&] { return in_flight < (size_t)(2 * W); });
+                in_flight++;
+                todo.push_back(b.get());
+                all.push_back(std::move(b));
+            }
+            cv_todo.notify_one();
         }
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            done_reading = true;
+        }
+        cv_todo.notify_all();
+        for (auto& w : workers) w.join();
         gzclose(zf);
+        for (const auto& b : all) {
+            for (const string& w : b->R.warnings) cout << "Warning: " << w << endl;
+            if (!b->R.err.empty()) throw b->R.err;
+            nline += b->R.nline;
+        }
+        if (!read_error.empty()) throw read_error;
     }
     if (nline != (int64_t)tri) throw("Error: incorrect number of lines in the grm file. *.grm.gz file and *.grm.id file are mismatched?");
     cout << "Pairwise genetic relationships between " << n << " individuals are included from [" + grm_gzfile + "]." << endl;

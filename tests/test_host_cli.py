@@ -93,6 +93,45 @@ def test_structured_gz_encoder_writes_the_same_text_as_zlib(tmp_path):
     assert gzip.decompress(open(tmp_path / "re_a.grm.gz", "rb").read()) == gzip.decompress(open(tmp_path / "re_b.grm.gz", "rb").read())
 
 
+def test_single_stream_gz_is_read_in_blocks_by_several_parsers(tmp_path):
+    """A .grm.gz that is one plain gzip stream (what the reference writes) is inflated by one thread and parsed in 8 MB
+    blocks by several: same matrix as the member-indexed route, N == 0 warnings in file order, and of two bad lines in
+    different blocks the first one is reported (n = 1300: 25 MB of text, four blocks)."""
+    import gzip
+    n = 1300
+    _selftest_writer(n, "a", tmp_path)
+    text = gzip.decompress(open(tmp_path / "a.grm.gz", "rb").read())
+    assert len(text) > 2.9 * (8 << 20)
+    ids = open(tmp_path / "a.grm.id").read()
+
+    def put(name, t):
+        open(tmp_path / (name + ".grm.gz"), "wb").write(gzip.compress(t, 1))
+        open(tmp_path / (name + ".grm.id"), "w").write(ids)
+
+    put("plain", text)
+    ra = run_cli(["--grm", "a", "--make-grm", "--out", "ra"], tmp_path)
+    rp = run_cli(["--grm", "plain", "--make-grm", "--out", "rp"], tmp_path)
+    assert ra.stderr.strip() == "" and rp.stderr.strip() == ""
+    assert gzip.decompress(open(tmp_path / "ra.grm.gz", "rb").read()) == gzip.decompress(open(tmp_path / "rp.grm.gz", "rb").read())
+    lines = text.split(b"\n")
+    zero = [5, 300000, 610000, 840000]
+    for k in zero:
+        f = lines[k].split(b"\t")
+        lines[k] = f[0] + b"\t" + f[1] + b"\t0\t0.000000e+00"
+    put("warn", b"\n".join(lines))
+    rw = run_cli(["--grm", "warn", "--make-grm", "--out", "rw"], tmp_path)
+    warned = [ln for ln in rw.stdout.split("\n") if ln.startswith("Warning: ")]
+    assert rw.stderr.strip() == "" and warned == ["Warning: " + lines[k].decode() for k in zero]
+    lines[700000] = b"oops"
+    lines[420000] = b"12\t34\t56"
+    put("bad", b"\n".join(lines))
+    rb = run_cli(["--grm", "bad", "--make-grm", "--out", "rb"], tmp_path)
+    assert rb.stderr.strip().endswith("Error occurs in line:\n12\t34\t56")
+    warned = [ln for ln in rb.stdout.split("\n") if ln.startswith("Warning: ")]
+    assert warned == ["Warning: " + lines[k].decode() for k in zero[:2]]      # only what precedes the bad line
+    assert not os.path.exists(tmp_path / "rb.grm.gz")
+
+
 def test_parallel_bin_writer_lays_out_the_full_square(tmp_path):
     """.grm.bin is written by a pool of threads in 16-row bands with pwrite (host/grm_bin_writer.h): n x n float64,
     symmetric, and element for element the matrix the text writer prints (n = 333: 21 bands, the last one ragged)."""
