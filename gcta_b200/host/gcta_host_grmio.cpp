@@ -95,6 +95,7 @@ inline bool parse_double(const char*& p, const char* e, double& v)
     } else {
         const string tok(p, q);
         v = strtod(tok.c_str(), nullptr);
+        if (std::isinf(v)) return false;   // out of range: `ss >> double` sets failbit, the reference rejects the line
     }
     p = q;
     return true;

@@ -113,6 +113,37 @@ CASES = [
 ]
 
 
+ODD_LINES = [
+    b"1\t1\t5\t1.0", b"1 1 5 1.0", b"  1   1  5   1.0  ", b"1\t1\t5\t1.0\r", b"1\t1\t5\t.5", b"1\t1\t5\t5.", b"1\t1\t5\t1e", b"1\t1\t5\t1e+",
+    b"1\t1\t5\t1.0e-3x", b"+1\t1\t5\t1.0", b"1\t+1\t5\t1.0", b"1\t1\t+5\t+1.0", b"1\t1\t5\t-0.0", b"1\t1\t5\tnan", b"1\t1\t5\tinf", b"1\t1\t5\t0x10",
+    b"1\t1\t5.7\t1.0", b"1\t1\t5e2\t1.0", b"1.0\t1\t5\t1.0", b"1\t1\t5\t1.0\t", b"1\t1\t5\t1.0 extra", b"1\t1\t5", b"", b"1\t1\t-3\t1.0", b"1\t1\t0\t1.0",
+    b"01\t01\t005\t001.500", b"1\t1\t5\t1.23456789012345678901234567890", b"1\t1\t5\t1e-400", b"1\t1\t5\t1e400",
+    b"1\t1\t5\t123456789012345678901234567890", b"1\t1\t5\t0.000000000000000000000000000001", b"1\t1\t99999999999\t1.0", b"1\t1\t5\t1,0",
+    b"2\t1\t5\t1.0", b"1\t2\t5\t1.0", b"1\t1\t5\t1.0E+00", b"1\t1\t5\t1D0", b"1\t1\t5\t 1.0\n", b"1\t1\t5\t1.0\n\n", b"\n1\t1\t5\t1.0",
+    b"99999999999\t1\t5\t1.0",
+]
+
+
+def test_odd_lines_are_accepted_or_rejected_like_the_reference(tmp_path):
+    """The tokenizer against `stringstream >> int >> int >> double >> double` (grm.cpp:428-441) on 41 one-line files:
+    separators, signs, bare dots, dangling exponents, hex, nan/inf, overflow and underflow, too few / too many tokens,
+    CR LF, empty lines, out-of-range indices.  Same verdict, same message, same re-saved value.  (Not compared: indices
+    below 1, which the reference does not check and writes out of bounds with.)"""
+    (tmp_path / "x.grm.id").write_text("F0\tI0\n")
+    for k, c in enumerate(ODD_LINES):
+        (tmp_path / "x.grm.gz").write_bytes(gzip.compress(c if c.endswith(b"\n") or c == b"" else c + b"\n"))
+        res = []
+        for tag, run in (("zzr", lambda a: oracle.run_ref(a, cwd=tmp_path, timeout=60)),
+                         ("zzm", lambda a: subprocess.run([BIN] + a, cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60))):
+            for ext in (".grm.gz", ".grm.id"):
+                if (tmp_path / (tag + ext)).exists():
+                    os.remove(tmp_path / (tag + ext))
+            p = run(["--grm", "x", "--make-grm", "--out", tag])
+            out = gzip.decompress((tmp_path / (tag + ".grm.gz")).read_bytes()) if (tmp_path / (tag + ".grm.gz")).exists() else None
+            res.append((p.stderr.replace(tag, "X"), out, [ln for ln in p.stdout.split("\n") if ln.startswith("Warning")]))
+        assert res[0] == res[1], (k, c)
+
+
 @pytest.mark.parametrize("seed", range(16))
 def test_randomised_grm_manipulation(tmp_path, seed):
     """Random GRMs with many related pairs (so that --grm-cutoff has ties to break), random sizes down to n = 1, random
