@@ -34,13 +34,24 @@ void gcta_host::read_famfile(const string& famfile)
     if (!fam) throw("Error: can not open the file [" + famfile + "] to read.");
     cout << "Reading PLINK FAM file from [" + famfile + "]." << endl;
     _fid.clear(); _pid.clear(); _fa_id.clear(); _mo_id.clear(); _sex.clear(); _pheno.clear();
-    string tok[6];
-    // six whitespace-separated tokens per individual; SEX and PHENO go through atoi (data.cpp:53-67)
-    while (fam >> tok[0]) {
-        for (int t = 1; t < 6; t++) fam >> tok[t];
-        _fid.push_back(tok[0]); _pid.push_back(tok[1]); _fa_id.push_back(tok[2]); _mo_id.push_back(tok[3]);
-        _sex.push_back(atoi(tok[4].c_str()));
-        _pheno.push_back(atoi(tok[5].c_str()));
+    // six whitespace-separated tokens per individual; SEX and PHENO go through atoi (data.cpp:53-67).  Same loop
+    // exit as the reference: end-of-file seen while reading a first field ends the loop, and a record cut short by the
+    // end of the file is completed with the last token read
+    string tok;
+    while (fam) {
+        fam >> tok;
+        if (fam.eof()) break;
+        _fid.push_back(tok);
+        fam >> tok;
+        _pid.push_back(tok);
+        fam >> tok;
+        _fa_id.push_back(tok);
+        fam >> tok;
+        _mo_id.push_back(tok);
+        fam >> tok;
+        _sex.push_back(atoi(tok.c_str()));
+        fam >> tok;
+        _pheno.push_back(atoi(tok.c_str()));
     }
     _indi_num = (int)_fid.size();
     cout << _indi_num << " individuals to be included from [" + famfile + "]." << endl;
@@ -63,15 +74,29 @@ void gcta_host::read_bimfile(const string& bimfile)
     if (!bim) throw("Error: can not open the file [" + bimfile + "] to read.");
     cout << "Reading PLINK BIM file from [" + bimfile + "]." << endl;
     _chr.clear(); _snp_name.clear(); _genet_dst.clear(); _bp.clear(); _allele1.clear(); _allele2.clear();
-    int chr = 0, bp = 0;
-    double cm = 0.0;
-    char a1 = '0', a2 = '0';
-    string name;
-    // int chr, name, double cM, int bp, then ONE character per allele (data.cpp:104-118)
-    while (bim >> chr) {
-        bim >> name >> cm >> bp >> a1 >> a2;
-        _chr.push_back(chr); _snp_name.push_back(name); _genet_dst.push_back(cm); _bp.push_back(bp);
-        _allele1.push_back(a1); _allele2.push_back(a2);
+    // int chr, name, double cM, int bp, then ONE character per allele (data.cpp:104-118).  The loop ends like the
+    // reference's: only end-of-file on the first field stops it cleanly; a field that does not parse (a chromosome "X",
+    // a two-letter allele followed by text, a fractional position) still appends one last record - built from whatever
+    // the failed extractions leave in the variables - before the failed stream ends the loop.  Pipelines that feed
+    // such files get the same SNP count and the same downstream messages.
+    int ival = 0;
+    double dval = 0.0;
+    char cval = '0';
+    string sval;
+    while (bim) {
+        bim >> ival;
+        if (bim.eof()) break;
+        _chr.push_back(ival);
+        bim >> sval;
+        _snp_name.push_back(sval);
+        bim >> dval;
+        _genet_dst.push_back(dval);
+        bim >> ival;
+        _bp.push_back(ival);
+        bim >> cval;
+        _allele1.push_back(cval);
+        bim >> cval;
+        _allele2.push_back(cval);
     }
     _snp_num = (int)_chr.size();
     _ref_A = _allele1;   // data.cpp:121
@@ -283,9 +308,14 @@ void gcta_host::update_sex(const string& sex_file)
     _sex.assign(_indi_num, 0);
     vector<char> confirm(_indi_num, 0);
     int icount = 0;
-    string fid, pid, code, rest;
-    while (in >> fid) {
-        in >> pid >> code;
+    // `code` also receives the rest of each line (as the reference's one buffer does, data.cpp:704-716): a last record
+    // without a sex code is then reported with an empty code instead of silently taking the previous one
+    string fid, pid, code;
+    while (in) {
+        in >> fid;
+        if (in.eof()) break;
+        in >> pid;
+        in >> code;
         if (code != "1" && code != "2" && code != "M" && code != "F")
             throw("Error: unrecognized sex code: \"" + fid + " " + pid + " " + code + "\" in [" + sex_file + "].");
         auto it = _id_map.find(fid + ":" + pid);
@@ -294,7 +324,7 @@ void gcta_host::update_sex(const string& sex_file)
             confirm[it->second] = 1;
             icount++;
         }
-        std::getline(in, rest);
+        std::getline(in, code);
     }
     for (int i : _keep)
         if (!confirm[i]) throw("Error: sex information for all of the included individuals should be updated.");

@@ -76,7 +76,7 @@ void gcta_host::update_freq(const string& freq)
         if (it != _snp_name_map.end()) {
             if (f > 1.0 || f < 0.0) throw("Error: invalid value of allele frequency for the SNP " + snp + ".");
             if (a != _allele1[it->second] && a != _allele2[it->second])
-                throw("Invalid allele type \"" + string(1, a) + "\" for the SNP " + _snp_name[it->second] + ".");
+                throw("Invalid allele type \"\" for the SNP " + _snp_name[it->second] + ".");   // the reference's text: it means to quote the allele but quotes an empty string (data.cpp:912-913)
             _mu[it->second] = (a == _ref_A[it->second]) ? f * 2.0 : (1.0 - f) * 2.0;   // data.cpp:915-916
             confirm[it->second] = 1;
             icount++;
