@@ -97,6 +97,46 @@ def test_unusual_list_files(tmp_path, name):
     assert er == em or (er == "" and "no CUDA device" in em)
 
 
+OPTION_CASES = [
+    ["--bfile", "t", "--make-grm", "--make-grm"], ["--bfile", "t", "--make-grm", "--out"], ["--bfile", "t", "--make-grm", "--maf"],
+    ["--bfile", "t", "--maf", "--make-grm"], ["--bfile", "t", "--chr", "abc", "--make-grm"], ["--bfile", "t", "--chr", "0", "--make-grm"],
+    ["--bfile", "t", "--chr", "101", "--make-grm"], ["--bfile", "t", "--autosome-num", "0", "--make-grm"],
+    ["--bfile", "t", "--autosome-num", "101", "--make-grm"], ["--bfile", "t", "--make-grm", "--keep"], ["--bfile"], ["--make-grm"], [],
+    ["--bfile", "t"], ["--bfile", "t", "--autosome"], ["--bfile", "t", "--maf", "-0.1", "--make-grm"], ["--bfile", "t", "--max-maf", "0.6", "--make-grm"],
+    ["--bfile", "t", "--grm-alg", "2", "--make-grm"], ["--bfile", "t", "--grm-alg", "x", "--make-grm"], ["--bfile", "t", "--make-grm-bin", "--make-grm"],
+    ["--bfile", "t", "--make-grm", "--make-grm-xchr"], ["--bfile", "t", "--rm-high-ld", "0", "--make-grm"], ["--bfile", "t", "--rm-high-ld", "1", "--make-grm"],
+    ["--bfile", "t", "--freq", "--make-grm"], ["--bfile", "t", "--extract-snp", "rs1", "--exclude-snp", "rs1", "--make-grm"], ["--bfile", "t", "-make-grm"],
+    ["--bfile", "t", "make-grm"], ["--BFILE", "t"], ["--bfile", "t", "--autosome", "--chr", "2", "--make-grm"],
+    ["--bfile", "t", "--chr", "2", "--autosome", "--make-grm"], ["--bfile", "t", "--save-ram", "--autosome", "--make-grm"], ["--grm", "x"],
+    ["--grm", "x", "--make-grm", "--grm-cutoff", "2"], ["--grm", "x", "--pca", "0"], ["--mgrm", "x", "--grm-adj", "-1", "--make-grm"],
+    ["--grm", "x", "--dc", "2", "--make-grm"], ["--bfile", "t", "--out", "a", "--out", "b", "--make-grm"], ["--bfile", "t", "--update-sex", "nofile", "--make-grm"],
+    ["--bfile", "t", "--update-freq", "nofile", "--make-grm"], ["--bfile", "t", "--update-ref-allele", "nofile", "--make-grm"],
+]
+
+
+@pytest.mark.parametrize("args", OPTION_CASES, ids=[" ".join(a) or "(none)" for a in OPTION_CASES])
+def test_option_handling(tmp_path, args):
+    """option.cpp:17-51, 111-135, 170-327, 547-571: echo lines, range errors, flags without their value (the next
+    token or the sentinel is taken), repeated and unknown flags, nothing to do."""
+    (tmp_path / "t.fam").write_text("\n".join(_fam()) + "\n")
+    (tmp_path / "t.bim").write_text("\n".join(_bim()) + "\n")
+    (tmp_path / "t.bed").write_bytes(BED)
+    out = [] if "--out" in args else ["--out"]
+    r = oracle.run_ref(args + (out and out + ["zzr"]), cwd=tmp_path, timeout=60)
+    m = subprocess.run([BIN] + args + (out and out + ["zzm"]), cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60)
+
+    def log(stdout, tag):
+        lines = [ln for ln in stdout.replace("\r", "\n").split("\n") if ln.strip()]
+        lines = lines[lines.index("Options:"):] if "Options:" in lines else lines
+        lines = [ln.replace(tag, "X") for ln in lines if not ln.startswith(("Analysis started", "Analysis finished", "Computational time"))]
+        stop = [k for k, ln in enumerate(lines) if ln.startswith(("Calculating allele", "Recoding genotypes", "Calculating the genetic"))]
+        return lines[:stop[0]] if stop else lines
+
+    assert log(m.stdout, "zzm") == log(r.stdout, "zzr")
+    er, em = r.stderr.strip().replace("zzr", "X"), m.stderr.strip().replace("zzm", "X")
+    assert er == em or (er == "" and "no CUDA device" in em)
+
+
 @pytest.mark.parametrize("name", sorted(CASES), ids=sorted(CASES))
 def test_unusual_fam_and_bim_files(tmp_path, name):
     fam, bim, flags = CASES[name]
