@@ -173,13 +173,20 @@ void gcta_host::read_grm_gz(const string& grm_file, vector<string>& grm_id, bool
     if (!i_grm_id) throw("Error: can not open the file [" + grm_id_file + "] to read.");
     vector<string> fid, pid;
     grm_id.clear();
-    string a, b, rest;
-    while (i_grm_id >> a) {   // FID IID, rest of the line ignored
-        i_grm_id >> b;
-        fid.push_back(a);
-        pid.push_back(b);
-        grm_id.push_back(a + ":" + b);
-        std::getline(i_grm_id, rest);
+    // FID IID, rest of the line ignored.  One buffer for every extraction and the loop exit of the reference
+    // (grm.cpp:392-402), so that a last line with a single token behaves the same: dropped when the file ends right
+    // after it, otherwise completed with that same token
+    string tok;
+    while (i_grm_id) {
+        i_grm_id >> tok;
+        if (i_grm_id.eof()) break;
+        fid.push_back(tok);
+        string id = tok + ":";
+        i_grm_id >> tok;
+        pid.push_back(tok);
+        id += tok;
+        grm_id.push_back(id);
+        std::getline(i_grm_id, tok);
     }
     i_grm_id.close();
     const int64_t n = (int64_t)grm_id.size();

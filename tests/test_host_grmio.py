@@ -144,6 +144,37 @@ def test_odd_lines_are_accepted_or_rejected_like_the_reference(tmp_path):
         assert res[0] == res[1], (k, c)
 
 
+ID_FILES = {
+    "extra_columns": "F0 I0 x y\nF1 I1 z\nF2 I2\n", "crlf": "F0\tI0\r\nF1\tI1\r\nF2\tI2\r\n", "blank_lines": "F0 I0\n\nF1 I1\n\n\nF2 I2\n",
+    "no_final_newline": "F0 I0\nF1 I1\nF2 I2", "one_column_last": "F0 I0\nF1 I1\nF2", "one_column_last_nl": "F0 I0\nF1 I1\nF2\n",
+    "too_many": "F0 I0\nF1 I1\nF2 I2\nF3 I3\n", "too_few": "F0 I0\nF1 I1\n", "duplicate": "F0 I0\nF0 I0\nF2 I2\n", "empty": "",
+    "tabs_and_spaces": "  F0   I0  \n\tF1\tI1\t\nF2 I2\n",
+}
+
+
+@pytest.mark.parametrize("name", sorted(ID_FILES), ids=sorted(ID_FILES))
+def test_unusual_grm_id_files(tmp_path, name):
+    """.grm.id read like grm.cpp:392-402 (extra columns, CR LF, blank lines, a last line with one token, more or fewer
+    IDs than the matrix has rows, duplicates), alone and followed by --keep and --grm-cutoff."""
+    text = "".join("%d\t%d\t%d\t%.6e\n" % (i + 1, j + 1, 100 + i + j, 1.0 if i == j else 0.01 * (i - j)) for i in range(3) for j in range(i + 1))
+    (tmp_path / "x.grm.gz").write_bytes(gzip.compress(text.encode()))
+    (tmp_path / "x.grm.id").write_bytes(ID_FILES[name].encode())
+    (tmp_path / "k.txt").write_text("F0 I0\nF2 I2\n")
+    for extra in ([], ["--keep", "k.txt"], ["--grm-cutoff", "0.015"]):
+        res = []
+        for tag, binary in (("zzr", oracle.REF_BIN), ("zzm", BIN)):
+            p = subprocess.run([binary, "--grm", "x"] + extra + ["--make-grm", "--out", tag], cwd=tmp_path, stdout=subprocess.PIPE,
+                               stderr=subprocess.PIPE, text=True, timeout=60)
+            files = []
+            for ext in (".grm.gz", ".grm.id"):
+                f = tmp_path / (tag + ext)
+                files.append(None if not f.exists() else gzip.decompress(f.read_bytes()) if ext == ".grm.gz" else f.read_bytes())
+                if f.exists():
+                    os.remove(f)
+            res.append((_body(p.stdout, tag), p.stderr.replace(tag, "X"), files))
+        assert res[0] == res[1], (name, extra)
+
+
 @pytest.mark.parametrize("seed", range(16))
 def test_randomised_grm_manipulation(tmp_path, seed):
     """Random GRMs with many related pairs (so that --grm-cutoff has ties to break), random sizes down to n = 1, random
