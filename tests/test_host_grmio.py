@@ -175,6 +175,32 @@ def test_unusual_grm_id_files(tmp_path, name):
         assert res[0] == res[1], (name, extra)
 
 
+MGRM_LISTS = {
+    "plain": "a\nb\n", "commas_semicolons": "a,\nb;\n", "two_tokens_on_a_line": "a b\n", "tabs_and_spaces": "\ta\t\n  b  \n", "crlf": "a\r\nb\r\n",
+    "same_file_twice": "a\na\n", "single": "a\n", "empty": "", "blank_only": "\n\n", "missing_file": "a\nnothere\n", "no_final_newline": "a\nb",
+    "comment_like": "a\nb\n#comment\n",
+}
+
+
+@pytest.mark.parametrize("name", sorted(MGRM_LISTS), ids=sorted(MGRM_LISTS))
+def test_unusual_mgrm_lists(tmp_path, name):
+    """The --mgrm file list is split like StrFunc::split_string (" ,\\t;\\n"); only lines with exactly one token count
+    (grm.cpp:656-672)."""
+    for nm, s in (("a", 0), ("b", 5)):
+        text = "".join("%d\t%d\t%d\t%.6e\n" % (i + 1, j + 1, 100 + i + j + s, 1.0 if i == j else 0.01 * (i - j) + 0.001 * s)
+                       for i in range(3) for j in range(i + 1))
+        (tmp_path / (nm + ".grm.gz")).write_bytes(gzip.compress(text.encode()))
+        (tmp_path / (nm + ".grm.id")).write_text("F0 I0\nF1 I1\nF2 I2\n")
+    (tmp_path / "l.txt").write_bytes(MGRM_LISTS[name].encode())
+    res = []
+    for tag, binary in (("zzr", oracle.REF_BIN), ("zzm", BIN)):
+        p = subprocess.run([binary, "--mgrm", "l.txt", "--make-grm", "--out", tag], cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                           text=True, timeout=60)
+        f = tmp_path / (tag + ".grm.gz")
+        res.append((_body(p.stdout, tag), p.stderr.replace(tag, "X"), gzip.decompress(f.read_bytes()) if f.exists() else None))
+    assert res[0] == res[1]
+
+
 @pytest.mark.parametrize("seed", range(16))
 def test_randomised_grm_manipulation(tmp_path, seed):
     """Random GRMs with many related pairs (so that --grm-cutoff has ties to break), random sizes down to n = 1, random
