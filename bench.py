@@ -124,6 +124,8 @@ def main_reference(a, rank, world):
     if not oracle.have_ref():
         raise RuntimeError("oracle/_ref/gcta_ref is not built")
     n_s, m_s = a.ref_n, a.ref_m
+    if a.warmup + a.steps > 20:   # keep the whole run within a few minutes: ~8 s per step at the default sample
+        m_s = max(1000, int(m_s * 20 / (a.warmup + a.steps)))
     # the reference has no threading of its own; all host cores are used by running one job per core
     procs = a.ref_procs if a.ref_procs > 0 else len(os.sched_getaffinity(0))
     secs = []
