@@ -307,7 +307,7 @@ void gcta_host::read_grm_gz(const string& grm_file, vector<string>& grm_id, bool
         while (!eof && first_bad.load() == INT64_MAX) {
             std::unique_ptr<Blk> b(new Blk());
             b->data.resize(BLOCK + carry.size());
-            memcpy(b->data.data(), carry.data(), carry.size());
+            if (!carry.empty()) memcpy(b->data.data(), carry.data(), carry.size());
             size_t have = carry.size();
             carry.clear();
             while (have < b->data.size()) {
