@@ -23,8 +23,25 @@ WORKER = textwrap.dedent("""
     fake_ms = 10.0 * (r.rank + 1)                      # rank 1 is the slow one
     thr = dist.job_throughput(r, n, m, 2, fake_ms)
     lo = r.min(b); hi = r.max(e)
+    # the exchange of the packed rows, with gloo standing in for the peer copies: every rank "posts" the slices
+    # gcta_b200_exchange_slice gives it, "pulls" the others' and must end up with the whole payload
+    import numpy as np
+    import torch.distributed as tdist
+    m_file, stride = 1003, 7
+    payload = ((np.arange(m_file * stride, dtype=np.int64) * 2654435761) %% 251).astype(np.uint8).reshape(m_file, stride)
+    mine = abi.exchange_slices(m_file, r.world, r.rank)
+    buf = np.zeros_like(payload)
+    for b0, e0 in mine:
+        buf[b0:e0] = payload[b0:e0]
+    pieces = [None] * r.world
+    tdist.all_gather_object(pieces, [(b0, e0, buf[b0:e0].tobytes()) for b0, e0 in mine])
+    for q, lst in enumerate(pieces):
+        if q != r.rank:
+            for b0, e0, raw in lst:
+                buf[b0:e0] = np.frombuffer(raw, dtype=np.uint8).reshape(e0 - b0, stride)
     print(json.dumps(dict(rank=r.rank, world=r.world, band=[b, e], pairs=pairs, total_pairs=total_pairs,
-                          total_tiles=total_tiles, thr=thr, lo=lo, hi=hi)))
+                          total_tiles=total_tiles, thr=thr, lo=lo, hi=hi, exchange_ok=bool((buf == payload).all()),
+                          rows_posted=int(sum(e0 - b0 for b0, e0 in mine)), segments=len(mine))))
     r.close()
 """) % ROOT
 
@@ -52,6 +69,9 @@ def test_two_gloo_ranks_partition_and_reduce(tmp_path):
         assert d["world"] == 2 and d["total_pairs"] == n * (n + 1) // 2 and d["lo"] == 0 and d["hi"] == n
         assert d["total_tiles"] == len(abi.tile_list(n))
         assert abs(d["thr"] - n * (n + 1) / 2 * m * 2 / 20e-3) < 1e-3 * d["thr"]      # max over ranks = 20 ms
+    # the row exchange: both ranks end with the complete payload, having uploaded about half of it each
+    assert all(d["exchange_ok"] and d["segments"] == 32 for d in outs)
+    assert outs[0]["rows_posted"] + outs[1]["rows_posted"] == 1003 and abs(outs[0]["rows_posted"] - outs[1]["rows_posted"]) <= 32
     # bands are balanced by tile count, not by rows
     t0, t1 = (len(abi.tile_list(n, *d["band"])) for d in outs)
     assert abs(t0 - t1) <= 0.15 * (t0 + t1)
