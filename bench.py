@@ -28,7 +28,15 @@ sys.path.insert(0, ROOT)
 
 METRIC = "grm_pair_snp_per_s"
 UNIT = "pair*SNP/s"
-SEED = 1236  # 1234 + config index
+# BASELINE.json configs[0..4]: name -> (n, M, missing rate, seed = 1234 + config index, GPUs it is named on)
+CONFIGS = {
+    "cfg1": (2000, 50000, 0.0, 1234, (1,)),
+    "cfg2": (10000, 500000, 0.02, 1235, (1,)),
+    "cfg3": (50000, 1000000, 0.0, 1236, (1, 2, 4, 8)),
+    "cfg4": (100000, 600000, 0.0, 1237, (8,)),
+    "cfg5": (20000, 5000000, 0.0, 1238, (1,)),
+}
+SEED = 1236
 
 
 def peaks():
@@ -144,7 +152,7 @@ def main_reference(a, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": 1e3 * sum(secs) / len(secs), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"synthetic .bed n={a.n} x M={a.m}, miss={a.miss}, --make-grm (BASELINE configs[2])", "timed_sample": sample},
+        "config": {"workload": f"synthetic .bed n={a.n} x M={a.m}, miss={a.miss}, --make-grm (BASELINE {a.config_name})", "timed_sample": sample},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -202,23 +210,29 @@ def main_ours(a, rank, world, local_rank):
     sust, burst, hbm, which = peaks()
     syrk_tflops = 2.0 * band_pairs * m * a.steps / (syrk_ms * 1e-3) / 1e12 if syrk_ms > 0 else 0.0
     syrk_tflops_min = -max_over_ranks(-syrk_tflops)
-    nchunks = len(plan.chunk_rows())   # K2 launches per step on this rank
-    # K1 (HBM bound) for reference: packed read + 16-bit Z write (+ diag re-read), SURVEY.md 8d
-    ldz = (n + 255) // 256 * 256
-    k1_bytes = m * ((n + 3) // 4 * 2 + 2 * ldz)
+    chain = int(os.environ.get("GCTA_B200_CHAIN_SNPS", "32768")) or (1 << 40)
+    chain = max(128, chain // 128 * 128)
+    k2_launches = sum(-(-((e - b + 63) // 64 * 64) // chain) for b, e in plan.chunk_rows())   # K2 launches per step on this rank
+    # Decode stage (K1s + K1f, HBM bound), SURVEY.md 8d: algorithmic bytes of THIS rank = M x (packed row read once +
+    # 16-bit Z row of the band's ldz columns written once); the second read of the packed rows by K1f is not algorithmic
+    ldz_rank = (max(row_end, 1) + 255) // 256 * 256
+    k1_bytes = m * ((n + 3) // 4 + 2 * ldz_rank)
+    k1_gbps = k1_bytes * a.steps / (dec_ms * 1e-3) / 1e9 if dec_ms > 0 else 0.0
+    k1_gbps_min = -max_over_ranks(-k1_gbps)
 
     # ---------------- end to end through the C ABI with host buffers ("e2e") ----------------
     e2e = None
-    if not a.no_e2e:
-        stride = (n + 3) // 4
+    stride = (n + 3) // 4
+    base = row_begin * (row_begin + 1) // 2
+    cnt = int(band_pairs)
+    if not (a.no_e2e and a.no_parity):
         h_bed = torch.empty(stride * m, dtype=torch.uint8, pin_memory=True)
         plan.download_bed(h_bed.data_ptr())
-        base = row_begin * (row_begin + 1) // 2
-        cnt = int(band_pairs)
         h_A = torch.empty(max(cnt, 1), dtype=torch.float32, pin_memory=True)
         h_N = np.empty(max(cnt, 1), dtype=np.int32)
         A_ptr = h_A.data_ptr() - 4 * base  # the ABI indexes the whole packed triangle; only the band is touched
         N_ptr = h_N.ctypes.data - 4 * base
+    if not a.no_e2e:
         e2e_steps = max(1, min(a.steps, a.e2e_steps))
         ex = None
         if world == 1:
@@ -315,10 +329,84 @@ def main_ours(a, rank, world, local_rank):
         if ex is not None:
             ph = ranks.gather([e2e_phases[k] for k in sorted(e2e_phases)])
             e2e["last_step_ms_per_rank"] = {k: [round(float(r[i]), 1) for r in ph] for i, k in enumerate(sorted(e2e_phases))}
+
+    # ---------------- parity of THIS run's output (SURVEY.md 8c sub-block identity) ----------------
+    # a seeded set of individuals that straddles every band boundary; the oracle (checker only, rank 0, float64 numpy)
+    # builds their GRM block from the host copy of the device-generated .bed with the device's 2p; every rank compares
+    # the rows of its own band.  N must be equal, A within the north-star's 1e-3, the diagonal mean within 1e-5.
+    parity = None
+    if not a.no_parity:
+        from oracle import oracle
+        mu_dev = np.empty(m, dtype=np.float64)
+        if a.no_e2e:
+            plan.run()
+        plan.download(A_ptr, N_ptr, mu_dev.ctypes.data)   # the band as the last step left it on the device (+ 2p)
+        bounds = sorted({abi.partition(n, r, world)[0] for r in range(world)} - {0})
+        pick = {0, n - 1}
+        for b in bounds:
+            pick |= {b - 2, b - 1, b, b + 1}
+        pick = {int(x) for x in pick if 0 <= x < n}
+        rng = np.random.default_rng(SEED)
+        rest = rng.permutation(n)
+        for x in rest:
+            if len(pick) >= min(a.parity_sub, n):
+                break
+            pick.add(int(x))
+        sub = np.array(sorted(pick), dtype=np.int64)
+        ns = len(sub)
         if rank == 0:
-            diag_idx = np.arange(min(1000, row_end - row_begin))
-            di = (diag_idx + row_begin) * (diag_idx + row_begin + 1) // 2 + diag_idx + row_begin - base
-            e2e["diag_mean_check"] = float(h_A.numpy()[di].mean())
+            t_or = time.perf_counter()
+            Aref, Nref, _ = oracle.make_grm_numpy_blocked(h_bed.numpy().reshape(m, stride), n, keep=sub, mu=mu_dev)
+            t_or = time.perf_counter() - t_or
+            ref = np.concatenate([Aref.ravel(), Nref.astype(np.float64).ravel()])
+        else:
+            ref = np.zeros(2 * ns * ns)
+        ref = ranks.broadcast(ref, 0)
+        Aref, Nref = ref[:ns * ns].reshape(ns, ns), ref[ns * ns:].reshape(ns, ns)
+        mine = [t for t in range(ns) if row_begin <= sub[t] < row_end]
+        dA_max, n_bad, dsum, dn = 0.0, 0, 0.0, 0
+        An, Nn = h_A.numpy(), h_N
+        for t in mine:
+            i = int(sub[t])
+            idx = i * (i + 1) // 2 + sub[:t + 1] - base
+            dA_max = max(dA_max, float(np.abs(An[idx].astype(np.float64) - Aref[t, :t + 1]).max()))
+            n_bad += int((Nn[idx] != np.rint(Nref[t, :t + 1]).astype(np.int32)).sum())
+            dsum += float(An[idx[-1]]) - Aref[t, t]
+            dn += 1
+        dA_max = max_over_ranks(dA_max)
+        n_bad = int(sum_over_ranks(n_bad))
+        dmean = sum_over_ranks(dsum) / max(1.0, sum_over_ranks(dn))
+        parity = {"max_abs_dA": dA_max, "diag_mean_delta": abs(dmean), "N_equal": n_bad == 0, "sub": ns,
+                  "pairs_checked": ns * (ns + 1) // 2, "band_boundaries_straddled": bounds,
+                  "ok": bool(dA_max <= 1e-3 and abs(dmean) <= 1e-5 and n_bad == 0),
+                  "oracle": "oracle.make_grm_numpy_blocked (float64) on the sub-block with the device's 2p; rank 0, not timed"}
+        if rank == 0:
+            parity["oracle_seconds"] = round(t_or, 1)
+
+    # ---------------- the one-shot plugin call on pageable buffers, plan creation included ("e2e_cold") ----------------
+    e2e_cold = None
+    if world == 1 and not a.no_cold and not a.no_parity:
+        bed_pg = np.array(h_bed.numpy())            # pageable copies: what a host program that malloc'ed its buffers passes
+        A_pg = np.empty(max(cnt, 1), dtype=np.float32)
+        N_pg = np.empty(max(cnt, 1), dtype=np.int32)
+        args, ka = abi.make_args(bed_pg, n, m, operand=abi.BF16 if a.operand == "bf16" else abi.FP16, device=local_rank)
+        import ctypes as C
+        oc = abi.Out()
+        oc.A_lower, oc.N_lower, oc.mu_out = A_pg.ctypes.data, N_pg.ctypes.data, None
+        err = C.create_string_buffer(abi.ERRCAP)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rc = abi.lib().gcta_b200_make_grm(C.byref(args), C.byref(oc), err, abi.ERRCAP)
+        cold_s = time.perf_counter() - t0
+        if rc:
+            e2e_cold = {"failed": err.value.decode(errors="replace")[:200]}
+        else:
+            same = float(np.abs(A_pg - h_A.numpy()[:len(A_pg)]).max())   # against the band downloaded for the parity check
+            e2e_cold = {"value": pairs_total * m / cold_s, "unit": UNIT, "ms_per_step": 1e3 * cold_s, "steps": 1,
+                        "api": "gcta_b200_make_grm, one call: plan creation (all cudaMalloc), upload from PAGEABLE host memory, compute, "
+                               "download into pageable host memory, plan destruction",
+                        "device_ms": oc.ms_total, "max_abs_diff_vs_plan_output": same}
+        del bed_pg, A_pg, N_pg
 
     line = None
     if rank == 0:
@@ -326,23 +414,33 @@ def main_ours(a, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": dev_ms_max / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": a.operand + " operands, f32 accumulate", "data": "synthetic",
-            "config": {"workload": f"synthetic .bed n={n} x M={m}, MAF U(0.01,0.5), miss={a.miss}, --make-grm (BASELINE configs[2])",
+            "config": {"workload": f"synthetic .bed n={n} x M={m}, MAF U(0.01,0.5), miss={a.miss}, --make-grm (BASELINE {a.config_name})",
                        "partition": f"{world} row band(s) of the lower triangle, packed genotypes replicated per GPU",
                        "l2": "inputs (packed bed + Z chunks) far larger than the 126 MB L2; no flush needed",
                        "timing": "CUDA events on the plan's stream, max over ranks"},
             "tflops": 2 * value / 1e12, "wall_ms_per_step": wall_ms_max / a.steps,
             "phases_ms_per_step_rank0": {"decode+diag": dec_ms / a.steps, "syrk": syrk_ms / a.steps, "paircount": pc_ms / a.steps,
                                          "finalize": fin_ms / a.steps},
-            "roofline": {"kernel": "syrk_tiles_kernel (K2)", "bound": "tensor", "achieved": syrk_tflops_min, "peak": sust, "unit": "TFLOP/s",
-                         "frac": syrk_tflops_min / sust, "frac_of_burst_peak": syrk_tflops_min / burst, "peak_source": which + " (sustained bf16, kernel timed inside a long step)",
-                         "traffic": k2_traffic(n, world), "launches_per_step": nchunks,
-                         "k1_decode_GBps": k1_bytes / (dec_ms / a.steps * 1e-3) / 1e9 if dec_ms > 0 else None, "hbm_peak_GBps": hbm},
+            # frac is quoted against the burst peak: the kernel beats the "sustained" figure (a long cuBLAS loop under the
+            # power cap), so that one is no ceiling; both are given
+            "roofline": {"kernel": "syrk_tiles_kernel (K2)", "bound": "tensor", "achieved": syrk_tflops_min, "peak": burst, "unit": "TFLOP/s",
+                         "frac": syrk_tflops_min / burst, "frac_of_sustained_peak": syrk_tflops_min / sust, "sustained_peak": sust,
+                         "peak_source": which + " (burst bf16; min over ranks of algorithmic flops / K2 event time)",
+                         "traffic": k2_traffic(n, world, chain, m), "launches_per_step": k2_launches},
+            "roofline_decode": {"kernel": "snp_stats_kernel + decode_emit_diag_kernel (K1s + K1f)", "bound": "hbm", "achieved": k1_gbps_min,
+                                "peak": hbm, "unit": "GB/s", "frac": k1_gbps_min / hbm, "peak_source": which + " (copy bandwidth)",
+                                "bytes_per_step_rank0": k1_bytes, "traffic": None,
+                                "note": "min over ranks; per-rank algorithmic bytes M x (ceil(n/4) + 2 ldz_rank) / that rank's decode event time"},
             "clocks": clocks, "gpu_launches": launches_total,
             "per_rank": [{"rows": [int(r[0]), int(r[1])], "ms_total": round(r[2], 2), "ms_syrk": round(r[3], 2), "ms_decode": round(r[4], 2),
                           "sm_mhz": r[5]} for r in per_rank],
         }
         if e2e:
             line["e2e"] = e2e
+        if parity:
+            line["parity"] = parity
+        if e2e_cold:
+            line["e2e_cold"] = e2e_cold
     # CPU baseline: the compiled reference on a bounded sample, rank 0 at N=1 only
     if rank == 0 and world == 1 and not a.no_cpu:
         try:
@@ -358,16 +456,17 @@ def main_ours(a, rank, world, local_rank):
     ranks.close()
 
 
-def k2_traffic(n, world):
+def k2_traffic(n, world, chain, m):
     """dram__bytes_read.sum + dram__bytes_write.sum of one K2 launch from the committed ncu capture (profiles/),
-    only when this run matches the captured shape (whole triangle of n individuals on one GPU); else None."""
+    only when this run launches the captured shape (whole triangle of n individuals on one GPU, same SNPs per launch);
+    else None."""
     p = os.path.join(ROOT, "profiles", "k2_traffic.json")
     if world != 1 or not os.path.exists(p):
         return None
     d = json.load(open(p))
-    if d.get("n") != n:
+    if d.get("n") != n or d.get("snps_per_launch") != min(chain, m):
         return None
-    return d["dram_bytes_read"] + d["dram_bytes_write"]   # bytes per launch of 85,056 SNPs (profiles/k2_traffic.json)
+    return d["dram_bytes_read"] + d["dram_bytes_write"]
 
 
 def main():
@@ -376,9 +475,9 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", "--individuals", dest="n", type=int, default=50000)   # --individuals: unambiguous under torchrun
-    ap.add_argument("--m", "--snps", dest="m", type=int, default=1000000)
-    ap.add_argument("--miss", type=float, default=0.0)
+    ap.add_argument("--n", "--individuals", dest="n", type=int, default=None)   # --individuals: unambiguous under torchrun
+    ap.add_argument("--m", "--snps", dest="m", type=int, default=None)
+    ap.add_argument("--miss", type=float, default=None)
     ap.add_argument("--operand", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--ref-n", type=int, default=600, help="individuals in the CPU reference sample")
     ap.add_argument("--ref-m", type=int, default=20000, help="SNPs in the CPU reference sample")
@@ -386,7 +485,21 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--config", default="cfg3", choices=sorted(CONFIGS), help="BASELINE.json configuration (cfg3 = the one the metric is quoted on)")
+    ap.add_argument("--force", action="store_true", help="run a configuration on a GPU count BASELINE.json does not name it on")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-cold", action="store_true")
+    ap.add_argument("--parity-sub", type=int, default=256, help="individuals in the sub-block parity check")
     a = ap.parse_args()
+    global SEED
+    cn, cm, cmiss, SEED, cgpus = CONFIGS[a.config]
+    a.n = cn if a.n is None else a.n
+    a.m = cm if a.m is None else a.m
+    a.miss = cmiss if a.miss is None else a.miss
+    a.config_name = a.config if (a.n, a.m, a.miss) == (cn, cm, cmiss) else "custom"
+    world_env = int(os.environ.get("WORLD_SIZE", "1"))
+    if a.impl == "ours" and a.config_name != "custom" and world_env not in cgpus and not a.force:
+        raise SystemExit(f"bench.py: {a.config} is named on {cgpus} GPU(s) in BASELINE.json, this run has {world_env}; pass --force to run it anyway")
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -40,6 +40,9 @@ inline int set_err(char* err, size_t cap, int code, const std::string& msg)
         if (!(cond)) return gb::set_err(err, errcap, GCTA_B200_ERR_ARG, std::string("Error: ") + (msg)); \
     } while (0)
 
+// slot of the (device, stream) pair in the SYRK kernels' wave-barrier counter arrays (syrk.cu); -1 = none left
+int wave_slot_of(int dev, void* stream);
+
 constexpr int TILE_M = 256;  // rows of S per tile (two UMMA M=128 halves, one TMEM accumulator each)
 constexpr int TILE_N = 256;  // columns of S per tile (= UMMA N, TMEM columns per accumulator)
 constexpr int UMMA_M = 128;  // rows per tcgen05.mma (= TMEM lanes)

@@ -13,6 +13,7 @@
 // All three are HBM-bound byte/bit kernels: 128-bit loads of packed genotypes, 128-bit
 // coalesced stores of Z.  Algorithmic bytes per SNP: ceil(n/4) read + 2*ldz written (K1).
 #include <algorithm>
+#include <atomic>
 #include <vector>
 
 #include "common.cuh"
@@ -595,16 +596,17 @@ __global__ void __launch_bounds__(256) snp_lut_kernel(const uint8_t* __restrict_
 // address is asked for once per device (with that device current) and remembered.
 static int static_lut_address(float** out, char* err, size_t errcap)
 {
-    static float* cached[64] = {};
+    // atomics: two host threads may make their first call at the same time; both then look the same address up
+    static std::atomic<float*> cached[64] = {};
     int dev = 0;
     GB_CUDA(cudaGetDevice(&dev));
     GB_ARG(dev >= 0 && dev < 64, "diag_accum_static: device ordinal above 63");
-    if (!cached[dev]) {
-        float* p = nullptr;
+    float* p = cached[dev].load(std::memory_order_acquire);
+    if (!p) {
         GB_CUDA(cudaGetSymbolAddress((void**)&p, g_static_zlut));
-        cached[dev] = p;
+        cached[dev].store(p, std::memory_order_release);
     }
-    *out = cached[dev];
+    *out = p;
     return 0;
 }
 

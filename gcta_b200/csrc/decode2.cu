@@ -1,0 +1,365 @@
+// decode2.cu - K1s + K1f: the standardisation stage as two streaming passes over the packed genotypes.
+//
+// K1s snp_stats        : one warp per included SNP row - allele counts of the kept individuals
+//                        (popc over bit planes, shuffle reduction), 2p, and the reference's
+//                        doubly-rounded standardised values as 4 floats per SNP.  Reads the packed
+//                        row once, writes ~50 bytes.  Replaces calcu_mu / mu_func
+//                        (data.cpp:759-803) and the per-SNP constants of std_XMat (data.cpp:1027-1040).
+// K1f decode_emit_diag : CTA = a slab of 2048 individuals x a run of SNP rows.  A thread owns one
+//                        32-bit packed column (16 individuals) and walks down the rows: per row one
+//                        4-byte load, eight nibble look-ups (two genotypes each) in a per-SNP table
+//                        in shared memory that yield the two 16-bit z values and their two float
+//                        squares, one 32-byte store of the Z row segment, and sixteen float adds into
+//                        the thread's own diagonal sums.  Missing genotypes are counted bit-sliced.
+//                        Replaces make_XMat / std_XMat (data.cpp:982-1056) and the diagonal of the
+//                        triple loop (grm.cpp:265-275) in ONE pass: the separate diagonal kernel and
+//                        its re-read of the packed rows are gone.
+//
+// Both are HBM-bound byte kernels.  Algorithmic bytes per SNP: ceil(n/4) (K1s) and
+// ceil(n/4) + 2*ldz (K1f).  This is the path for the common case (every individual kept,
+// autosomes, --grm-alg 0, one 16-bit plane); keep lists, the X chromosome, --grm-alg 1 and the
+// split-FP16 mode stay on the row-per-CTA kernels of decode.cu.
+#include <algorithm>
+#include <cstdlib>
+
+#include "common.cuh"
+
+namespace gb {
+
+constexpr int F_THREADS = 128;            // threads per CTA = packed 32-bit columns per slab
+constexpr int F_SLAB = F_THREADS * 16;    // individuals per slab
+constexpr int F_TB = 48;                  // SNP rows per table block (multiple of 6)
+constexpr int F_FLUSH_BLOCKS = 64;        // table blocks between flushes of the float partial sums (3072 rows)
+
+__device__ __forceinline__ int warp_sum2(int v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1s
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) snp_stats_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n_kept,
+                                                         const uint32_t* __restrict__ keepmask,
+                                                         const int32_t* __restrict__ include, int64_t k0, int64_t kc,
+                                                         const double* __restrict__ mu_in, int divide, double* __restrict__ mu_out,
+                                                         int32_t* __restrict__ cnt_out, int32_t* __restrict__ sum_out,
+                                                         float* __restrict__ zlut, unsigned long long* __restrict__ total_missing)
+{
+    __shared__ int miss_s[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t kk = (int64_t)blockIdx.x * 8 + warp;
+    int missing = 0;
+    if (kk < kc) {
+        const int64_t k = k0 + kk;
+        const uint4* row16 = reinterpret_cast<const uint4*>(bed + (int64_t)(include ? include[k] : (int32_t)k) * pitch);
+        const uint4* km16 = reinterpret_cast<const uint4*>(keepmask);
+        int cnt = 0, sum = 0;
+        const int nvec = (int)(pitch / 16);
+#pragma unroll 4
+        for (int v = lane; v < nvec; v += 32) {
+            const uint4 w = __ldg(row16 + v), km = __ldg(km16 + v);
+            const uint32_t ww[4] = {w.x, w.y, w.z, w.w}, kw[4] = {km.x, km.y, km.z, km.w};
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint32_t lo = ww[q] & 0x55555555u, hi = (ww[q] >> 1) & 0x55555555u;
+                const uint32_t nm = ~(lo & ~hi) & kw[q];   // kept and not missing (even bit positions)
+                cnt += __popc(nm);
+                sum += __popc(nm & ~hi) + __popc(nm & ~lo);
+            }
+        }
+        cnt = warp_sum2(cnt);
+        sum = warp_sum2(sum);
+        if (lane == 0) {
+            // mu = 2p and the doubly-rounded z values (data.cpp:801, 1027-1040), same operation order as decode.cu
+            const double mu = mu_in ? mu_in[k] : (cnt > 0 ? __ddiv_rn((double)sum, (double)cnt) : 0.0);
+            const double var = __dmul_rn(mu, __dsub_rn(1.0, __dmul_rn(0.5, mu)));
+            const double isd = fabs(var) < 1.0e-50 ? 0.0 : __dsqrt_rn(__ddiv_rn(1.0, var));
+            float z[4];
+#pragma unroll
+            for (int code = 0; code < 4; code++) {
+                const int x = code == 0 ? 2 : (code == 2 ? 1 : 0);
+                float v = __double2float_rn(__dsub_rn((double)x, mu));              // X -= mu   (data.cpp:1039)
+                if (divide) v = __double2float_rn(__dmul_rn((double)v, isd));       // X *= sd   (data.cpp:1040)
+                z[code] = code == 1 ? 0.0f : v;                                     // missing contributes nothing
+            }
+            mu_out[k] = mu;
+            cnt_out[k] = cnt;
+            sum_out[k] = sum;
+            reinterpret_cast<float4*>(zlut + k * 8)[0] = make_float4(z[0], z[1], z[2], z[3]);
+            reinterpret_cast<float4*>(zlut + k * 8)[1] = make_float4(z[0], z[1], z[2], z[3]);   // "male" half: same on autosomes
+            missing = (int)(n_kept - cnt);
+        }
+    }
+    if (lane == 0) miss_s[warp] = missing;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) t += (unsigned long long)miss_s[i];
+        if (t) atomicAdd(total_missing, t);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1f
+// ------------------------------------------------------------------------------------------------
+struct FusedParams {
+    const uint8_t* bed;
+    int64_t pitch, n_file;
+    const int32_t* include;
+    int64_t k0, kc, kc_pad;
+    const float* zlut;
+    int bf16;
+    uint16_t* Z;
+    int64_t ldz, n_out;
+    double* diag;
+    int32_t* nii;
+    int64_t diag_f0, diag_f1;   // file individuals whose diagonal is wanted
+    int64_t rows_per_cta;
+};
+
+__device__ __forceinline__ uint32_t f2h16(float z, int bf16)
+{
+    return bf16 ? (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(z)) : (uint32_t)__half_as_ushort(__float2half_rn(z));
+}
+
+__device__ __forceinline__ void st_z256(uint16_t* dst, const uint32_t (&o)[8])
+{
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]),
+                 "r"(o[5]), "r"(o[6]), "r"(o[7]));   // no "memory" clobber: nothing in the kernel reads Z, and the table look-ups of the next row may move above it
+}
+
+// one packed word = 16 genotypes of one SNP: look the eight nibbles up, store, accumulate.
+// `row_addr` is the shared-memory address of the SNP's 256-byte table row (256-byte aligned, so the
+// nibble's byte offset is OR-ed in by the same LOP3 that masks it): z pairs at [8 nib], squares at [128 + 8 nib].
+template <bool DIAG>
+__device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_t* zdst, int nvalid, float (&acc)[16])
+{
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        // entries are 8 bytes apart: offset ((w >> 4j) & 15) * 8
+        const uint32_t a = (j == 0 ? (w << 3) & 0x78u : (w >> (4 * j - 3)) & 0x78u) | row_addr;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(o[j]) : "r"(a));
+        if (DIAG) {
+            float qx, qy;
+            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2+128];" : "=f"(qx), "=f"(qy) : "r"(a));
+            acc[2 * j] += qx;
+            acc[2 * j + 1] += qy;
+        }
+    }
+    if (nvalid >= 16) st_z256(zdst, o);
+    else {   // the one column that straddles n_out, and the zero padding behind it
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (2 * j >= nvalid) o[j] = 0;
+            else if (2 * j + 1 >= nvalid) o[j] &= 0xFFFFu;
+        }
+        reinterpret_cast<uint4*>(zdst)[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        reinterpret_cast<uint4*>(zdst)[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    }
+}
+
+template <bool DIAG>
+__device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64_t r1, int64_t col, bool in_z, bool can_load, int nvalid,
+                                         uint8_t (*tab)[F_TB][256], int64_t (*row_off)[F_TB])
+{
+    const int tid = threadIdx.x;
+    const int64_t i0 = col * 16;
+    float acc[16];
+    uint32_t m16[8];
+#pragma unroll
+    for (int e = 0; e < 16; e++) acc[e] = 0.0f;
+#pragma unroll
+    for (int g = 0; g < 8; g++) m16[g] = 0;
+    const bool tdiag = DIAG && in_z && i0 < p.diag_f1 && i0 + 16 > p.diag_f0;
+    int rows_acc = 0;
+
+    auto build = [&](int buf, int64_t rbase) {
+        const int nr = (int)min((int64_t)F_TB, r1 - rbase);
+        for (int idx = tid; idx < nr * 16; idx += F_THREADS) {
+            const int row = idx >> 4, nib = idx & 15;
+            const int64_t k = p.k0 + rbase + row;
+            const float za = __ldg(p.zlut + k * 8 + (nib & 3)), zb = __ldg(p.zlut + k * 8 + (nib >> 2));
+            *reinterpret_cast<uint32_t*>(&tab[buf][row][8 * nib]) = f2h16(za, p.bf16) | (f2h16(zb, p.bf16) << 16);
+            if (DIAG) *reinterpret_cast<float2*>(&tab[buf][row][128 + 8 * nib]) = make_float2(za * za, zb * zb);   // exact products rounded once to float
+        }
+        for (int row = tid; row < nr; row += F_THREADS) {
+            const int64_t k = p.k0 + rbase + row;
+            row_off[buf][row] = (p.include ? (int64_t)p.include[k] : k) * p.pitch;
+        }
+    };
+    auto flush = [&]() {
+        if (tdiag) {
+#pragma unroll
+            for (int e = 0; e < 16; e++) {
+                const int64_t f = i0 + e;
+                if (f >= p.diag_f0 && f < p.diag_f1 && f < p.n_file) {
+                    // m16[g]: low half = individual g, high half = individual 8+g; m16[4+g]: individuals 4+g, 12+g
+                    const int g = e & 3, hi = (e >> 2) & 1, top = e >> 3;
+                    const int miss = (int)((m16[g + 4 * hi] >> (16 * top)) & 0xFFFFu);
+                    atomicAdd(p.diag + f, (double)acc[e]);
+                    atomicAdd(p.nii + f, rows_acc - miss);
+                }
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 16; e++) acc[e] = 0.0f;
+#pragma unroll
+        for (int g = 0; g < 8; g++) m16[g] = 0;
+        rows_acc = 0;
+    };
+
+    const uint8_t* colp = p.bed + col * 4;
+    int buf = 0, blocks = 0;
+    build(0, r0);
+    __syncthreads();
+    for (int64_t rbase = r0; rbase < r1; rbase += F_TB, buf ^= 1) {
+        if (rbase + F_TB < r1) build(buf ^ 1, rbase + F_TB);   // next block's tables while this one is consumed
+        const int nr = (int)min((int64_t)F_TB, r1 - rbase);
+        if (in_z) {
+            uint16_t* zrow = p.Z + rbase * p.ldz + i0;
+            const uint32_t tab_addr = smem_u32(&tab[buf][0][0]);
+            uint32_t c8[4] = {0, 0, 0, 0};
+            int row = 0;
+            for (; row + 6 <= nr; row += 6) {
+                uint32_t w[6];
+#pragma unroll
+                for (int u = 0; u < 6; u++) w[u] = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + row_off[buf][row + u])) : 0u;
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    uint32_t c2 = 0;
+#pragma unroll
+                    for (int u = 3 * h; u < 3 * h + 3; u++) {
+                        emit_word<DIAG>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz, nvalid, acc);
+                        if (DIAG) c2 += (w[u] & 0x55555555u) & ~(w[u] >> 1);   // missing = code 01b, one count per 2-bit lane
+                    }
+                    if (DIAG) {
+#pragma unroll
+                        for (int g = 0; g < 4; g++) c8[g] += (c2 >> (2 * g)) & 0x03030303u;
+                    }
+                }
+            }
+            for (; row < nr; row++) {
+                const uint32_t w = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + row_off[buf][row])) : 0u;
+                emit_word<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc);
+                if (DIAG) {
+                    const uint32_t c2 = (w & 0x55555555u) & ~(w >> 1);
+#pragma unroll
+                    for (int g = 0; g < 4; g++) c8[g] += (c2 >> (2 * g)) & 0x03030303u;
+                }
+            }
+            if (DIAG) {
+                // byte b of c8[g] = individual 4b + g (at most F_TB per byte) -> 16-bit lanes
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    m16[g] += c8[g] & 0x00FF00FFu;
+                    m16[4 + g] += (c8[g] >> 8) & 0x00FF00FFu;
+                }
+                rows_acc += nr;
+                if (++blocks == F_FLUSH_BLOCKS) { flush(); blocks = 0; }
+            }
+        }
+        __syncthreads();   // the next block's tables are complete; this block's may be overwritten
+    }
+    if (DIAG) flush();
+}
+
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(F_THREADS, MIN_CTAS) decode_emit_diag_kernel(const FusedParams p)
+{
+    // per SNP row 256 bytes: 16 nibble entries of 8 bytes holding the two 16-bit z values of the nibble's two individuals
+    // (4 bytes used; 16 entries x 8 bytes = every other bank, so a warp's look-ups never conflict), then 16 float2 squares
+    __shared__ __align__(256) uint8_t tab[2][F_TB][256];
+    __shared__ int64_t row_off[2][F_TB];                 // byte offset of each SNP row
+    const int64_t col = (int64_t)blockIdx.x * F_THREADS + threadIdx.x;   // packed 32-bit column = individuals [16 col, 16 col + 16)
+    const int64_t i0 = col * 16;
+    const bool in_z = i0 < p.ldz;                        // threads behind ldz only help with the tables and the barriers
+    const bool can_load = in_z && col * 4 < p.pitch;
+    const int nvalid = (int)max((int64_t)0, min((int64_t)16, p.n_out - i0));
+    const int64_t r0 = (int64_t)blockIdx.y * p.rows_per_cta, r1 = min(r0 + p.rows_per_cta, p.kc);
+    // does the slab hold individuals whose diagonal this band needs?  (uniform per CTA)
+    const int64_t s0 = (int64_t)blockIdx.x * F_SLAB;
+    const bool cta_diag = p.diag != nullptr && s0 < p.diag_f1 && s0 + F_SLAB > p.diag_f0;
+    if (r0 < r1) {
+        if (cta_diag) run_rows<true>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+        else run_rows<false>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+    }
+    // padding rows of the last 64-SNP block: zero
+    if (blockIdx.y == gridDim.y - 1 && in_z) {
+        for (int64_t kk = p.kc; kk < p.kc_pad; kk++) {
+            uint4* d = reinterpret_cast<uint4*>(p.Z + kk * p.ldz + i0);
+            d[0] = make_uint4(0, 0, 0, 0);
+            d[1] = make_uint4(0, 0, 0, 0);
+        }
+    }
+}
+
+}  // namespace gb
+
+// K1s through the C ABI (device pointers).  d_mu / d_cnt / d_sum / d_zlut / d_total_missing as for gcta_b200_bed_decode.
+extern "C" int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_keepmask, int64_t n,
+                                   const int32_t* d_include, int64_t k0, int64_t kc, const double* d_mu_in, int32_t alg,
+                                   double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
+                                   unsigned long long* d_total_missing, void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_bed && d_keepmask && d_mu && d_cnt && d_sum && d_zlut && d_total_missing, "snp_stats: null pointer");
+    GB_ARG(pitch > 0 && pitch % 16 == 0 && ((uintptr_t)d_bed & 15) == 0, "snp_stats: bed pitch and pointer must be multiples of 16 bytes");
+    GB_ARG(pitch * 4 >= n_file && n_file > 0 && n > 0 && n <= n_file, "snp_stats: pitch too small for n_file, or bad n");
+    GB_ARG(kc > 0 && k0 >= 0, "snp_stats: empty SNP range");
+    GB_ARG(((uintptr_t)d_zlut & 15) == 0, "snp_stats: zlut must be 16-byte aligned");
+    snp_stats_kernel<<<(unsigned)((kc + 7) / 8), 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, n, d_keepmask, d_include, k0, kc, d_mu_in,
+                                                                                  alg == 0, d_mu, d_cnt, d_sum, d_zlut, d_total_missing);
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// K1f through the C ABI (device pointers).  Every file individual is kept (n == n_file), autosomes, one 16-bit plane.
+extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_include,
+                                          int64_t k0, int64_t kc, const float* d_zlut, int32_t operand, void* d_Z, int64_t ldz,
+                                          double* d_diag, int32_t* d_nii, int64_t diag_f0, int64_t diag_f1,
+                                          void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_bed && d_zlut && d_Z, "decode_emit_diag: null pointer");
+    GB_ARG((d_diag == nullptr) == (d_nii == nullptr), "decode_emit_diag: d_diag and d_nii go together");
+    GB_ARG(pitch > 0 && pitch % 16 == 0 && ((uintptr_t)d_bed & 15) == 0, "decode_emit_diag: bed pitch and pointer must be multiples of 16 bytes");
+    GB_ARG(pitch * 4 >= n_file && n_file > 0, "decode_emit_diag: pitch too small for n_file");
+    GB_ARG(ldz > 0 && ldz % 256 == 0, "decode_emit_diag: ldz must be a positive multiple of 256");
+    GB_ARG(((uintptr_t)d_Z & 31) == 0, "decode_emit_diag: Z must be 32-byte aligned");
+    GB_ARG(kc > 0 && k0 >= 0, "decode_emit_diag: empty SNP range");
+    GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "decode_emit_diag: operand must be FP16 or BF16");
+    FusedParams p;
+    p.bed = d_bed; p.pitch = pitch; p.n_file = n_file; p.include = d_include; p.k0 = k0; p.kc = kc; p.kc_pad = (kc + 63) / 64 * 64;
+    p.zlut = d_zlut; p.bf16 = operand == GCTA_B200_BF16; p.Z = (uint16_t*)d_Z; p.ldz = ldz;
+    p.n_out = n_file < ldz ? n_file : ldz;   // a Z narrower than n keeps only the first ldz individuals (row bands need no more)
+    p.diag = d_diag; p.nii = d_nii;
+    p.diag_f0 = d_diag ? std::max<int64_t>(0, diag_f0) : 0;
+    p.diag_f1 = d_diag ? std::min<int64_t>(n_file, diag_f1) : 0;
+    int dev = 0, sms = 0;
+    GB_CUDA(cudaGetDevice(&dev));
+    GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int64_t slabs = (ldz / 16 + F_THREADS - 1) / F_THREADS;
+    // rows per CTA: about four CTAs per slab and SM (the tail of a launch stays short), at least one table block, and few
+    // enough rows that the 16-bit missing counters cannot overflow between flushes
+    const int64_t rows_env = getenv("GCTA_B200_DECODE_ROWS") ? atoll(getenv("GCTA_B200_DECODE_ROWS")) : 0;
+    int64_t groups = std::max<int64_t>(1, ((int64_t)sms * 16 + slabs - 1) / slabs);
+    int64_t rows = rows_env > 0 ? rows_env : (kc + groups - 1) / groups;
+    rows = std::max<int64_t>(rows, F_TB);
+    rows = (rows + F_TB - 1) / F_TB * F_TB;
+    groups = (kc + rows - 1) / rows;
+    GB_ARG(groups <= 65535, "decode_emit_diag: SNP range too long for one launch");
+    p.rows_per_cta = rows;
+    dim3 grid((unsigned)slabs, (unsigned)groups);
+    // resident CTAs per SM the kernel is compiled for: 4 (104 registers) by default, GCTA_B200_DECODE_OCC=6 selects the
+    // 80-register build (a few spilled bytes, half again as many warps in flight)
+    const int occ = getenv("GCTA_B200_DECODE_OCC") ? atoi(getenv("GCTA_B200_DECODE_OCC")) : 4;
+    if (occ >= 6) decode_emit_diag_kernel<6><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+    else decode_emit_diag_kernel<4><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}

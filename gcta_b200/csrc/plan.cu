@@ -151,7 +151,9 @@ struct gcta_b200_plan {
     std::vector<int32_t> h_include, h_tiles;
     std::vector<int64_t> cstart;   // SNP chunk c = included SNPs [cstart[c], cstart[c+1]); every chunk <= `chunk` SNPs
     int64_t nchunks() const { return (int64_t)cstart.size() - 1; }
-    bool downloaded = false;   // the last run already streamed A (and filled N) into the caller's buffers
+    bool downloaded = false;   // the last run already streamed A (and filled N) into the caller's buffers ...
+    const float* streamed_A = nullptr;   // ... namely these (plan_download into other buffers still copies)
+    const int32_t* streamed_N = nullptr;
     int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
     uint8_t *d_bed = nullptr, *d_bed_own = nullptr;   // d_bed: the buffer the kernels read; d_bed_own: the plan's allocation
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
@@ -165,6 +167,8 @@ struct gcta_b200_plan {
     unsigned long long* d_total_missing = nullptr;
     std::vector<cudaEvent_t> events;
     bool ran = false, overlap = false;
+    bool fused_decode = false;   // K1s + K1f (decode2.cu) instead of K1 + K1d
+    int64_t chain = 32768;       // SNPs accumulated in one TMEM chain before the accumulator is added into S
     int64_t total_missing = 0;
     std::vector<void*> allocs;
 };
@@ -247,6 +251,9 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     p->has_keep = a->keep != nullptr && !(n == a->n_file);
     p->has_include = a->include != nullptr;
     p->has_mu = a->mu != nullptr;
+    // the two streaming passes of decode2.cu cover the common case; GCTA_B200_DECODE=legacy forces the row-per-CTA kernels
+    p->fused_decode = !p->has_keep && !a->xchr && a->alg == 0 && p->operand != GCTA_B200_FP16X2 &&
+                      !(getenv("GCTA_B200_DECODE") && strcmp(getenv("GCTA_B200_DECODE"), "legacy") == 0);
 #define PLAN_TRY(x) do { int rc_ = (x); if (rc_) { gcta_b200_plan_destroy(p); return rc_; } } while (0)
 #define PLAN_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { gcta_b200_plan_destroy(p); \
         return set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed: ") + #x + ": " + cudaGetErrorString(e_)); } } while (0)
@@ -339,6 +346,14 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         kc = std::min<int64_t>(kc, round_up(m, 64));
         kc = std::min<int64_t>(kc, 1 << 23);   // counts of one chunk must stay exact in the FP32 accumulator
         p->chunk = kc;
+        // Length of one accumulation chain in TMEM.  The tensor cores add each MMA's partial sum into the FP32 accumulator
+        // with truncation, so a long chain of same-sign products (the off-diagonal of duplicates or close relatives, which
+        // grows like the diagonal) drifts low by ~2^-25 per MMA of the chain; the add of a finished chain into S is a
+        // round-to-nearest FP32 add.  32,768 SNPs = 2,048 MMAs keeps that bias below 5e-5 relative; the SYRK of a Z chunk
+        // is issued as one launch per chain-length slice of it.  GCTA_B200_CHAIN_SNPS overrides (0 = whole chunk).
+        if (const char* e = getenv("GCTA_B200_CHAIN_SNPS")) p->chain = atoll(e);
+        if (p->chain <= 0) p->chain = 1ll << 40;
+        p->chain = std::max<int64_t>(128, p->chain / 128 * 128);
         // Chunk table.  When the plan picks the chunk length itself and there are many SNPs, the chunks ramp up: 1/64 of
         // the SNPs first, then twice the previous chunk until the Z buffer's length is reached.  A run that receives its
         // packed rows while it computes (plan_run_streamed / plan_run_to_host, per-chunk events of an exchange) can only
@@ -540,6 +555,8 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
     const int ngroups = (int)gstart.size() - 1;
     const int nseg = std::min(8, ngroups);
     std::vector<cudaEvent_t> evs;
+    struct Seg { int64_t base, cnt; };
+    std::vector<Seg> segs;
     int rc = 0;
     int gi = 0;
     for (int s = 0; s < nseg && !rc && gi < ngroups; s++) {
@@ -553,7 +570,12 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
         const int64_t r0 = (b0 + (int64_t)gi * R) * TILE_M, r1 = std::min<int64_t>((b0 + (int64_t)ge * R) * TILE_M, p->row_end);
         gi = ge;
         if (t1 <= t0) continue;
-        rc = gcta_b200_syrk_tiles_ab(Z, Z, p->ldz, kp, p->operand, p->d_tiles + 2 * t0, t1 - t0, p->d_S + t0 * (TILE_M * TILE_N), st, err, errcap);
+        for (int64_t ks = 0; ks < kp && !rc; ks += p->chain) {   // one launch per TMEM chain, as in plan_run_impl
+            const uint16_t* Zs = (const uint16_t*)Z + ks * p->ldz;
+            rc = gcta_b200_syrk_tiles_ab(Zs, Zs, p->ldz, std::min<int64_t>(p->chain, kp - ks), p->operand, p->d_tiles + 2 * t0, t1 - t0,
+                                         p->d_S + t0 * (TILE_M * TILE_N), st, err, errcap);
+            if (ks > 0) ++*launches;
+        }
         if (rc) break;
         const int64_t seg_base = r0 * (r0 + 1) / 2, seg_cnt = r1 * (r1 + 1) / 2 - seg_base;
         rc = gcta_b200_finalize_tiles(p->d_S + t0 * (TILE_M * TILE_N), nullptr, (int32_t)p->m, p->d_tiles + 2 * t0, t1 - t0, p->n, p->d_keep, p->d_diag,
@@ -563,10 +585,8 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
         cudaEvent_t ev;
         cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
         if (e == cudaSuccess) { evs.push_back(ev); e = cudaEventRecord(ev, st); }
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(p->stream_copy, ev, 0);
-        if (e == cudaSuccess)
-            e = cudaMemcpyAsync(out->A_lower + seg_base, p->d_A_lower + (seg_base - band_base), (size_t)seg_cnt * 4, cudaMemcpyDeviceToHost, p->stream_copy);
         if (e != cudaSuccess) rc = set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed in the pipelined download: ") + cudaGetErrorString(e));
+        segs.push_back({seg_base, seg_cnt});
     }
     // every launch of the chunk is queued: only now start the host threads that fill N (== m everywhere), so that
     // nothing competes with the launching thread for cores while the GPU waits for its next kernel
@@ -578,6 +598,16 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
         const int64_t cnt = p->band_count;
         for (int t = 0; t < nt; t++)
             fill.emplace_back([=]() { std::fill(dst + cnt * t / nt, dst + cnt * (t + 1) / nt, mval); });
+    }
+    // The copies are issued only now, after every kernel of the chunk is in the queue: into pinned memory they are
+    // asynchronous anyway; into pageable memory each call blocks this thread until its segment has been computed and
+    // copied (the driver stages it), while the GPU already works on the next segments - so the download overlaps the
+    // tensor work for either kind of caller buffer.
+    for (size_t i = 0; i < segs.size() && i < evs.size() && !rc; i++) {
+        cudaError_t e = cudaStreamWaitEvent(p->stream_copy, evs[i], 0);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(out->A_lower + segs[i].base, p->d_A_lower + (segs[i].base - band_base), (size_t)segs[i].cnt * 4, cudaMemcpyDeviceToHost, p->stream_copy);
+        if (e != cudaSuccess) rc = set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed in the pipelined download: ") + cudaGetErrorString(e));
     }
     cudaError_t e2 = cudaStreamSynchronize(p->stream_copy);
     for (auto& t : fill) t.join();
@@ -640,7 +670,15 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     auto syrk = [&](const void* Za, const void* Zb, int64_t kp, int op, void* outp, bool int_acc, cudaStream_t s) -> int {
         if (p->d_pairs) return gcta_b200_syrk_pairs(Za, Zb, p->ldz, kp, op, p->d_pairs, p->npairs, outp, int_acc, s, err, errcap);
         if (int_acc) return gcta_b200_count_tiles(Za, p->ldz, kp, op, p->d_tiles, p->ntiles, (int32_t*)outp, s, err, errcap);
-        return gcta_b200_syrk_tiles_ab(Za, Zb, p->ldz, kp, op, p->d_tiles, p->ntiles, (float*)outp, s, err, errcap);
+        // one launch per TMEM chain (p->chain SNPs): see plan_create
+        for (int64_t ks = 0; ks < kp; ks += p->chain) {
+            const int64_t kl = std::min<int64_t>(p->chain, kp - ks);
+            int rc = gcta_b200_syrk_tiles_ab((const uint16_t*)Za + ks * p->ldz, (const uint16_t*)Zb + ks * p->ldz, p->ldz, kl, op, p->d_tiles,
+                                             p->ntiles, (float*)outp, s, err, errcap);
+            if (rc) return rc;
+            if (ks > 0) launches++;
+        }
+        return 0;
     };
     GB_CUDA(cudaEventRecord(p->events[0], st));
     GB_CUDA(cudaMemsetAsync(p->d_S, 0, (size_t)p->ntiles * TILE_M * TILE_N * sizeof(float), st));
@@ -658,7 +696,16 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         if (!bed_host && c < (int64_t)p->chunk_ready.size() && p->chunk_ready[c])   // ... or were delivered by the caller
             GB_CUDA(cudaStreamWaitEvent(sd, p->chunk_ready[c], 0));                  // (e.g. an NVLink all-gather per chunk)
         GB_CUDA(cudaEventRecord(EV(c, 0), sd));
-        int rc = gcta_b200_bed_decode_ex(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
+        int rc = 0;
+        if (p->fused_decode) {
+            rc = gcta_b200_snp_stats(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->n, p->d_include, k0, kc, p->d_mu_in, p->alg, p->d_mu,
+                                     p->d_cnt, p->d_sum, p->d_zlut, p->d_total_missing, sd, err, errcap);
+            // Z and the band's diagonal in one pass over the packed rows
+            if (!rc) rc = gcta_b200_decode_emit_diag(p->d_bed, p->pitch, p->n_file, p->d_include, k0, kc, p->d_zlut, p->operand, Z, p->ldz,
+                                                     p->d_diag, p->d_nii, p->diag_f0, p->diag_f1, sd, err, errcap);
+            if (rc) return rc;
+        } else {
+        rc = gcta_b200_bed_decode_ex(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
                                          p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
                                          p->d_dk, p->d_total_missing, sd, err, errcap);
         if (rc) return rc;
@@ -667,6 +714,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
                                                                 p->d_include, k0, kc, p->d_zlut, p->d_diag + p->diag_f0, p->d_nii + p->diag_f0, p->d_dk,
                                                                 p->d_dw ? p->d_dw + p->diag_f0 : nullptr, sd, err, errcap) : 0;
         if (rc) return rc;
+        }
         GB_CUDA(cudaEventRecord(EV(c, 1), sd));
         GB_CUDA(cudaStreamWaitEvent(st, EV(c, 1), 0));
         GB_CUDA(cudaEventRecord(EV(c, 2), st));
@@ -771,7 +819,11 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         }
     }
     GB_CUDA(cudaEventRecord(p->events[e_pc], st));
-    if (pipelined) p->downloaded = true;   // A is on the host already, N filled
+    if (pipelined) {   // A is on the host already, N filled
+        p->downloaded = true;
+        p->streamed_A = out->A_lower;
+        p->streamed_N = out->N_lower;
+    }
     else {
         int rc = gcta_b200_finalize_tiles_ex(p->d_S, tm > 0 ? p->d_Ntiles : nullptr, (int32_t)p->m, (p->alg == 1 && tm > 0) ? p->d_Dtiles : nullptr,
                                              d_const, p->alg == 1 ? p->d_dw : nullptr, p->d_tiles, p->ntiles, p->n, p->d_keep,
@@ -838,7 +890,8 @@ extern "C" int gcta_b200_plan_download(gcta_b200_plan* p, gcta_b200_out* out, ch
     GB_ARG(p->ran, "plan_download: plan_run has not completed");
     GB_CUDA(cudaSetDevice(p->device));
     const int64_t base = p->row_begin * (p->row_begin + 1) / 2;
-    const bool have = p->downloaded;   // plan_run_to_host already delivered A and N behind the last SYRK
+    // plan_run_to_host already delivered A (and N) behind the last SYRK - into these very buffers?
+    const bool have = p->downloaded && p->streamed_A == out->A_lower && (!out->N_lower || p->streamed_N == out->N_lower);
     if (!have) GB_CUDA(cudaMemcpyAsync(out->A_lower + base, p->d_A_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
     if (out->N_lower && p->total_missing > 0)
         GB_CUDA(cudaMemcpyAsync(out->N_lower + base, p->d_N_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));

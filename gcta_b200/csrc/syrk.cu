@@ -20,6 +20,8 @@
 
 #include <atomic>
 #include <cstdlib>
+#include <map>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -77,7 +79,7 @@ template <bool INT_ACC, int EB = 2>
 __global__ void __launch_bounds__(SYRK_THREADS, 1)
 syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                   const int2* __restrict__ tiles, int ntiles, int nkb, float* __restrict__ S, uint32_t idesc,
-                  unsigned int* wave_counter)
+                  unsigned int* wave_counter, int epi_red)
 {
     using G = Geo<EB>;
     extern __shared__ uint8_t smem_raw[];
@@ -209,6 +211,13 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                         o.z += __float2int_rn(__uint_as_float(v[4 * g + 2]));
                         o.w += __float2int_rn(__uint_as_float(v[4 * g + 3]));
                         *pi = o;
+                    } else if (epi_red) {
+                        // fire-and-forget vector reduction in L2: every element of S belongs to exactly one CTA of a launch
+                        // and launches are stream-ordered, so the sum is the same round-to-nearest add as the read-modify-write
+                        // below, without the epilogue waiting for S to arrive from HBM
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v[4 * g + 0]), "r"(v[4 * g + 1]),
+                                     "r"(v[4 * g + 2]), "r"(v[4 * g + 3])
+                                     : "memory");
                     } else {
                         float4 o = *p;
                         o.x += __uint_as_float(v[4 * g + 0]);
@@ -233,10 +242,25 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     }
 }
 
-// arrival counters of the wave barrier; launches take slots round-robin so that launches in flight on different
-// streams of one device never share a counter
+// arrival counters of the wave barrier: one slot per (device, stream).  Launches on one stream run in order, and each
+// resets its slot by a memset on that stream, so a slot is never shared by two launches in flight; a process that uses
+// more than WAVE_SLOTS streams per device runs the extra ones without the barrier.
 constexpr int WAVE_SLOTS = 64;
 static __device__ unsigned int g_wave_counter[WAVE_SLOTS];
+
+int wave_slot_of(int dev, void* stream)
+{
+    static std::mutex mu;
+    static std::map<std::pair<int, void*>, int> slots;
+    static int used[64] = {};
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = slots.find({dev, stream});
+    if (it != slots.end()) return it->second;
+    if (dev < 0 || dev >= 64 || used[dev] >= WAVE_SLOTS) return -1;
+    const int slot = used[dev]++;
+    slots[{dev, stream}] = slot;
+    return slot;
+}
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -310,31 +334,40 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
     const int2* tl = reinterpret_cast<const int2*>(d_tiles);
     int nt = (int)ntiles, nkb = (int)(kc_pad / kblock);
     uint32_t id = idesc;
-    typedef void (*KernelFn)(const CUtensorMap, const CUtensorMap, const int2*, int, int, float*, uint32_t, unsigned int*);
+    typedef void (*KernelFn)(const CUtensorMap, const CUtensorMap, const int2*, int, int, float*, uint32_t, unsigned int*, int);
     const KernelFn kfn = eb == 1 ? (KernelFn)syrk_tiles_kernel<true, 1> : (int_acc ? (KernelFn)syrk_tiles_kernel<true> : (KernelFn)syrk_tiles_kernel<false>);
     unsigned int* counter = nullptr;
     // Wave barrier on by default (cfg3: +10 % whole-job, HBM reads of K2 -40 %; profiles/README.md); GCTA_B200_WAVESYNC=0 disables
     static const bool wave_sync = !(getenv("GCTA_B200_WAVESYNC") && atoi(getenv("GCTA_B200_WAVESYNC")) == 0);
     if (wave_sync && ntiles > grid) {
-        static unsigned int* cached[64] = {};
-        static std::atomic<unsigned> next_slot{0};
-        if (dev < 64 && !cached[dev]) GB_CUDA(cudaGetSymbolAddress((void**)&cached[dev], g_wave_counter));
-        counter = dev < 64 ? cached[dev] + (next_slot++ % WAVE_SLOTS) : nullptr;
+        static std::atomic<unsigned int*> cached[64] = {};
+        const int slot = wave_slot_of(dev, stream);
+        if (slot >= 0) {
+            unsigned int* base = cached[dev].load();
+            if (!base) {
+                GB_CUDA(cudaGetSymbolAddress((void**)&base, g_wave_counter));
+                cached[dev].store(base);
+            }
+            counter = base + slot;
+        }
     }
+    // GCTA_B200_EPI_RED=0: epilogue as read-modify-write instead of red.global.add.v4.f32
+    static const int epi_red_env = !(getenv("GCTA_B200_EPI_RED") && atoi(getenv("GCTA_B200_EPI_RED")) == 0);
+    int epi_red = epi_red_env && !int_acc;
     if (counter) {
         // the barrier needs all CTAs resident at once: cooperative launch guarantees it (or fails loudly)
         GB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), (cudaStream_t)stream));
-        void* args[] = {&tmap, &tmapB, &tl, &nt, &nkb, &d_S, &id, &counter};
+        void* args[] = {&tmap, &tmapB, &tl, &nt, &nkb, &d_S, &id, &counter, &epi_red};
         cudaError_t ce = cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid), dim3(SYRK_THREADS), args, SYRK_SMEM, (cudaStream_t)stream);
         if (ce == cudaErrorCooperativeLaunchTooLarge || ce == cudaErrorNotSupported || ce == cudaErrorLaunchOutOfResources) {
             // e.g. part of the GPU is held by another context: run the same kernel without the barrier
             cudaGetLastError();
             counter = nullptr;
-            kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
+            kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter, epi_red);
         } else
             GB_CUDA(ce);
     } else
-        kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter);
+        kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter, epi_red);
     GB_CUDA(cudaGetLastError());
     return 0;
 }

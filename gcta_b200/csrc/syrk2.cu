@@ -353,10 +353,16 @@ extern "C" int gcta_b200_syrk_pairs(const void* d_Za, const void* d_Zb, int64_t 
     attrs[nattrs].val.clusterDim.x = 2; attrs[nattrs].val.clusterDim.y = 1; attrs[nattrs].val.clusterDim.z = 1;
     nattrs++;
     if (wave_sync && npairs > ncl) {
-        static unsigned int* cached[64] = {};
-        static std::atomic<unsigned> next_slot{0};
-        if (dev < 64 && !cached[dev]) GB_CUDA(cudaGetSymbolAddress((void**)&cached[dev], g_wave_counter2));
-        counter = dev < 64 ? cached[dev] + (next_slot++ % WAVE_SLOTS2) : nullptr;
+        static std::atomic<unsigned int*> cached[64] = {};
+        const int slot = wave_slot_of(dev, stream);   // one counter per (device, stream), like syrk.cu
+        if (slot >= 0) {
+            unsigned int* base = cached[dev].load();
+            if (!base) {
+                GB_CUDA(cudaGetSymbolAddress((void**)&base, g_wave_counter2));
+                cached[dev].store(base);
+            }
+            counter = base + slot;
+        }
         if (counter) {
             GB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), (cudaStream_t)stream));
             attrs[nattrs].id = cudaLaunchAttributeCooperative;   // the barrier needs every CTA resident

@@ -71,6 +71,17 @@ class Ranks:
         self._dist.all_gather(out, t)
         return [o.cpu().tolist() for o in out]
 
+    def broadcast(self, arr, src: int = 0):
+        """numpy float64 array of the same shape on every rank -> rank `src`'s values"""
+        if self._dist is None:
+            return arr
+        import numpy as np
+        import torch
+        dev = self.device if self.device is not None else "cpu"
+        t = torch.from_numpy(np.ascontiguousarray(arr, dtype=np.float64)).to(dev)
+        self._dist.broadcast(t, src=src)
+        return t.cpu().numpy()
+
     def close(self):
         if self._dist is not None:
             self._dist.destroy_process_group()

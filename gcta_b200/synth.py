@@ -105,3 +105,70 @@ def write_plink(prefix: str, payload: np.ndarray, n: int, chrom=None, sex=None, 
         for k in range(m):
             c = 1 + (k % 22) if chrom is None else int(chrom[k])
             f.write(f"{c}\trs{k}\t0\t{k + 1}\tA\tG\n")
+
+
+def _unpack_copies(rows: np.ndarray, n: int) -> np.ndarray:
+    """packed rows -> int8 [m, n] copies of allele 1 (0/1/2), -1 = missing"""
+    codes = np.stack([(rows >> s) & 3 for s in (0, 2, 4, 6)], axis=-1).reshape(rows.shape[0], -1)[:, :n]
+    return np.array([2, -1, 1, 0], dtype=np.int8)[codes]
+
+
+def _pack_copies(x: np.ndarray) -> np.ndarray:
+    """int8 [m, n] copies (-1 = missing) -> packed rows uint8 [m, ceil(n/4)] (pad bits 0)"""
+    m, n = x.shape
+    stride = (n + 3) // 4
+    code = np.zeros((m, stride * 4), dtype=np.uint8)
+    code[:, :n] = np.array([3, 2, 0, 1], dtype=np.uint8)[x.astype(np.int64)]   # 0 -> 11, 1 -> 10b, 2 -> 00, -1 -> 01b
+    code = code.reshape(m, stride, 4)
+    return (code[:, :, 0] | (code[:, :, 1] << 2) | (code[:, :, 2] << 4) | (code[:, :, 3] << 6)).astype(np.uint8)
+
+
+def make_related_payload(seed: int, n_founders: int, m: int, n_dup: int = 0, n_po: int = 0, n_sib: int = 0,
+                         miss_rate: float = 0.0, block: int = 4096):
+    """Founders as in make_bed_payload plus relatives appended behind them (a GRM's large off-diagonals):
+
+      n_dup  exact duplicates of founders 0 .. n_dup-1                       (A_ij ~ 1)
+      n_po   children of founder pairs (2i, 2i+1), Mendelian sampling        (parent-offspring, A_ij ~ 0.5)
+      n_sib  sib pairs: two children each of founder pairs (2i, 2i+1) taken from the top of the founder list
+             (full sibs, A_ij ~ 0.5)
+
+    Duplicates copy the founder's missing calls; the children's are drawn independently (seeded).  Returns (payload uint8 [m, ceil(n/4)], n,
+    pairs) with pairs = list of (i, j, kind), i > j, the related pairs in individual indices."""
+    n = n_founders + n_dup + n_po + 2 * n_sib
+    assert n_dup <= n_founders and 2 * n_po <= n_founders and 2 * n_sib <= n_founders
+    stride = (n + 3) // 4
+    out = np.empty((m, stride), dtype=np.uint8)
+    rng = np.random.default_rng(seed ^ 0x5EED)
+    for k0 in range(0, m, block):
+        mm = min(block, m - k0)
+        thr = snp_thresholds(seed, mm, miss_rate=miss_rate, k0=k0)
+        f = _unpack_copies(bed_rows(seed, n_founders, k0, mm, thr), n_founders)   # founders, -1 = missing
+        g = np.where(f < 0, 0, f)   # a missing parental genotype transmits like a 0 (only matters when miss_rate > 0)
+
+        def child(a, b):
+            ta = (rng.random((mm, len(a))) * 2 < g[:, a]).astype(np.int8)   # allele 1 transmitted w.p. copies / 2
+            tb = (rng.random((mm, len(b))) * 2 < g[:, b]).astype(np.int8)
+            c = ta + tb
+            if miss_rate > 0:
+                c[rng.random(c.shape) < miss_rate] = -1
+            return c
+
+        cols = [f]
+        if n_dup:
+            cols.append(f[:, :n_dup])
+        if n_po:
+            cols.append(child(np.arange(0, 2 * n_po, 2), np.arange(1, 2 * n_po, 2)))
+        if n_sib:
+            pa = n_founders - 2 * n_sib + np.arange(0, 2 * n_sib, 2)
+            cols.append(child(pa, pa + 1))
+            cols.append(child(pa, pa + 1))
+        out[k0:k0 + mm] = _pack_copies(np.concatenate(cols, axis=1))
+    pairs = []
+    base = n_founders
+    pairs += [(base + i, i, "dup") for i in range(n_dup)]
+    base += n_dup
+    for i in range(n_po):
+        pairs += [(base + i, 2 * i, "po"), (base + i, 2 * i + 1, "po")]
+    base += n_po
+    pairs += [(base + n_sib + i, base + i, "sib") for i in range(n_sib)]
+    return out, n, pairs

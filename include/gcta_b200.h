@@ -66,7 +66,9 @@ typedef struct {
     int64_t n;              /* number kept (n_file when keep == NULL) */
     const int32_t* include; /* _include: ascending file indices of included SNPs, NULL = all */
     int64_t m;              /* number included (m_file when include == NULL) */
-    const double* mu;       /* per included SNP 2p, as --update-freq leaves _mu (data.cpp:915-916);
+    const double* mu;       /* per included SNP 2p OF ALLELE 1 (.bim column 5), i.e. the mean dosage the packed codes count.
+                               The reference's _mu (data.cpp:794, 915-916) is 2p of its reference allele: a caller passes
+                               _mu[k] where _allele1[k] == _ref_A[k] and 2 - _mu[k] where --update-ref-allele flipped it.
                                NULL = compute like calcu_mu (data.cpp:759-803) */
     const int32_t* sex;     /* per FILE individual, 1 = male 2 = female (_sex); only read when xchr */
     int32_t xchr;           /* grm_xchr_flag: sex-weighted mu, male rows * sqrt(0.5) (data.cpp:1045-1055) */
@@ -213,6 +215,25 @@ int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
                          void* d_Z, int64_t ldz,
                          double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
                          unsigned long long* d_total_missing, void* stream, char* err, size_t errcap);
+
+/* K1s + K1f - the same stage as two streaming passes, used by the plan whenever every file individual is kept, the
+ * SNPs are autosomal, alg == 0 and the operand is one 16-bit plane (the other cases stay on gcta_b200_bed_decode +
+ * gcta_b200_diag_accum).
+ *   gcta_b200_snp_stats        per included SNP in [k0, k0+kc): allele counts of the kept individuals, 2p, and the
+ *                              doubly-rounded standardised values (calcu_mu / mu_func data.cpp:759-803; the per-SNP
+ *                              constants of std_XMat data.cpp:1027-1040).  Outputs as for gcta_b200_bed_decode.
+ *   gcta_b200_decode_emit_diag reads each packed row once more and writes the 16-bit Z chunk (make_XMat / std_XMat,
+ *                              data.cpp:982-1056) AND, in the same pass, adds sum_k z_fk^2 (float64) and the non-missing
+ *                              counts of file individuals [diag_f0, diag_f1) into d_diag / d_nii (grm.cpp:265-275);
+ *                              d_diag == d_nii == NULL skips the diagonal.  d_Z 32-byte aligned, layout as above. */
+int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_keepmask, int64_t n,
+                        const int32_t* d_include, int64_t k0, int64_t kc, const double* d_mu_in, int32_t alg,
+                        double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
+                        unsigned long long* d_total_missing, void* stream, char* err, size_t errcap);
+int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_include,
+                               int64_t k0, int64_t kc, const float* d_zlut, int32_t operand, void* d_Z, int64_t ldz,
+                               double* d_diag, int32_t* d_nii, int64_t diag_f0, int64_t diag_f1,
+                               void* stream, char* err, size_t errcap);
 
 /* K1d - exact per-individual diagonal: diag[f] += sum_k z_fk^2 in float64 and nii[f] += number
  * of non-missing SNPs, over included SNPs [k0, k0+kc), per FILE individual f (grm.cpp:265-275). */

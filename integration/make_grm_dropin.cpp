@@ -30,9 +30,15 @@ void gcta::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
     }
     std::vector<int32_t> include(_include.begin(), _include.end()), sex((size_t)n, 0);
     for (int64_t i = 0; i < n; i++) sex[(size_t)i] = _sex[_keep[i]];
-    std::vector<double> mu;   // --update-freq / an earlier --maf left 2p in _mu, indexed by SNP (data.cpp:915-916, 779)
+    // --update-freq / an earlier --maf left 2p of the REFERENCE allele in _mu, indexed by SNP (data.cpp:915-916, 779, 794);
+    // the library centres the dosage of allele 1 (.bim column 5), so a SNP whose reference allele was flipped by
+    // --update-ref-allele hands over 2 - 2p
+    std::vector<double> mu;
     if (!_mu.empty())
-        for (size_t j = 0; j < _include.size(); j++) mu.push_back(_mu[_include[j]]);
+        for (size_t j = 0; j < _include.size(); j++) {
+            const int id = _include[j];
+            mu.push_back(_allele1[id] == _ref_A[id] ? _mu[id] : 2.0 - _mu[id]);
+        }
 
     cout << "Recoding genotypes (individual major mode) ..." << endl;               // make_XMat's and std_XMat's lines,
     if (_mu.empty()) cout << "Calculating allele frequencies ..." << endl;         // so that logs stay comparable

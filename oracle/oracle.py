@@ -97,9 +97,14 @@ def z_lut(mu: float, divide: bool = True) -> np.ndarray:
 def decode_x(bed: np.ndarray, n_file: int, keep=None, include=None) -> np.ndarray:
     """int8 [m, n]: copies of allele 1 (0/1/2), -1 = missing.  data.cpp:176-181, 1001-1006."""
     rows = bed if include is None else bed[np.asarray(include)]
-    codes = np.stack([(rows >> s) & 3 for s in (0, 2, 4, 6)], axis=-1).reshape(rows.shape[0], -1)[:, :n_file]
-    if keep is not None:
-        codes = codes[:, np.asarray(keep)]
+    if keep is not None and len(keep) * 4 < n_file:
+        # few individuals of many: fetch only their bytes (sub-block checks at the BASELINE shapes)
+        kp = np.asarray(keep, dtype=np.int64)
+        codes = (rows[:, kp >> 2] >> ((kp & 3) * 2).astype(np.uint8)[None, :]) & 3
+    else:
+        codes = np.stack([(rows >> s) & 3 for s in (0, 2, 4, 6)], axis=-1).reshape(rows.shape[0], -1)[:, :n_file]
+        if keep is not None:
+            codes = codes[:, np.asarray(keep)]
     lut = np.array([2, -1, 1, 0], dtype=np.int8)  # code 00->2, 01b->missing, 10b->1, 11->0
     return lut[codes]
 
@@ -152,6 +157,32 @@ def make_grm_numpy(bed: np.ndarray, n_file: int, keep=None, include=None, mu=Non
     dn = np.diag(N) == 0
     A[np.diag_indices_from(A)] = np.where(dn, 1.0, np.diag(A))
     return A, N, mu
+
+
+def make_grm_numpy_blocked(bed: np.ndarray, n_file: int, keep=None, mu=None, block: int = 8192):
+    """make_grm_numpy (alg 0, autosomes, all SNPs) accumulated over SNP blocks, for sub-blocks of individuals at SNP
+    counts whose standardised matrix would not fit in memory at once.  With `keep` and the FULL-sample `mu` this is the
+    sub-block identity of SURVEY.md 8c.  grm.cpp:249-298 up to summation order."""
+    n = n_file if keep is None else len(keep)
+    m = bed.shape[0]
+    S = np.zeros((n, n))
+    Nf = np.zeros((n, n))
+    mu_all = np.empty(m)
+    for k0 in range(0, m, block):
+        k1 = min(m, k0 + block)
+        x = decode_x(bed[k0:k1], n_file, keep)
+        z, ok, mu_b = standardise(x, None if mu is None else np.asarray(mu)[k0:k1])
+        mu_all[k0:k1] = mu_b
+        z64 = z.astype(np.float64)
+        S += z64.T @ z64
+        okf = ok.astype(np.float32)
+        Nf += okf.T @ okf          # 0/1 products, block sums below 2^24: exact in float32
+    N = np.rint(Nf).astype(np.int32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        A = np.where(N > 0, S / np.where(N > 0, N, 1), 0.0)
+    dn = np.diag(N) == 0
+    A[np.diag_indices_from(A)] = np.where(dn, 1.0, np.diag(A))
+    return A, N, mu_all
 
 
 def pack_lower(Mx: np.ndarray) -> np.ndarray:

@@ -139,5 +139,40 @@ def main():
     print("golden fixtures written under", OUT)
 
 
+def round2():
+    """Fixtures added in round 2 (the earlier ones are left untouched):
+    g9_refallele - --update-ref-allele flips the reference allele of every other SNP, then --maf / --update-freq leave
+                   2p of the REFERENCE allele in _mu (data.cpp:794, 915-916): what a caller must convert before it
+                   hands 2p of allele 1 to the library;
+    g10_related  - duplicates, parent-offspring and sib pairs next to unrelated founders (large off-diagonals)."""
+    d = fresh("g9_refallele")
+    n, m = 60, 240
+    synth.write_plink(d + "/t", synth.make_bed_payload(9, n, m, miss_rate=0.02), n)
+    with open(d + "/refA.txt", "w") as f:
+        for k in range(m):
+            f.write(f"rs{k} {'G' if k % 2 else 'A'}\n")
+    run("g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--maf", "0.05", "--make-grm", "--out", "o_maf"])
+    run("g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--freq", "--out", "full"])
+    run("g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--update-freq", "full.freq", "--make-grm-bin", "--out", "ob_uf"])
+    run("g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--update-freq", "full.freq", "--make-grm", "--out", "o_uf"])
+
+    d = fresh("g10_related")
+    bed, n, pairs = synth.make_related_payload(10, 40, 600, n_dup=4, n_po=4, n_sib=4, miss_rate=0.01)
+    synth.write_plink(d + "/t", bed, n)
+    with open(d + "/pairs.txt", "w") as f:
+        for i, j, kind in pairs:
+            f.write(f"{i} {j} {kind}\n")
+    run("g10_related", ["--bfile", "t", "--make-grm", "--out", "o"])
+    run("g10_related", ["--bfile", "t", "--make-grm-bin", "--out", "ob"])
+    run("g10_related", ["--bfile", "t", "--grm-cutoff", "0.3", "--make-grm", "--out", "o_cut"])   # --grm-cutoff only acts on --grm input: ignored here
+    for dd in ("g9_refallele", "g10_related"):
+        for fn in os.listdir(os.path.join(OUT, dd)):
+            if fn.endswith(".log"):
+                os.remove(os.path.join(OUT, dd, fn))
+
+
 if __name__ == "__main__":
-    main()
+    if "--round2" in sys.argv:
+        round2()
+    else:
+        main()

@@ -57,6 +57,10 @@ CASES = [
     ("g5_subset", ["--bfile", "t", "--keep", "keep.txt", "--extract", "extract.txt", "--make-grm"], "o", False),
     ("g5_subset", ["--bfile", "t", "--keep", "keep.txt", "--update-freq", "full.freq", "--make-grm-bin"], "ob_uf", True),   # 2p handed over
     ("g5_subset", ["--bfile", "t", "--maf", "0.1", "--make-grm"], "o_maf", False),   # the reference's own calcu_mu + filter first
+    # reference allele flipped for every other SNP: _mu then holds 2p of the flipped allele and must be turned back
+    ("g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--maf", "0.05", "--make-grm"], "o_maf", False),
+    ("g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--update-freq", "full.freq", "--make-grm-bin"], "ob_uf", True),
+    ("g10_related", ["--bfile", "t", "--make-grm"], "o", False),   # duplicates, parent-offspring, sibs
 ]
 
 

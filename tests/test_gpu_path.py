@@ -26,6 +26,7 @@ def _names(path):
     ("g4_xchr", "o", "ob", {"xchr": 1}),
     ("g5_subset", "o", "ob", {"subset": True}),
     ("g7_nomiss", "o", "ob", {}),
+    ("g10_related", "o", "ob", {}),   # duplicates, parent-offspring and sib pairs: off-diagonals of 0.4 .. 0.9
 ])
 @pytest.mark.parametrize("operand", [abi.FP16, abi.BF16])
 def test_golden(case, txt, binf, kw, operand):

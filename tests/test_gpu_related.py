@@ -1,0 +1,94 @@
+"""Parity where the numbers are quoted and where the GRM is used (GPU).
+
+* related individuals: duplicates, parent-offspring and sib pairs have off-diagonals of 0.5 .. 1 whose numerators grow
+  like the diagonal's; the reference accumulates them in float64 (grm.cpp:288-289), the tensor cores in FP32 chains.
+  This is the population --grm-cutoff acts on (grm.cpp:450-493).
+* BASELINE config 2's shape (n = 10,000 x M = 500,000, 2 % missing): the only configuration that runs the counting
+  pass (grm.cpp:270, 291) at length.
+
+The oracle for these sizes is the sub-block identity of SURVEY.md 8c: the GRM of a subset of individuals computed with
+the full sample's 2p equals that block of the full GRM.
+"""
+import numpy as np
+import pytest
+
+from gcta_b200 import abi, synth
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _lower_index(i, j):
+    i, j = np.maximum(i, j).astype(np.int64), np.minimum(i, j).astype(np.int64)
+    return i * (i + 1) // 2 + j
+
+
+def test_related_individuals_long_chains(monkeypatch):
+    n_f, m = 2000, 400_000
+    bed, n, pairs = synth.make_related_payload(77, n_f, m, n_dup=50, n_po=50, n_sib=50)
+    rel = sorted({i for i, _, _ in pairs} | {j for _, j, _ in pairs})
+    rng = np.random.default_rng(3)
+    others = rng.choice(np.setdiff1d(np.arange(n), rel), 60, replace=False)
+    sub = np.sort(np.concatenate([np.array(rel), others])).astype(np.int64)
+    pos = {int(f): t for t, f in enumerate(sub)}
+    pi = np.array([pos[i] for i, _, _ in pairs])
+    pj = np.array([pos[j] for _, j, _ in pairs])
+    kinds = np.array([k for _, _, k in pairs])
+    Aref = None
+    report = {}
+    # "0": one TMEM chain per Z chunk - here all 400,000 SNPs, 25,000 chained MMAs; default: 32,768-SNP chains
+    for chain in ("0", None):
+        if chain is None:
+            monkeypatch.delenv("GCTA_B200_CHAIN_SNPS", raising=False)
+        else:
+            monkeypatch.setenv("GCTA_B200_CHAIN_SNPS", chain)
+        A, N, mu, out = abi.make_grm(bed, n, m)
+        assert out.total_missing == 0 and (N == m).all()
+        if Aref is None:
+            Aref, Nref, _ = oracle.make_grm_numpy_blocked(bed, n, keep=sub, mu=mu)
+        ii, jj = np.tril_indices(len(sub))
+        got = A[_lower_index(sub[ii], sub[jj])].astype(np.float64)
+        d_all = np.abs(got - Aref[ii, jj]).max()
+        d_rel = np.abs(A[_lower_index(sub[pi], sub[pj])].astype(np.float64) - Aref[pi, pj])
+        dd = abs(A[_lower_index(sub, sub)].astype(np.float64).mean() - np.diag(Aref).mean())
+        report[chain or "default"] = (d_all, d_rel.max(), dd)
+        by_kind = {k: float(d_rel[kinds == k].max()) for k in ("dup", "po", "sib")}
+        print(f"related pairs, chain={chain or 'default (32768)'}: max|dA| over the {len(sub)}-individual block {d_all:.3e}, "
+              f"over the {len(pairs)} related pairs {d_rel.max():.3e} {by_kind}, diag-mean delta {dd:.3e}; "
+              f"A(dup) ~ {Aref[pi, pj][kinds == 'dup'].mean():.3f}, A(po) ~ {Aref[pi, pj][kinds == 'po'].mean():.3f}")
+        assert d_all <= 1e-3 and dd <= 1e-5
+    # the default chain length keeps the related pairs well inside the bar
+    assert report["default"][1] <= 1e-4, report
+
+
+def test_config2_shape_counts_exact():
+    """n = 10,000 x M = 500,000, 2 % missing, generated on the device; 500-individual sub-block against the oracle:
+    N bit-exact through the E4M3 counting pass, A within 1e-3, diagonal mean within 1e-5."""
+    n, m, miss = 10_000, 500_000, 0.02
+    seed = 1235
+    thr = synth.snp_thresholds(seed, m, miss_rate=miss)
+    stride = (n + 3) // 4
+    bed = np.empty((m, stride), dtype=np.uint8)
+    A = np.zeros(n * (n + 1) // 2, dtype=np.float32)
+    N = np.zeros(n * (n + 1) // 2, dtype=np.int32)
+    mu = np.zeros(m)
+    with abi.Plan(n, m) as p:
+        p.synth(seed, thr)
+        p.download_bed(bed)
+        o = p.run()
+        p.download(A, N, mu)
+        assert o.total_missing > 0
+        print(f"config 2 shape: step {o.ms_total:.1f} ms (decode {o.ms_decode:.1f}, syrk {o.ms_syrk:.1f}, counts {o.ms_paircount:.1f})")
+    # the device generator equals the host one (first rows)
+    assert np.array_equal(bed[:64], synth.bed_rows(seed, n, 0, 64, thr[:64]))
+    sub = np.sort(np.random.default_rng(5).choice(n, 500, replace=False)).astype(np.int64)
+    Aref, Nref, _ = oracle.make_grm_numpy_blocked(bed, n, keep=sub, mu=mu)
+    ii, jj = np.tril_indices(len(sub))
+    idx = _lower_index(sub[ii], sub[jj])
+    assert np.array_equal(N[idx], Nref[ii, jj]), "N differs from the oracle"
+    dA = np.abs(A[idx].astype(np.float64) - Aref[ii, jj]).max()
+    dd = abs(A[_lower_index(sub, sub)].astype(np.float64).mean() - np.diag(Aref).mean())
+    print(f"config 2 shape: max|dA| {dA:.3e}, diag-mean delta {dd:.3e}, N exact on {len(idx)} pairs")
+    assert dA <= 1e-3 and dd <= 1e-5
+    mu_ref, _, _ = oracle.snp_mu(bed[:300], n)
+    assert np.array_equal(mu[:300], mu_ref)

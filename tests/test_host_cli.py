@@ -256,6 +256,14 @@ def test_cli_keep_extract_maf_update_freq(tmp_path):
 
 
 @pytest.mark.gpu
+def test_cli_update_ref_allele_and_related(tmp_path):
+    _full_case(tmp_path, "g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--update-freq", "full.freq", "--make-grm"], "o_uf",
+               ["--bfile", "t", "--update-ref-allele", "refA.txt", "--update-freq", "full.freq", "--make-grm-bin"], "ob_uf")
+    _full_case(tmp_path, "g9_refallele", ["--bfile", "t", "--update-ref-allele", "refA.txt", "--maf", "0.05", "--make-grm"], "o_maf")
+    _full_case(tmp_path, "g10_related", ["--bfile", "t", "--make-grm"], "o", ["--bfile", "t", "--make-grm-bin"], "ob")
+
+
+@pytest.mark.gpu
 def test_cli_xchr(tmp_path):
     _full_case(tmp_path, "g4_xchr", ["--bfile", "t", "--make-grm-xchr"], "o", ["--bfile", "t", "--make-grm-xchr-bin"], "ob")
 

@@ -14,6 +14,7 @@ import numpy as np
 import pytest
 
 from gcta_b200 import abi, synth
+from oracle import oracle
 
 pytestmark = pytest.mark.gpu
 torch = pytest.importorskip("torch")
@@ -43,37 +44,67 @@ def _existing(bed_d, pitch, n, m, km_d, k0, kc):
     return diag.cpu().numpy(), nii.cpu().numpy()
 
 
-def _static(bed_d, pitch, n, km_d, k0, kc):
+def _static(bed_d, pitch, n, km_d, k0, kc, inc_d=None):
     diag = torch.zeros(n, dtype=torch.float64, device="cuda")
     nii = torch.zeros(n, dtype=torch.int32, device="cuda")
-    abi.call("gcta_b200_diag_accum_static", P(bed_d.data_ptr()), I64(pitch), I64(n), P(km_d.data_ptr()), P(None), I64(k0),
+    abi.call("gcta_b200_diag_accum_static", P(bed_d.data_ptr()), I64(pitch), I64(n), P(km_d.data_ptr()),
+             P(None if inc_d is None else inc_d.data_ptr()), I64(k0),
              I64(kc), P(diag.data_ptr()), P(nii.data_ptr()), P(torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     return diag.cpu().numpy(), nii.cpu().numpy()
 
 
-def _device_inputs(seed, n, m, miss):
+def _device_inputs(seed, n, m, miss, kept=None, want_host=False):
     bed = synth.make_bed_payload(seed, n, m, miss_rate=miss)
     stride = bed.shape[1]
     pitch = (stride + 15) // 16 * 16
     bp = np.zeros((m, pitch), dtype=np.uint8)
     bp[:, :stride] = bed
     km = np.zeros(pitch // 4, dtype=np.uint32)
-    for f in range(n):
+    for f in (range(n) if kept is None else kept):
         km[f >> 4] |= np.uint32(1 << ((f & 15) * 2))
-    return torch.from_numpy(bp).cuda(), pitch, torch.from_numpy(km).cuda()
+    out = (torch.from_numpy(bp).cuda(), pitch, torch.from_numpy(km).cuda())
+    return out + (bed,) if want_host else out
+
+
+def _oracle_diag(bed, n, k0, kc, kept=None, include=None):
+    """float64 sum of the float32 squares and the non-missing counts, per FILE individual, for included SNPs
+    [k0, k0+kc); 2p from the kept individuals only (what the keep mask selects)"""
+    inc = None if include is None else np.asarray(include)[k0:k0 + kc]
+    rows = bed[k0:k0 + kc] if include is None else bed[inc]
+    mu, _, _ = oracle.snp_mu(rows, n, keep=None if kept is None else np.asarray(kept, dtype=np.int32))
+    z, ok, _ = oracle.standardise(oracle.decode_x(rows, n), mu=mu)
+    z64 = z.astype(np.float64)
+    return (z64 * z64).sum(0), ok.sum(0).astype(np.int32)
 
 
 def test_static_table_variant_matches_existing_entry_point_twice():
     # first call: larger range; second call: different data, shorter range starting at k0 > 0, so any
     # stale table entry from call 1 that leaked into call 2 would change the sums
     for seed, n, m, miss, k0, kc in [(301, 777, 900, 0.05, 0, 900), (302, 500, 640, 0.01, 128, 300)]:
-        bed_d, pitch, km_d = _device_inputs(seed, n, m, miss)
+        bed_d, pitch, km_d, bed = _device_inputs(seed, n, m, miss, want_host=True)
         d_ref, n_ref = _existing(bed_d, pitch, n, m, km_d, k0, kc)
         d_new, n_new = _static(bed_d, pitch, n, km_d, k0, kc)
         assert np.array_equal(n_new, n_ref)
         assert np.abs(d_new - d_ref).max() <= 1e-9 * max(1.0, d_ref.max())
         assert d_ref.max() > 0
+        # and against the oracle directly (float32 partial sums over 768 SNPs: 1e-6 relative)
+        d_or, n_or = _oracle_diag(bed, n, k0, kc)
+        assert np.array_equal(n_new, n_or) and np.allclose(d_new, d_or, rtol=1e-6, atol=1e-9)
+
+
+def test_static_table_variant_with_a_keep_mask_subset_and_an_include_list():
+    """2p comes from the kept individuals only; the SNP rows are reached through d_include"""
+    n, m_file = 333, 500
+    rng = np.random.default_rng(7)
+    kept = np.sort(rng.choice(n, 200, replace=False))
+    inc = np.sort(rng.choice(m_file, 320, replace=False)).astype(np.int32)
+    bed_d, pitch, km_d, bed = _device_inputs(303, n, m_file, 0.04, kept=kept, want_host=True)
+    inc_d = torch.from_numpy(inc).cuda()
+    for k0, kc in [(0, 320), (64, 100)]:
+        d_new, n_new = _static(bed_d, pitch, n, km_d, k0, kc, inc_d)
+        d_or, n_or = _oracle_diag(bed, n, k0, kc, kept=kept, include=inc)
+        assert np.array_equal(n_new, n_or) and np.allclose(d_new, d_or, rtol=1e-6, atol=1e-9)
 
 
 def test_static_table_variant_rejects_ranges_beyond_its_capacity():
