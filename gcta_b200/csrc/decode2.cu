@@ -29,7 +29,8 @@ namespace gb {
 constexpr int F_THREADS = 128;            // threads per CTA = packed 32-bit columns per slab
 constexpr int F_SLAB = F_THREADS * 16;    // individuals per slab
 constexpr int F_TB = 48;                  // SNP rows per table block (multiple of 6)
-constexpr int F_FLUSH_BLOCKS = 64;        // table blocks between flushes of the float partial sums (3072 rows)
+constexpr int F_FLUSH_BLOCKS = 16;        // table blocks between flushes of the float partial sums (768 rows: the rounding of a
+                                          // float running sum grows with its length; measured 5e-7 relative at 3072 rows)
 
 __device__ __forceinline__ int warp_sum2(int v)
 {
@@ -163,18 +164,56 @@ __device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_
     }
 }
 
+// The same with fewer instructions per genotype: the eight nibble offsets come out of two masked copies of the word by
+// PRMT, which also merges them into the (256-byte aligned) table address, and the squares are added two at a time by
+// the packed FADD2 (acc2[j] = sums of individuals 2j and 2j+1 as a float pair).
 template <bool DIAG>
+__device__ __forceinline__ void emit_word2(uint32_t w, uint32_t row_addr, uint16_t* zdst, int nvalid, unsigned long long (&acc2)[8])
+{
+    const uint32_t ev = (w << 3) & 0x78787878u;   // 8 x nibbles 0, 2, 4, 6 in bytes 0..3
+    const uint32_t od = (w >> 1) & 0x78787878u;   // 8 x nibbles 1, 3, 5, 7
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        uint32_t a;
+        const uint32_t src = (j & 1) ? od : ev;
+        // byte 0 = the nibble's offset, bytes 1..3 = those of the row address
+        if ((j >> 1) == 0) asm("prmt.b32 %0, %1, %2, 0x7650;" : "=r"(a) : "r"(src), "r"(row_addr));
+        else if ((j >> 1) == 1) asm("prmt.b32 %0, %1, %2, 0x7651;" : "=r"(a) : "r"(src), "r"(row_addr));
+        else if ((j >> 1) == 2) asm("prmt.b32 %0, %1, %2, 0x7652;" : "=r"(a) : "r"(src), "r"(row_addr));
+        else asm("prmt.b32 %0, %1, %2, 0x7653;" : "=r"(a) : "r"(src), "r"(row_addr));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(o[j]) : "r"(a));
+        if (DIAG) {
+            unsigned long long q;
+            asm volatile("ld.shared.b64 %0, [%1+128];" : "=l"(q) : "r"(a));
+            asm("add.rn.f32x2 %0, %0, %1;" : "+l"(acc2[j]) : "l"(q));
+        }
+    }
+    if (nvalid >= 16) st_z256(zdst, o);
+    else {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (2 * j >= nvalid) o[j] = 0;
+            else if (2 * j + 1 >= nvalid) o[j] &= 0xFFFFu;
+        }
+        reinterpret_cast<uint4*>(zdst)[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        reinterpret_cast<uint4*>(zdst)[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    }
+}
+
+template <bool DIAG, int VAR>
 __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64_t r1, int64_t col, bool in_z, bool can_load, int nvalid,
                                          uint8_t (*tab)[F_TB][256], int64_t (*row_off)[F_TB])
 {
     const int tid = threadIdx.x;
     const int64_t i0 = col * 16;
-    float acc[16];
+    float acc[16];                 // VAR 0
+    unsigned long long acc2[8];    // VAR 1: float pairs
     uint32_t m16[8];
 #pragma unroll
     for (int e = 0; e < 16; e++) acc[e] = 0.0f;
 #pragma unroll
-    for (int g = 0; g < 8; g++) m16[g] = 0;
+    for (int g = 0; g < 8; g++) { m16[g] = 0; acc2[g] = 0ull; }
     const bool tdiag = DIAG && in_z && i0 < p.diag_f1 && i0 + 16 > p.diag_f0;
     int rows_acc = 0;
 
@@ -201,7 +240,8 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
                     // m16[g]: low half = individual g, high half = individual 8+g; m16[4+g]: individuals 4+g, 12+g
                     const int g = e & 3, hi = (e >> 2) & 1, top = e >> 3;
                     const int miss = (int)((m16[g + 4 * hi] >> (16 * top)) & 0xFFFFu);
-                    atomicAdd(p.diag + f, (double)acc[e]);
+                    const float sum = VAR == 0 ? acc[e] : __uint_as_float((uint32_t)(acc2[e >> 1] >> (32 * (e & 1))));
+                    atomicAdd(p.diag + f, (double)sum);
                     atomicAdd(p.nii + f, rows_acc - miss);
                 }
             }
@@ -209,7 +249,7 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
 #pragma unroll
         for (int e = 0; e < 16; e++) acc[e] = 0.0f;
 #pragma unroll
-        for (int g = 0; g < 8; g++) m16[g] = 0;
+        for (int g = 0; g < 8; g++) { m16[g] = 0; acc2[g] = 0ull; }
         rows_acc = 0;
     };
 
@@ -234,7 +274,8 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
                     uint32_t c2 = 0;
 #pragma unroll
                     for (int u = 3 * h; u < 3 * h + 3; u++) {
-                        emit_word<DIAG>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz, nvalid, acc);
+                        if (VAR == 0) emit_word<DIAG>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz, nvalid, acc);
+                        else emit_word2<DIAG>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz, nvalid, acc2);
                         if (DIAG) c2 += (w[u] & 0x55555555u) & ~(w[u] >> 1);   // missing = code 01b, one count per 2-bit lane
                     }
                     if (DIAG) {
@@ -245,7 +286,8 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
             }
             for (; row < nr; row++) {
                 const uint32_t w = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + row_off[buf][row])) : 0u;
-                emit_word<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc);
+                if (VAR == 0) emit_word<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc);
+                else emit_word2<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc2);
                 if (DIAG) {
                     const uint32_t c2 = (w & 0x55555555u) & ~(w >> 1);
 #pragma unroll
@@ -268,7 +310,7 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
     if (DIAG) flush();
 }
 
-template <int MIN_CTAS>
+template <int MIN_CTAS, int VAR>
 __global__ void __launch_bounds__(F_THREADS, MIN_CTAS) decode_emit_diag_kernel(const FusedParams p)
 {
     // per SNP row 256 bytes: 16 nibble entries of 8 bytes holding the two 16-bit z values of the nibble's two individuals
@@ -285,8 +327,8 @@ __global__ void __launch_bounds__(F_THREADS, MIN_CTAS) decode_emit_diag_kernel(c
     const int64_t s0 = (int64_t)blockIdx.x * F_SLAB;
     const bool cta_diag = p.diag != nullptr && s0 < p.diag_f1 && s0 + F_SLAB > p.diag_f0;
     if (r0 < r1) {
-        if (cta_diag) run_rows<true>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
-        else run_rows<false>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+        if (cta_diag) run_rows<true, VAR>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+        else run_rows<false, VAR>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
     }
     // padding rows of the last 64-SNP block: zero
     if (blockIdx.y == gridDim.y - 1 && in_z) {
@@ -358,8 +400,15 @@ extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, i
     // resident CTAs per SM the kernel is compiled for: 4 (104 registers) by default, GCTA_B200_DECODE_OCC=6 selects the
     // 80-register build (a few spilled bytes, half again as many warps in flight)
     const int occ = getenv("GCTA_B200_DECODE_OCC") ? atoi(getenv("GCTA_B200_DECODE_OCC")) : 4;
-    if (occ >= 6) decode_emit_diag_kernel<6><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
-    else decode_emit_diag_kernel<4><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+    // GCTA_B200_DECODE_VAR=0: plain shift/mask addressing and scalar FADDs (kept for A/B runs)
+    const int var = getenv("GCTA_B200_DECODE_VAR") ? atoi(getenv("GCTA_B200_DECODE_VAR")) : 1;
+    if (occ >= 6) {
+        if (var == 0) decode_emit_diag_kernel<6, 0><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+        else decode_emit_diag_kernel<6, 1><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+    } else {
+        if (var == 0) decode_emit_diag_kernel<4, 0><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+        else decode_emit_diag_kernel<4, 1><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+    }
     GB_CUDA(cudaGetLastError());
     return 0;
 }

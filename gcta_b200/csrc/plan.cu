@@ -156,6 +156,12 @@ struct gcta_b200_plan {
     const int32_t* streamed_N = nullptr;
     int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
     uint8_t *d_bed = nullptr, *d_bed_own = nullptr;   // d_bed: the buffer the kernels read; d_bed_own: the plan's allocation
+    // Packed file larger than its HBM allowance: no resident copy; the rows of one SNP chunk at a time pass through two
+    // ring buffers fed from host memory (plan_run_streamed / plan_run_to_host / make_grm only)
+    bool stream_bed = false;
+    uint8_t* d_ring[2] = {nullptr, nullptr};
+    int64_t ring_rows = 0;
+    cudaEvent_t slot_free[2] = {nullptr, nullptr};   // the last kernel that reads ring slot j has finished
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
     int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr, *d_pairs = nullptr;   // d_pairs: CTA-pair work list of the cta_group::2 SYRK
@@ -204,6 +210,8 @@ extern "C" void gcta_b200_plan_destroy(gcta_b200_plan* p)
     if (p->stream2) cudaStreamDestroy(p->stream2);
     if (p->stream_copy) cudaStreamDestroy(p->stream_copy);
     for (cudaEvent_t e : p->upload_events) cudaEventDestroy(e);
+    for (int j = 0; j < 2; j++)
+        if (p->slot_free[j]) cudaEventDestroy(p->slot_free[j]);
     delete p;
 }
 
@@ -270,10 +278,20 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     PLAN_CUDA(cudaStreamCreateWithFlags(&p->stream2, cudaStreamNonBlocking));
 
-    // fixed-size buffers
-    PLAN_TRY(dev_alloc(p, &p->d_bed, (size_t)p->pitch * a->m_file, err, errcap));
-    p->d_bed_own = p->d_bed;
-    if (p->pitch != p->stride) PLAN_CUDA(cudaMemset(p->d_bed, 0, (size_t)p->pitch * a->m_file));
+    // fixed-size buffers.  The packed genotypes stay resident unless they exceed their allowance: half of the free HBM,
+    // or GCTA_B200_BED_CAP_GIB (a decimal number of GiB; for tests) - then they are streamed chunk by chunk (see stream_bed)
+    {
+        size_t free_b = 0, total_b = 0;
+        PLAN_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        double cap = 0.5 * (double)free_b;
+        if (const char* e = getenv("GCTA_B200_BED_CAP_GIB")) cap = atof(e) * 1073741824.0;
+        p->stream_bed = (double)p->pitch * (double)a->m_file > cap;
+    }
+    if (!p->stream_bed) {
+        PLAN_TRY(dev_alloc(p, &p->d_bed, (size_t)p->pitch * a->m_file, err, errcap));
+        p->d_bed_own = p->d_bed;
+        if (p->pitch != p->stride) PLAN_CUDA(cudaMemset(p->d_bed, 0, (size_t)p->pitch * a->m_file));
+    }
     PLAN_TRY(dev_alloc(p, &p->d_keepmask, (size_t)p->pitch / 4, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_mu, (size_t)m, err, errcap));
     PLAN_TRY(dev_alloc(p, &p->d_cnt, (size_t)m, err, errcap));
@@ -367,6 +385,19 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         for (int64_t len = head > 0 ? head : kc; p->cstart.back() < m; len = std::min<int64_t>(kc, 2 * len))
             p->cstart.push_back(std::min<int64_t>(m, p->cstart.back() + len));
         PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz * planes, err, errcap));
+        if (p->stream_bed) {
+            // two ring buffers, each large enough for the file rows any one chunk reads
+            for (int64_t c = 0; c < p->nchunks(); c++) {
+                int64_t r0 = 0, r1 = 0;
+                gcta_b200_plan_chunk_rows(p, c, &r0, &r1);
+                p->ring_rows = std::max(p->ring_rows, r1 - r0);
+            }
+            for (int j = 0; j < 2; j++) {
+                PLAN_TRY(dev_alloc(p, &p->d_ring[j], (size_t)p->ring_rows * p->pitch, err, errcap));
+                PLAN_CUDA(cudaMemset(p->d_ring[j], 0, (size_t)p->ring_rows * p->pitch));   // the pad bytes of every row stay zero
+                PLAN_CUDA(cudaEventCreateWithFlags(&p->slot_free[j], cudaEventDisableTiming));
+            }
+        }
         p->overlap = getenv("GCTA_B200_OVERLAP") && atoi(getenv("GCTA_B200_OVERLAP")) > 0;
         if (p->overlap && kc < round_up(m, 64)) PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[1], (size_t)kc * p->ldz * planes, err, errcap));
     }
@@ -378,6 +409,7 @@ extern "C" int gcta_b200_plan_upload(gcta_b200_plan* p, const uint8_t* bed_host,
 {
     using namespace gb;
     GB_ARG(p && bed_host, "plan_upload: null argument");
+    GB_ARG(!p->stream_bed, "plan_upload: the packed genotypes exceed their HBM allowance and are streamed from the host; use plan_run_streamed / plan_run_to_host");
     GB_CUDA(cudaSetDevice(p->device));
     // re-pitch rows to a multiple of 16 bytes so K1 can use 128-bit loads; pad bytes are zero
     if (p->pitch != p->stride) GB_CUDA(cudaMemsetAsync(p->d_bed, 0, (size_t)p->pitch * p->m_file, p->stream));
@@ -391,6 +423,7 @@ extern "C" int gcta_b200_plan_use_device_bed(gcta_b200_plan* p, void* d_bed, int
 {
     using namespace gb;
     GB_ARG(p, "plan_use_device_bed: null plan");
+    GB_ARG(!p->stream_bed || !d_bed, "plan_use_device_bed: this plan streams its genotypes from the host");
     if (pitch) *pitch = p->pitch;
     if (d_bed) {
         GB_ARG(((uintptr_t)d_bed & 15) == 0, "plan_use_device_bed: buffer must be 16-byte aligned");
@@ -437,6 +470,7 @@ extern "C" int gcta_b200_plan_upload_rows_async(gcta_b200_plan* p, const uint8_t
 {
     using namespace gb;
     GB_ARG(p && bed_host, "plan_upload_rows_async: null argument");
+    GB_ARG(!p->stream_bed, "plan_upload_rows_async: the packed genotypes exceed their HBM allowance and are streamed from the host; use plan_run_streamed / plan_run_to_host");
     GB_ARG(row_begin >= 0 && row_begin <= row_end && row_end <= p->m_file, "plan_upload_rows_async: bad row range");
     GB_CUDA(cudaSetDevice(p->device));
     if (row_end > row_begin)
@@ -460,6 +494,7 @@ extern "C" int gcta_b200_plan_upload_rows(gcta_b200_plan* p, const uint8_t* bed_
 {
     using namespace gb;
     GB_ARG(p && bed_host, "plan_upload_rows: null argument");
+    GB_ARG(!p->stream_bed, "plan_upload_rows: the packed genotypes exceed their HBM allowance and are streamed from the host; use plan_run_streamed / plan_run_to_host");
     GB_ARG(row_begin >= 0 && row_begin <= row_end && row_end <= p->m_file, "plan_upload_rows: bad row range");
     GB_CUDA(cudaSetDevice(p->device));
     if (row_end > row_begin)
@@ -473,6 +508,7 @@ extern "C" int gcta_b200_plan_download_bed(gcta_b200_plan* p, uint8_t* bed_host,
 {
     using namespace gb;
     GB_ARG(p && bed_host, "plan_download_bed: null argument");
+    GB_ARG(!p->stream_bed, "plan_download_bed: the packed genotypes exceed their HBM allowance and are streamed from the host; use plan_run_streamed / plan_run_to_host");
     GB_CUDA(cudaSetDevice(p->device));
     GB_CUDA(cudaMemcpy2DAsync(bed_host, (size_t)p->stride, p->d_bed, (size_t)p->pitch, (size_t)p->stride, (size_t)p->m_file,
                               cudaMemcpyDeviceToHost, p->stream));
@@ -517,6 +553,7 @@ extern "C" int gcta_b200_plan_synth(gcta_b200_plan* p, uint64_t seed, const uint
 {
     using namespace gb;
     GB_ARG(p && thr_host, "plan_synth: null argument");
+    GB_ARG(!p->stream_bed, "plan_synth: the packed genotypes exceed their HBM allowance and are streamed from the host; use plan_run_streamed / plan_run_to_host");
     GB_CUDA(cudaSetDevice(p->device));
     uint4* d_thr = nullptr;
     GB_CUDA(cudaMalloc(&d_thr, (size_t)p->m_file * 16));
@@ -635,20 +672,52 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             up.push_back(ev);
         }
     }
-    // host -> HBM copy of the file rows chunk c needs; issued one chunk ahead of the compute so that it overlaps
-    // even when the host buffer is pageable (then the call blocks the host, but the GPU is already busy)
-    auto issue_upload = [&](int64_t c) -> cudaError_t {
-        if (!bed_host || c >= nch_up) return cudaSuccess;
+    GB_ARG(!p->stream_bed || bed_host, "plan_run: the packed genotypes exceed their HBM allowance and are streamed from the host; use plan_run_streamed / plan_run_to_host");
+    // file rows chunk c reads
+    auto chunk_rows = [&](int64_t c, int64_t& r0, int64_t& r1) {
         const int64_t k0 = p->cstart[c], k1 = p->cstart[c + 1];
-        int64_t r0 = k0, r1 = k1;
+        r0 = k0; r1 = k1;
         if (p->has_include) {
             r0 = *std::min_element(p->h_include.begin() + k0, p->h_include.begin() + k1);
             r1 = *std::max_element(p->h_include.begin() + k0, p->h_include.begin() + k1) + 1;
         }
-        cudaError_t e = cudaMemcpy2DAsync(p->d_bed + r0 * p->pitch, (size_t)p->pitch, bed_host + r0 * p->stride, (size_t)p->stride,
+    };
+    // host -> HBM copy of the file rows chunk c needs; issued one chunk ahead of the compute so that it overlaps
+    // even when the host buffer is pageable (then the call blocks the host, but the GPU is already busy).
+    // Resident genotypes: into place in the whole-file buffer.  Streamed genotypes: into ring slot seq & 1, once the
+    // kernels that read the slot's previous contents have finished (`seq` counts the chunks staged during this run).
+    int64_t seq_next = 0;
+    bool slot_used[2] = {false, false};
+    auto issue_upload = [&](int64_t c) -> cudaError_t {
+        if (!bed_host || c >= nch_up) return cudaSuccess;
+        int64_t r0, r1;
+        chunk_rows(c, r0, r1);
+        uint8_t* dst = p->d_bed + r0 * p->pitch;
+        if (p->stream_bed) {
+            const int slot = (int)(seq_next++ & 1);
+            dst = p->d_ring[slot];
+            if (slot_used[slot]) {
+                cudaError_t e = cudaStreamWaitEvent(p->stream_copy, p->slot_free[slot], 0);
+                if (e != cudaSuccess) return e;
+            }
+        }
+        cudaError_t e = cudaMemcpy2DAsync(dst, (size_t)p->pitch, bed_host + r0 * p->stride, (size_t)p->stride,
                                           (size_t)p->stride, (size_t)(r1 - r0), cudaMemcpyHostToDevice, p->stream_copy);
         if (e != cudaSuccess) return e;
         return cudaEventRecord(up[c], p->stream_copy);
+    };
+    // what the kernels of the seq-th staged chunk (chunk c) take as "the packed file": row r lives at bed + r * pitch
+    auto bed_of = [&](int64_t c, int64_t seq) -> const uint8_t* {
+        if (!p->stream_bed) return p->d_bed;
+        int64_t r0, r1;
+        chunk_rows(c, r0, r1);
+        return p->d_ring[seq & 1] - r0 * p->pitch;
+    };
+    // the last kernel reading the seq-th staged chunk has been queued on `s`
+    auto release_slot = [&](int64_t seq, cudaStream_t s) -> cudaError_t {
+        if (!p->stream_bed) return cudaSuccess;
+        slot_used[seq & 1] = true;
+        return cudaEventRecord(p->slot_free[seq & 1], s);
     };
     GB_CUDA(issue_upload(0));
     // Two streams: `sd` standardises chunk c+1 (K1, K1d - HBM / ALU work) while `st` runs the SYRK of
@@ -697,25 +766,27 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             GB_CUDA(cudaStreamWaitEvent(sd, p->chunk_ready[c], 0));                  // (e.g. an NVLink all-gather per chunk)
         GB_CUDA(cudaEventRecord(EV(c, 0), sd));
         int rc = 0;
+        const uint8_t* bedc = bed_of(c, c);   // first pass: chunk c is the c-th staged chunk
         if (p->fused_decode) {
-            rc = gcta_b200_snp_stats(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->n, p->d_include, k0, kc, p->d_mu_in, p->alg, p->d_mu,
+            rc = gcta_b200_snp_stats(bedc, p->pitch, p->n_file, p->d_keepmask, p->n, p->d_include, k0, kc, p->d_mu_in, p->alg, p->d_mu,
                                      p->d_cnt, p->d_sum, p->d_zlut, p->d_total_missing, sd, err, errcap);
             // Z and the band's diagonal in one pass over the packed rows
-            if (!rc) rc = gcta_b200_decode_emit_diag(p->d_bed, p->pitch, p->n_file, p->d_include, k0, kc, p->d_zlut, p->operand, Z, p->ldz,
+            if (!rc) rc = gcta_b200_decode_emit_diag(bedc, p->pitch, p->n_file, p->d_include, k0, kc, p->d_zlut, p->operand, Z, p->ldz,
                                                      p->d_diag, p->d_nii, p->diag_f0, p->diag_f1, sd, err, errcap);
             if (rc) return rc;
         } else {
-        rc = gcta_b200_bed_decode_ex(p->d_bed, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
+        rc = gcta_b200_bed_decode_ex(bedc, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
                                          p->d_mu_in, p->xchr, p->alg, p->operand, Z, p->ldz, p->d_mu, p->d_cnt, p->d_sum, p->d_zlut,
                                          p->d_dk, p->d_total_missing, sd, err, errcap);
         if (rc) return rc;
         // the diagonal is only needed for this band's own individuals: hand K1d that slice of columns
-        rc = p->diag_f1 > p->diag_f0 ? gcta_b200_diag_accum_ex(p->d_bed + p->diag_f0 / 4, p->pitch, p->diag_f1 - p->diag_f0, p->d_sexmale ? p->d_sexmale + p->diag_f0 / 16 : nullptr,
+        rc = p->diag_f1 > p->diag_f0 ? gcta_b200_diag_accum_ex(bedc + p->diag_f0 / 4, p->pitch, p->diag_f1 - p->diag_f0, p->d_sexmale ? p->d_sexmale + p->diag_f0 / 16 : nullptr,
                                                                 p->d_include, k0, kc, p->d_zlut, p->d_diag + p->diag_f0, p->d_nii + p->diag_f0, p->d_dk,
                                                                 p->d_dw ? p->d_dw + p->diag_f0 : nullptr, sd, err, errcap) : 0;
         if (rc) return rc;
         }
         GB_CUDA(cudaEventRecord(EV(c, 1), sd));
+        GB_CUDA(release_slot(c, sd));
         GB_CUDA(cudaStreamWaitEvent(st, EV(c, 1), 0));
         GB_CUDA(cudaEventRecord(EV(c, 2), st));
         if (to_host && c == nchunks - 1 && out->A_lower && p->operand != GCTA_B200_FP16X2 && !p->d_pairs && p->alg == 0 && p->ntiles > 0) {
@@ -760,16 +831,29 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         rc = dev_alloc(p, &p->d_N_lower, (size_t)p->band_count, err, errcap);
         if (rc) return rc;
     }
+    GB_ARG(!(p->stream_bed && tm > 0 && use_popc), "plan_run: GCTA_B200_N_MODE=popc needs resident genotypes");
+    // Streamed genotypes: a pass that reads the packed rows again (the indicator passes below) stages every chunk a second
+    // time through the ring, one chunk ahead of the kernels like the first pass.
+    auto restage_begin = [&]() -> cudaError_t { return p->stream_bed ? issue_upload(0) : cudaSuccess; };
+    auto restage_wait = [&](int64_t c) -> cudaError_t { return p->stream_bed ? cudaStreamWaitEvent(st, up[c], 0) : cudaSuccess; };
+    auto restage_next = [&](int64_t c, int64_t seq) -> cudaError_t {
+        cudaError_t e = release_slot(seq, st);
+        return e != cudaSuccess ? e : (p->stream_bed ? issue_upload(c + 1) : cudaSuccess);
+    };
     if (tm > 0 && !use_popc) {
         GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
+        const int64_t seq0 = seq_next;
+        GB_CUDA(restage_begin());
         for (int64_t c = 0; c < nchunks; c++) {   // the Z buffer is free again: reuse it for the indicator chunks
             const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
+            GB_CUDA(restage_wait(c));
             // 8-bit E4M3 indicators (kind::f8f6f4: twice the MMA rate, half the bytes) unless the CTA-pair kernel or
             // GCTA_B200_N_MODE=tensor16 asks for the 16-bit route; both give the same integers
             const int opN = (p->d_pairs || (nmode && strcmp(nmode, "tensor16") == 0)) ? op16 : GCTA_B200_E4M3;
-            int rc = gcta_b200_nonmiss_matrix(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, opN,
+            int rc = gcta_b200_nonmiss_matrix(bed_of(c, seq0 + c), p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, opN,
                                               p->d_Zbuf[0], p->ldz, st, err, errcap);
             if (rc) return rc;
+            GB_CUDA(restage_next(c, seq0 + c));
             rc = syrk(p->d_Zbuf[0], p->d_Zbuf[0], round_up(kc, opN == GCTA_B200_E4M3 ? 128 : 64), opN, p->d_Ntiles, true, st);
             if (rc) return rc;
             launches += 2;
@@ -807,11 +891,15 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
                 if (rc) return rc;
             }
             GB_CUDA(cudaMemsetAsync(p->d_Dtiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
+            const int64_t seq0 = seq_next;
+            GB_CUDA(restage_begin());
             for (int64_t c = 0; c < nchunks; c++) {
                 const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
-                int rc = gcta_b200_nonmiss_matrix_ex(p->d_bed, p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16, p->d_dk,
+                GB_CUDA(restage_wait(c));
+                int rc = gcta_b200_nonmiss_matrix_ex(bed_of(c, seq0 + c), p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, op16, p->d_dk,
                                                      p->d_Zbuf[0], p->ldz, st, err, errcap);
                 if (rc) return rc;
+                GB_CUDA(restage_next(c, seq0 + c));
                 rc = syrk(p->d_Zbuf[0], p->d_Zbuf[0], round_up(kc, 64), op16, p->d_Dtiles, false, st);
                 if (rc) return rc;
                 launches += 2;
