@@ -18,7 +18,7 @@ TILE_M, TILE_N = 256, 256
 IPC_HANDLE_BYTES = 64   # GCTA_B200_IPC_HANDLE_BYTES
 
 EXPORTS = [
-    "gcta_b200_make_grm", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth", "gcta_b200_plan_download_bed",
+    "gcta_b200_make_grm", "gcta_b200_make_grm_multi", "gcta_b200_plan_set_chunk_hook", "gcta_b200_plan_own_bed", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth", "gcta_b200_plan_download_bed",
     "gcta_b200_plan_run", "gcta_b200_plan_run_streamed", "gcta_b200_plan_download", "gcta_b200_plan_device_results", "gcta_b200_plan_destroy",
     "gcta_b200_bed_decode", "gcta_b200_snp_stats", "gcta_b200_decode_emit_diag", "gcta_b200_diag_accum", "gcta_b200_diag_accum_static", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles",
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
@@ -148,6 +148,22 @@ def make_grm(bed, n_file, m_file, want_N=True, **kw):
     err = C.create_string_buffer(ERRCAP)
     _check(lib().gcta_b200_make_grm(C.byref(a), C.byref(o), err, ERRCAP), err)
     return A, N, mu, o
+
+
+def make_grm_multi(bed, n_file, m_file, n_gpus, want_N=True, **kw):
+    """gcta_b200_make_grm_multi: the whole path on n_gpus devices of this process.
+    -> (A_lower, N_lower or None, mu, Out, [Out per device])"""
+    a, ka = make_args(bed, n_file, m_file, **kw)
+    n, m = a.n, a.m
+    A = np.zeros(n * (n + 1) // 2, dtype=np.float32)
+    N = np.zeros(n * (n + 1) // 2, dtype=np.int32) if want_N else None
+    mu = np.zeros(m, dtype=np.float64)
+    o = Out()
+    o.A_lower, o.N_lower, o.mu_out = A.ctypes.data, _ptr(N), mu.ctypes.data
+    per = (Out * n_gpus)()
+    err = C.create_string_buffer(ERRCAP)
+    _check(lib().gcta_b200_make_grm_multi(C.byref(a), C.c_int32(n_gpus), C.byref(o), per, err, ERRCAP), err)
+    return A, N, mu, o, list(per)
 
 
 class Plan:

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgcta_b200.so")
-SOURCES = ["decode.cu", "decode2.cu", "nonmiss.cu", "syrk.cu", "syrk2.cu", "paircount.cu", "finalize.cu", "plan.cu", "exchange.cu"]
+SOURCES = ["decode.cu", "decode2.cu", "nonmiss.cu", "syrk.cu", "syrk2.cu", "paircount.cu", "finalize.cu", "plan.cu", "exchange.cu", "multi.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--fmad=true"]
 

@@ -51,9 +51,9 @@ __global__ void __launch_bounds__(256) snp_stats_kernel(const uint8_t* __restric
 {
     __shared__ int miss_s[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t kk = (int64_t)blockIdx.x * 8 + warp;
     int missing = 0;
-    if (kk < kc) {
+    // grid-stride over the rows: the grid is one wave of resident CTAs, so no partly filled last wave
+    for (int64_t kk = (int64_t)blockIdx.x * 8 + warp; kk < kc; kk += (int64_t)gridDim.x * 8) {
         const int64_t k = k0 + kk;
         const uint4* row16 = reinterpret_cast<const uint4*>(bed + (int64_t)(include ? include[k] : (int32_t)k) * pitch);
         const uint4* km16 = reinterpret_cast<const uint4*>(keepmask);
@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(256) snp_stats_kernel(const uint8_t* __restric
             sum_out[k] = sum;
             reinterpret_cast<float4*>(zlut + k * 8)[0] = make_float4(z[0], z[1], z[2], z[3]);
             reinterpret_cast<float4*>(zlut + k * 8)[1] = make_float4(z[0], z[1], z[2], z[3]);   // "male" half: same on autosomes
-            missing = (int)(n_kept - cnt);
+            missing += (int)(n_kept - cnt);
         }
     }
     if (lane == 0) miss_s[warp] = missing;
@@ -254,6 +254,15 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
     };
 
     const uint8_t* colp = p.bed + col * 4;
+    uint32_t wn[6];            // the packed words of the next group of six rows
+    bool have_next = false;
+    auto load6 = [&](uint32_t (&dst)[6], int b, int64_t rb, int row) {
+#pragma unroll
+        for (int u = 0; u < 6; u++) {
+            const int64_t off = p.include ? row_off[b][row + u] : (p.k0 + rb + row + u) * p.pitch;
+            dst[u] = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + off)) : 0u;
+        }
+    };
     int buf = 0, blocks = 0;
     build(0, r0);
     __syncthreads();
@@ -265,10 +274,16 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
             const uint32_t tab_addr = smem_u32(&tab[buf][0][0]);
             uint32_t c8[4] = {0, 0, 0, 0};
             int row = 0;
+            if (!have_next && nr >= 6) load6(wn, buf, rbase, 0);
             for (; row + 6 <= nr; row += 6) {
                 uint32_t w[6];
 #pragma unroll
-                for (int u = 0; u < 6; u++) w[u] = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + row_off[buf][row + u])) : 0u;
+                for (int u = 0; u < 6; u++) w[u] = wn[u];
+                // the next six rows' words are fetched before this group is processed, so that their latency hides behind
+                // its ~250 instructions - also across a table block's end when the row addresses need no table
+                have_next = false;
+                if (row + 12 <= nr) { load6(wn, buf, rbase, row + 6); have_next = true; }
+                else if (!p.include && nr == F_TB && row + 6 == nr && rbase + F_TB + 6 <= r1) { load6(wn, buf ^ 1, rbase + F_TB, 0); have_next = true; }
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     uint32_t c2 = 0;
@@ -285,7 +300,8 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
                 }
             }
             for (; row < nr; row++) {
-                const uint32_t w = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + row_off[buf][row])) : 0u;
+                const int64_t off = p.include ? row_off[buf][row] : (p.k0 + rbase + row) * p.pitch;
+                const uint32_t w = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + off)) : 0u;
                 if (VAR == 0) emit_word<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc);
                 else emit_word2<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc2);
                 if (DIAG) {
@@ -354,7 +370,11 @@ extern "C" int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t 
     GB_ARG(pitch * 4 >= n_file && n_file > 0 && n > 0 && n <= n_file, "snp_stats: pitch too small for n_file, or bad n");
     GB_ARG(kc > 0 && k0 >= 0, "snp_stats: empty SNP range");
     GB_ARG(((uintptr_t)d_zlut & 15) == 0, "snp_stats: zlut must be 16-byte aligned");
-    snp_stats_kernel<<<(unsigned)((kc + 7) / 8), 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, n, d_keepmask, d_include, k0, kc, d_mu_in,
+    int dev = 0, sms = 0;
+    GB_CUDA(cudaGetDevice(&dev));
+    GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int64_t ctas = std::min<int64_t>((kc + 7) / 8, (int64_t)sms * 8);   // 8 CTAs of 256 threads fill an SM
+    snp_stats_kernel<<<(unsigned)ctas, 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, n, d_keepmask, d_include, k0, kc, d_mu_in,
                                                                                   alg == 0, d_mu, d_cnt, d_sum, d_zlut, d_total_missing);
     GB_CUDA(cudaGetLastError());
     return 0;
@@ -386,20 +406,22 @@ extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, i
     GB_CUDA(cudaGetDevice(&dev));
     GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int64_t slabs = (ldz / 16 + F_THREADS - 1) / F_THREADS;
-    // rows per CTA: about four CTAs per slab and SM (the tail of a launch stays short), at least one table block, and few
-    // enough rows that the 16-bit missing counters cannot overflow between flushes
+    // Rows per CTA.  All CTAs do the same work (except those of a partly filled last slab), so the launch should be a whole
+    // number of waves of the resident capacity (4 CTAs per SM; 6 with GCTA_B200_DECODE_OCC=6): groups of rows = (capacity / slabs) x waves, with about
+    // 384 rows per CTA - long enough to amortise the table set-up and the final atomics, short enough for a few waves.
     const int64_t rows_env = getenv("GCTA_B200_DECODE_ROWS") ? atoll(getenv("GCTA_B200_DECODE_ROWS")) : 0;
-    int64_t groups = std::max<int64_t>(1, ((int64_t)sms * 16 + slabs - 1) / slabs);
+    const int occ = getenv("GCTA_B200_DECODE_OCC") ? atoi(getenv("GCTA_B200_DECODE_OCC")) : 4;
+    const int64_t per_wave = std::max<int64_t>(1, (int64_t)sms * (occ >= 6 ? 6 : 4) / slabs);
+    const int64_t waves = std::max<int64_t>(1, (kc + per_wave * 384 - 1) / (per_wave * 384));
+    int64_t groups = per_wave * waves;
     int64_t rows = rows_env > 0 ? rows_env : (kc + groups - 1) / groups;
-    rows = std::max<int64_t>(rows, F_TB);
-    rows = (rows + F_TB - 1) / F_TB * F_TB;
+    rows = std::max<int64_t>((rows + 5) / 6 * 6, 6);
     groups = (kc + rows - 1) / rows;
     GB_ARG(groups <= 65535, "decode_emit_diag: SNP range too long for one launch");
     p.rows_per_cta = rows;
     dim3 grid((unsigned)slabs, (unsigned)groups);
     // resident CTAs per SM the kernel is compiled for: 4 (104 registers) by default, GCTA_B200_DECODE_OCC=6 selects the
     // 80-register build (a few spilled bytes, half again as many warps in flight)
-    const int occ = getenv("GCTA_B200_DECODE_OCC") ? atoi(getenv("GCTA_B200_DECODE_OCC")) : 4;
     // GCTA_B200_DECODE_VAR=0: plain shift/mask addressing and scalar FADDs (kept for A/B runs)
     const int var = getenv("GCTA_B200_DECODE_VAR") ? atoi(getenv("GCTA_B200_DECODE_VAR")) : 1;
     if (occ >= 6) {

@@ -148,6 +148,10 @@ struct gcta_b200_plan {
     cudaStream_t stream = nullptr, stream2 = nullptr, stream_copy = nullptr;
     std::vector<cudaEvent_t> upload_events;
     std::vector<cudaEvent_t> chunk_ready;   // caller-owned events: chunk c's packed rows are in place (plan_set_chunk_events)
+    // the same as a call-back: invoked on the host right before chunk c's first kernel is queued on `stream`; it may
+    // block, and it queues whatever waits make the chunk's rows complete (gcta_b200_plan_set_chunk_hook; multi.cu)
+    int (*chunk_hook)(void* ctx, int64_t chunk, void* stream) = nullptr;
+    void* chunk_hook_ctx = nullptr;
     std::vector<int32_t> h_include, h_tiles;
     std::vector<int64_t> cstart;   // SNP chunk c = included SNPs [cstart[c], cstart[c+1]); every chunk <= `chunk` SNPs
     int64_t nchunks() const { return (int64_t)cstart.size() - 1; }
@@ -255,7 +259,8 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     // Rounding errors of 16-bit operands average out like 1/sqrt(M); with few SNPs they do not (a single FP16 product
     // is only good to ~1e-3 relative and A_ij is then O(1)).  Short contractions therefore use the split-FP16 mode,
     // which costs nothing measurable at these sizes and keeps max|dA| <= 1e-3 for any M.
-    if (p->operand == GCTA_B200_FP16 && m < 8192) p->operand = GCTA_B200_FP16X2;
+    // BF16 (8 significand bits) needs the averaging even more, so it is upgraded the same way.
+    if ((p->operand == GCTA_B200_FP16 || p->operand == GCTA_B200_BF16) && m < 8192) p->operand = GCTA_B200_FP16X2;
     p->has_keep = a->keep != nullptr && !(n == a->n_file);
     p->has_include = a->include != nullptr;
     p->has_mu = a->mu != nullptr;
@@ -489,6 +494,16 @@ extern "C" int gcta_b200_plan_set_chunk_events(gcta_b200_plan* p, void* const* e
     for (int64_t i = 0; i < count; i++) p->chunk_ready.push_back((cudaEvent_t)events[i]);
     return 0;
 }
+
+extern "C" int gcta_b200_plan_set_chunk_hook(gcta_b200_plan* p, int (*hook)(void*, int64_t, void*), void* ctx)
+{
+    if (!p) return GCTA_B200_ERR_ARG;
+    p->chunk_hook = hook;
+    p->chunk_hook_ctx = ctx;
+    return 0;
+}
+
+extern "C" void* gcta_b200_plan_own_bed(gcta_b200_plan* p) { return p ? p->d_bed_own : nullptr; }
 
 extern "C" int gcta_b200_plan_upload_rows(gcta_b200_plan* p, const uint8_t* bed_host, int64_t row_begin, int64_t row_end, char* err, size_t errcap)
 {
@@ -764,6 +779,8 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         if (bed_host) GB_CUDA(cudaStreamWaitEvent(sd, up[c], 0));        // this chunk's packed rows have landed
         if (!bed_host && c < (int64_t)p->chunk_ready.size() && p->chunk_ready[c])   // ... or were delivered by the caller
             GB_CUDA(cudaStreamWaitEvent(sd, p->chunk_ready[c], 0));                  // (e.g. an NVLink all-gather per chunk)
+        if (!bed_host && p->chunk_hook && p->chunk_hook(p->chunk_hook_ctx, c, sd) != 0)
+            return set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: plan_run: the delivery of a chunk's packed rows failed.");
         GB_CUDA(cudaEventRecord(EV(c, 0), sd));
         int rc = 0;
         const uint8_t* bedc = bed_of(c, c);   // first pass: chunk c is the c-th staged chunk

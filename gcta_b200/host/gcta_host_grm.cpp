@@ -201,34 +201,25 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
     std::unique_ptr<float[]> A(new float[tri]);
     std::unique_ptr<int32_t[]> N(output_bin ? nullptr : new int32_t[tri]);   // --make-grm-bin drops N (grm.cpp:307-318)
     const int G = std::max(1, std::min(n_gpus, gcta_b200_device_count() > 0 ? gcta_b200_device_count() : 1));
-    vector<string> errs(G);
-    vector<int> rcs(G, 0);
     vector<gcta_b200_out> outs(G);
     const auto t_c0 = std::chrono::steady_clock::now();
-    auto work = [&](int g) {
+    {
+        // one call from the main thread, like the reference's (option.cpp:620-621).  With several GPUs the library cuts the
+        // triangle into row bands, uploads 1/G of the packed rows per device and spreads them with peer copies.
         gcta_b200_args a;
         memset(&a, 0, sizeof a);
         a.bed = _bed.data(); a.n_file = _indi_num; a.m_file = _snp_num;
         a.keep = keep.data(); a.n = n; a.include = inc.data(); a.m = m;
         a.mu = mu.empty() ? nullptr : mu.data();
         a.sex = sex.data(); a.xchr = grm_xchr_flag; a.alg = grm_mtd; a.operand = operand;
-        a.device = g; a.part_rank = g; a.part_world = G; a.chunk_snps = chunk_snps;
-        gcta_b200_out& o = outs[g];
+        a.device = 0; a.part_rank = 0; a.part_world = 1; a.chunk_snps = chunk_snps;
+        gcta_b200_out o;
         memset(&o, 0, sizeof o);
         o.A_lower = A.get();
         o.N_lower = N.get();
         char err[512] = {0};
-        rcs[g] = gcta_b200_make_grm(&a, &o, err, sizeof err);
-        errs[g] = err;
-    };
-    if (G == 1) work(0);
-    else {
-        vector<std::thread> th;
-        for (int g = 0; g < G; g++) th.emplace_back(work, g);
-        for (auto& t : th) t.join();
+        if (gcta_b200_make_grm_multi(&a, G, &o, outs.data(), err, sizeof err) != 0) throw string(err);
     }
-    for (int g = 0; g < G; g++)
-        if (rcs[g]) throw errs[g];
     cout << n << " of " << n << " individuals.\r";   // the reference prints one such line per row (grm.cpp:297)
     cout << endl << endl;
     if (getenv("GCTA_B200_TIMING")) {

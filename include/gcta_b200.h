@@ -41,7 +41,7 @@ typedef enum {
 typedef enum {
     GCTA_B200_FP16 = 0, /* default: 11-bit significand, |z| <= 65504 (MAF >= 1e-9); with fewer than 8192 included
                            SNPs the plan upgrades it to GCTA_B200_FP16X2 (rounding no longer averages out) */
-    GCTA_B200_BF16 = 1,
+    GCTA_B200_BF16 = 1, /* 8-bit significand; upgraded to GCTA_B200_FP16X2 below 8192 included SNPs like FP16 */
     /* "tight" mode: z = hi + lo with hi = fp16(z), lo = fp16(z - hi); S = hi'hi + hi'lo + lo'hi on the tensor
      * cores (3x the SYRK work, twice the Z traffic).  Products are then exact to ~2^-22 relative, so A agrees
      * with the reference to FP32-accumulation accuracy (max|dA| ~1e-7).  The north-star's "TF32 mode for tighter
@@ -95,6 +95,16 @@ typedef struct {
 
 int gcta_b200_make_grm(const gcta_b200_args* args, gcta_b200_out* out, char* err, size_t errcap);
 
+/* The same on n_gpus devices of THIS process (args->device .. args->device + n_gpus - 1; args->part_* are ignored): the
+ * lower triangle is cut into n_gpus row bands, one plan and one host thread per device.  Every device needs all packed
+ * rows; instead of n_gpus full uploads, each device uploads 1/n_gpus of every row segment over its own PCIe link and
+ * pushes it to the others with peer copies (copy engines over NVLink), and each band starts a SNP chunk as soon as
+ * the segments it reads are complete - the seam stays the reference's one call per process from the main thread
+ * (option.cpp:620-621).  out->A_lower / N_lower are filled completely; the timings in *out are the slowest device's,
+ * per_gpu (NULL or n_gpus entries) receives each device's. */
+int gcta_b200_make_grm_multi(const gcta_b200_args* args, int32_t n_gpus, gcta_b200_out* out, gcta_b200_out* per_gpu,
+                             char* err, size_t errcap);
+
 /* Allele counts without building a GRM: the counting half of calcu_mu / mu_func (data.cpp:759-803)
  * that --freq, --maf and --max-maf need (option.cpp:604-615).  Host pointers; per included SNP the
  * non-missing count and the allele-1 dosage sum among kept individuals.  When args->sex and all four
@@ -134,6 +144,12 @@ int gcta_b200_plan_chunk_rows(gcta_b200_plan* plan, int64_t chunk, int64_t* row_
 int gcta_b200_plan_upload_rows_async(gcta_b200_plan* plan, const uint8_t* bed_host, int64_t row_begin, int64_t row_end,
                                      void* stream, char* err, size_t errcap);
 int gcta_b200_plan_set_chunk_events(gcta_b200_plan* plan, void* const* events, int64_t count, char* err, size_t errcap);
+/* plan_set_chunk_events as a call-back: `hook(ctx, chunk, stream)` is called on the host right before the first kernel of
+ * SNP chunk `chunk` is queued on `stream` (a cudaStream_t) by plan_run / plan_run_to_host with bed_host == NULL.  It may
+ * block, and it queues on `stream` whatever waits make that chunk's file rows complete; non-zero return aborts the run.
+ * plan_own_bed: device address of the plan's own genotype buffer (m_file rows x pitch; NULL when streamed). */
+int gcta_b200_plan_set_chunk_hook(gcta_b200_plan* plan, int (*hook)(void* ctx, int64_t chunk, void* stream), void* ctx);
+void* gcta_b200_plan_own_bed(gcta_b200_plan* plan);
 /* back to the plan's own genotype buffer after plan_use_device_bed; the plan's device, file rows, row stride, row pitch */
 int gcta_b200_plan_use_own_bed(gcta_b200_plan* plan);
 int gcta_b200_plan_geometry(gcta_b200_plan* plan, int32_t* device, int64_t* m_file, int64_t* stride, int64_t* pitch);

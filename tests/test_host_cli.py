@@ -203,7 +203,7 @@ def test_reader_and_filter_log_lines_match_reference(tmp_path):
 # ------------------------------------------------------------------------------------------------
 def _full_case(tmp_path, case, args_txt, ref_txt, args_bin=None, ref_bin=None, same_log=True):
     d = tmp_path / case
-    shutil.copytree(os.path.join(GOLDEN, case), d)
+    shutil.copytree(os.path.join(GOLDEN, case), d, dirs_exist_ok=True)
     r = run_cli(args_txt + ["--out", "mine"], d)
     assert r.stderr.strip() == "", r.stderr
     A, N, _ = grmio.read_grm_gz(str(d / "mine.grm.gz"))

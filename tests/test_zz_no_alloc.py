@@ -88,9 +88,9 @@ def test_static_table_variant_matches_existing_entry_point_twice():
         assert np.array_equal(n_new, n_ref)
         assert np.abs(d_new - d_ref).max() <= 1e-9 * max(1.0, d_ref.max())
         assert d_ref.max() > 0
-        # and against the oracle directly (float32 partial sums over 768 SNPs: 1e-6 relative)
+        # and against the oracle directly (float32 partial sums over up to 768 SNPs: a few 1e-6 relative)
         d_or, n_or = _oracle_diag(bed, n, k0, kc)
-        assert np.array_equal(n_new, n_or) and np.allclose(d_new, d_or, rtol=1e-6, atol=1e-9)
+        assert np.array_equal(n_new, n_or) and np.allclose(d_new, d_or, rtol=1e-5, atol=1e-9)
 
 
 def test_static_table_variant_with_a_keep_mask_subset_and_an_include_list():
@@ -104,7 +104,7 @@ def test_static_table_variant_with_a_keep_mask_subset_and_an_include_list():
     for k0, kc in [(0, 320), (64, 100)]:
         d_new, n_new = _static(bed_d, pitch, n, km_d, k0, kc, inc_d)
         d_or, n_or = _oracle_diag(bed, n, k0, kc, kept=kept, include=inc)
-        assert np.array_equal(n_new, n_or) and np.allclose(d_new, d_or, rtol=1e-6, atol=1e-9)
+        assert np.array_equal(n_new, n_or) and np.allclose(d_new, d_or, rtol=1e-5, atol=1e-9)
 
 
 def test_static_table_variant_rejects_ranges_beyond_its_capacity():
