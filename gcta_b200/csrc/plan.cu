@@ -10,7 +10,9 @@
 // the lower triangle, balanced by tile count, so outputs are disjoint contiguous ranges of
 // the packed triangle and no collective is needed on the data path.
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
+#include <memory>
 #include <thread>
 #include <vector>
 
@@ -584,6 +586,114 @@ extern "C" int gcta_b200_plan_synth(gcta_b200_plan* p, uint64_t seed, const uint
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Pageable host genotypes.  cudaMemcpy2DAsync from pageable memory lets the driver stage the rows itself, on the
+// calling thread, at a few GB/s (measured: 12.5 GB in ~3 s, twice the compute of the headline workload).  Instead, a few
+// host threads copy the rows into pinned slots of their own - re-pitched on the way, so that the device copy is one
+// contiguous block - and queue the host->device copies on their own streams, running ahead of the compute by the depth
+// of their slots.  Per thread and SNP chunk an event marks "my slabs of this chunk are queued"; the run waits for all of
+// them before it standardises the chunk (on the host until the record exists, on the device until it fires).
+// ------------------------------------------------------------------------------------------------
+namespace gb {
+
+struct Stager {
+    static constexpr int K = 6, SLOTS = 2;
+    static constexpr int64_t SLOT_BYTES = 16ll << 20;
+    gcta_b200_plan* p = nullptr;
+    const uint8_t* host = nullptr;
+    std::vector<int64_t> r0, r1;                        // file rows of each chunk
+    uint8_t* pinned[K][SLOTS] = {};
+    cudaStream_t streams[K] = {};
+    cudaEvent_t slot_done[K][SLOTS] = {};
+    std::vector<cudaEvent_t> chunk_done[K];             // [t][c]
+    std::atomic<int64_t> posted[K];                     // chunks whose event thread t has recorded
+    std::atomic<int> failed{0}, stop{0};
+    std::vector<std::thread> threads;
+
+    ~Stager() { finish(); }
+    void finish()
+    {
+        stop.store(1);
+        for (auto& t : threads) t.join();
+        threads.clear();
+        for (int t = 0; t < K; t++) {
+            if (streams[t]) cudaStreamSynchronize(streams[t]);
+            for (int i = 0; i < SLOTS; i++) {
+                if (slot_done[t][i]) cudaEventDestroy(slot_done[t][i]);
+                if (pinned[t][i]) cudaFreeHost(pinned[t][i]);
+                slot_done[t][i] = nullptr; pinned[t][i] = nullptr;
+            }
+            for (cudaEvent_t e : chunk_done[t]) cudaEventDestroy(e);
+            chunk_done[t].clear();
+            if (streams[t]) cudaStreamDestroy(streams[t]);
+            streams[t] = nullptr;
+        }
+        cudaGetLastError();
+    }
+    bool start(gcta_b200_plan* plan, const uint8_t* bed_host, uint8_t* d_bed, int64_t pitch, int64_t stride, const std::vector<int64_t>& rb,
+               const std::vector<int64_t>& re)
+    {
+        p = plan; host = bed_host; r0 = rb; r1 = re;
+        const int64_t nch = (int64_t)r0.size();
+        for (int t = 0; t < K; t++) {
+            posted[t].store(0);
+            if (cudaStreamCreateWithFlags(&streams[t], cudaStreamNonBlocking) != cudaSuccess) return false;
+            for (int i = 0; i < SLOTS; i++) {
+                if (cudaHostAlloc((void**)&pinned[t][i], (size_t)SLOT_BYTES, cudaHostAllocDefault) != cudaSuccess) return false;
+                memset(pinned[t][i], 0, (size_t)SLOT_BYTES);   // the pad bytes of every re-pitched row stay zero
+                if (cudaEventCreateWithFlags(&slot_done[t][i], cudaEventDisableTiming) != cudaSuccess) return false;
+            }
+            chunk_done[t].assign((size_t)nch, nullptr);
+            for (int64_t c = 0; c < nch; c++)
+                if (cudaEventCreateWithFlags(&chunk_done[t][(size_t)c], cudaEventDisableTiming) != cudaSuccess) return false;
+        }
+        const int64_t slab_rows = std::max<int64_t>(1, SLOT_BYTES / pitch);
+        const int device = plan_device();
+        for (int t = 0; t < K; t++)
+            threads.emplace_back([=]() {
+                bool ok = cudaSetDevice(device) == cudaSuccess;
+                int slot = 0;
+                bool used[SLOTS] = {};
+                for (int64_t c = 0; ok && c < nch && !stop.load(); c++) {
+                    int64_t j = 0;
+                    for (int64_t a = r0[(size_t)c]; ok && a < r1[(size_t)c]; a += slab_rows, j++) {
+                        if (j % K != t) continue;
+                        const int64_t b = std::min(r1[(size_t)c], a + slab_rows);
+                        if (used[slot]) ok = cudaEventSynchronize(slot_done[t][slot]) == cudaSuccess;   // its last copy has left the slot
+                        uint8_t* dst = pinned[t][slot];
+                        if (pitch == stride) memcpy(dst, host + a * stride, (size_t)((b - a) * stride));
+                        else
+                            for (int64_t r = a; r < b; r++) memcpy(dst + (r - a) * pitch, host + r * stride, (size_t)stride);
+                        ok = ok && cudaMemcpyAsync(d_bed + a * pitch, dst, (size_t)((b - a) * pitch), cudaMemcpyHostToDevice, streams[t]) == cudaSuccess &&
+                             cudaEventRecord(slot_done[t][slot], streams[t]) == cudaSuccess;
+                        used[slot] = true;
+                        slot = (slot + 1) % SLOTS;
+                    }
+                    ok = ok && cudaEventRecord(chunk_done[t][(size_t)c], streams[t]) == cudaSuccess;
+                    if (ok) posted[t].store(c + 1, std::memory_order_release);
+                }
+                if (!ok) failed.store(1);
+            });
+        return true;
+    }
+    int plan_device() const;
+    // queue on `s` the waits that make chunk c's rows complete
+    bool wait_chunk(int64_t c, cudaStream_t s)
+    {
+        for (int t = 0; t < K; t++) {
+            while (posted[t].load(std::memory_order_acquire) <= c) {
+                if (failed.load()) return false;
+                std::this_thread::yield();
+            }
+            if (cudaStreamWaitEvent(s, chunk_done[t][(size_t)c], 0) != cudaSuccess) return false;
+        }
+        return true;
+    }
+};
+int Stager::plan_device() const { return p->device; }
+
+}  // namespace gb
+
 // Last SNP chunk of a run whose results go straight to host buffers and in which nothing is missing: the tile list
 // is cut at raster-group boundaries into a few segments; each segment's SYRK is followed by its own finalize and an
 // asynchronous device->host copy of its rows on the copy stream, so the download of A hides behind the remaining
@@ -734,7 +844,20 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         slot_used[seq & 1] = true;
         return cudaEventRecord(p->slot_free[seq & 1], s);
     };
-    GB_CUDA(issue_upload(0));
+    // pageable host memory and a resident genotype buffer: pinned staging by helper threads (see Stager)
+    std::unique_ptr<Stager> stager;
+    if (bed_host && !p->stream_bed && !(getenv("GCTA_B200_STAGE") && atoi(getenv("GCTA_B200_STAGE")) == 0)) {
+        cudaPointerAttributes attr;
+        const bool pageable = cudaPointerGetAttributes(&attr, bed_host) != cudaSuccess || attr.type == cudaMemoryTypeUnregistered;
+        cudaGetLastError();
+        if (pageable && p->pitch * p->m_file >= (64ll << 20)) {
+            std::vector<int64_t> rb((size_t)nch_up), re((size_t)nch_up);
+            for (int64_t c = 0; c < nch_up; c++) chunk_rows(c, rb[(size_t)c], re[(size_t)c]);
+            stager.reset(new Stager());
+            if (!stager->start(p, bed_host, p->d_bed, p->pitch, p->stride, rb, re)) stager.reset();   // fall back to the driver's staging
+        }
+    }
+    if (!stager) GB_CUDA(issue_upload(0));
     // Two streams: `sd` standardises chunk c+1 (K1, K1d - HBM / ALU work) while `st` runs the SYRK of
     // chunk c on the tensor cores; two Z buffers alternate.  Ordering is by events only.
     // Measured on cfg3 (profiles/README.md): co-running the decode with the SYRK steals issue slots and power
@@ -776,7 +899,9 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
         void* Z = (p->overlap && p->d_Zbuf[1]) ? p->d_Zbuf[c & 1] : p->d_Zbuf[0];
         if (c >= 2) GB_CUDA(cudaStreamWaitEvent(sd, EV(c - 2, 3), 0));   // the SYRK that last read this Z buffer
-        if (bed_host) GB_CUDA(cudaStreamWaitEvent(sd, up[c], 0));        // this chunk's packed rows have landed
+        if (stager) {
+            if (!stager->wait_chunk(c, sd)) return set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: plan_run: staging the packed genotypes through pinned memory failed.");
+        } else if (bed_host) GB_CUDA(cudaStreamWaitEvent(sd, up[c], 0));        // this chunk's packed rows have landed
         if (!bed_host && c < (int64_t)p->chunk_ready.size() && p->chunk_ready[c])   // ... or were delivered by the caller
             GB_CUDA(cudaStreamWaitEvent(sd, p->chunk_ready[c], 0));                  // (e.g. an NVLink all-gather per chunk)
         if (!bed_host && p->chunk_hook && p->chunk_hook(p->chunk_hook_ctx, c, sd) != 0)
@@ -829,8 +954,9 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         if (rc) return rc;
         GB_CUDA(cudaEventRecord(EV(c, 3), st));
         launches += 3;
-        GB_CUDA(issue_upload(c + 1));
+        if (!stager) GB_CUDA(issue_upload(c + 1));
     }
+    if (stager) stager->finish();
     unsigned long long tm = 0;
     GB_CUDA(cudaMemcpyAsync(&tm, p->d_total_missing, 8, cudaMemcpyDeviceToHost, st));
     GB_CUDA(cudaStreamSynchronize(st));

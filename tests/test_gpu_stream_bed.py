@@ -98,3 +98,26 @@ def test_config5_shape_streamed_through_a_4_gib_allowance(monkeypatch):
     assert np.array_equal(A0[off], A1[off])
     assert np.abs(A0[~off].astype(np.float64) - A1[~off]).max() <= 1e-7
     assert abs(A1[~off].astype(np.float64).mean() - 1.0) < 1e-3
+
+
+def test_pageable_host_genotypes_go_through_pinned_staging(monkeypatch):
+    """a pageable .bed payload of 150 MB: the one-shot call stages it through pinned slots with helper threads
+    (GCTA_B200_STAGE=0: the driver's own staging); same result either way, with an include list and without"""
+    n, m, seed = 6000, 100_000, 321
+    bed = np.empty((m, (n + 3) // 4), dtype=np.uint8)           # numpy memory is pageable
+    with abi.Plan(n, m) as p:
+        p.synth(seed, synth.snp_thresholds(seed, m, miss_rate=0.01))
+        p.download_bed(bed)
+    inc = np.sort(np.random.default_rng(1).choice(m, 60_000, replace=False)).astype(np.int32)
+    for include in (None, inc):
+        monkeypatch.setenv("GCTA_B200_STAGE", "0")
+        A0, N0, mu0, _ = abi.make_grm(bed, n, m, include=include)
+        monkeypatch.delenv("GCTA_B200_STAGE")
+        A1, N1, mu1, _ = abi.make_grm(bed, n, m, include=include)
+        _same(A0, N0, mu0, A1, N1, mu1, n)
+    # and against the oracle on a sub-block (the last run had the include list)
+    sub = np.arange(0, n, 40).astype(np.int64)
+    Aref, Nref, _ = oracle.make_grm_numpy_blocked(bed[inc], n, keep=sub, mu=mu1)
+    ii, jj = np.tril_indices(len(sub))
+    idx = sub[ii] * (sub[ii] + 1) // 2 + sub[jj]
+    assert np.array_equal(N1[idx], Nref[ii, jj]) and np.abs(A1[idx].astype(np.float64) - Aref[ii, jj]).max() <= 1e-3
