@@ -168,6 +168,11 @@ struct gcta_b200_plan {
     uint8_t* d_ring[2] = {nullptr, nullptr};
     int64_t ring_rows = 0;
     cudaEvent_t slot_free[2] = {nullptr, nullptr};   // the last kernel that reads ring slot j has finished
+    // pinned bounce slots of the helper threads that move pageable host buffers (Stager: genotypes in, Drainer: results out)
+    static constexpr int HELPERS = 6, HSLOTS = 2;
+    static constexpr int64_t HSLOT_BYTES = 16ll << 20;
+    uint8_t* h_up[HELPERS][HSLOTS] = {};
+    uint8_t* h_down[HELPERS][HSLOTS] = {};
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
     int32_t *d_keep = nullptr, *d_include = nullptr, *d_cnt = nullptr, *d_sum = nullptr, *d_nii = nullptr, *d_tiles = nullptr;
     int32_t *d_Ntiles = nullptr, *d_N_lower = nullptr, *d_pairs = nullptr;   // d_pairs: CTA-pair work list of the cta_group::2 SYRK
@@ -218,6 +223,11 @@ extern "C" void gcta_b200_plan_destroy(gcta_b200_plan* p)
     for (cudaEvent_t e : p->upload_events) cudaEventDestroy(e);
     for (int j = 0; j < 2; j++)
         if (p->slot_free[j]) cudaEventDestroy(p->slot_free[j]);
+    for (int t = 0; t < gcta_b200_plan::HELPERS; t++)
+        for (int i = 0; i < gcta_b200_plan::HSLOTS; i++) {
+            if (p->h_up[t][i]) cudaFreeHost(p->h_up[t][i]);
+            if (p->h_down[t][i]) cudaFreeHost(p->h_down[t][i]);
+        }
     delete p;
 }
 
@@ -597,12 +607,12 @@ extern "C" int gcta_b200_plan_synth(gcta_b200_plan* p, uint64_t seed, const uint
 namespace gb {
 
 struct Stager {
-    static constexpr int K = 6, SLOTS = 2;
-    static constexpr int64_t SLOT_BYTES = 16ll << 20;
+    static constexpr int K = gcta_b200_plan::HELPERS, SLOTS = gcta_b200_plan::HSLOTS;
+    static constexpr int64_t SLOT_BYTES = gcta_b200_plan::HSLOT_BYTES;
     gcta_b200_plan* p = nullptr;
     const uint8_t* host = nullptr;
     std::vector<int64_t> r0, r1;                        // file rows of each chunk
-    uint8_t* pinned[K][SLOTS] = {};
+    uint8_t* pinned[K][SLOTS] = {};                     // the plan's h_up slots (allocated on first use, freed with the plan)
     cudaStream_t streams[K] = {};
     cudaEvent_t slot_done[K][SLOTS] = {};
     std::vector<cudaEvent_t> chunk_done[K];             // [t][c]
@@ -620,8 +630,7 @@ struct Stager {
             if (streams[t]) cudaStreamSynchronize(streams[t]);
             for (int i = 0; i < SLOTS; i++) {
                 if (slot_done[t][i]) cudaEventDestroy(slot_done[t][i]);
-                if (pinned[t][i]) cudaFreeHost(pinned[t][i]);
-                slot_done[t][i] = nullptr; pinned[t][i] = nullptr;
+                slot_done[t][i] = nullptr;
             }
             for (cudaEvent_t e : chunk_done[t]) cudaEventDestroy(e);
             chunk_done[t].clear();
@@ -639,8 +648,11 @@ struct Stager {
             posted[t].store(0);
             if (cudaStreamCreateWithFlags(&streams[t], cudaStreamNonBlocking) != cudaSuccess) return false;
             for (int i = 0; i < SLOTS; i++) {
-                if (cudaHostAlloc((void**)&pinned[t][i], (size_t)SLOT_BYTES, cudaHostAllocDefault) != cudaSuccess) return false;
-                memset(pinned[t][i], 0, (size_t)SLOT_BYTES);   // the pad bytes of every re-pitched row stay zero
+                if (!plan->h_up[t][i]) {
+                    if (cudaHostAlloc((void**)&plan->h_up[t][i], (size_t)SLOT_BYTES, cudaHostAllocDefault) != cudaSuccess) return false;
+                    memset(plan->h_up[t][i], 0, (size_t)SLOT_BYTES);   // the pad bytes of every re-pitched row stay zero
+                }
+                pinned[t][i] = plan->h_up[t][i];
                 if (cudaEventCreateWithFlags(&slot_done[t][i], cudaEventDisableTiming) != cudaSuccess) return false;
             }
             chunk_done[t].assign((size_t)nch, nullptr);
@@ -691,6 +703,79 @@ struct Stager {
     }
 };
 int Stager::plan_device() const { return p->device; }
+
+}  // namespace gb
+
+// ------------------------------------------------------------------------------------------------
+// Pageable host results.  A device->host copy into pageable memory is staged by the driver on the calling thread at a
+// few GB/s - slower still when the pages have never been touched (a fresh `new float[...]`), which is the usual case
+// for the 5 GB of A at the headline size (measured: 1.2 s, against 1.75 s for the whole compute).  The Drainer moves a
+// list of (device range -> host range, optional "ready" event) pieces with the same helper-thread scheme as the Stager:
+// each thread copies its slabs into its own pinned slots on its own stream and memcpy's them out, so bus transfers,
+// page faults and memcpy run in parallel.
+// ------------------------------------------------------------------------------------------------
+namespace gb {
+
+struct DrainPiece { void* dst; const void* src; int64_t bytes; cudaEvent_t ready; };
+
+static bool host_is_pageable(const void* ptr)
+{
+    cudaPointerAttributes attr;
+    const bool pg = cudaPointerGetAttributes(&attr, ptr) != cudaSuccess || attr.type == cudaMemoryTypeUnregistered;
+    cudaGetLastError();
+    return pg;
+}
+
+// blocks until every piece is in host memory; false on a CUDA error
+static bool drain_to_pageable(gcta_b200_plan* p, const std::vector<DrainPiece>& pieces)
+{
+    constexpr int K = gcta_b200_plan::HELPERS, SLOTS = gcta_b200_plan::HSLOTS;
+    constexpr int64_t SLOT = gcta_b200_plan::HSLOT_BYTES;
+    for (int t = 0; t < K; t++)
+        for (int i = 0; i < SLOTS; i++)
+            if (!p->h_down[t][i] && cudaHostAlloc((void**)&p->h_down[t][i], (size_t)SLOT, cudaHostAllocDefault) != cudaSuccess) {
+                cudaGetLastError();
+                return false;
+            }
+    struct Slab { char* dst; const char* src; int64_t bytes; cudaEvent_t ready; };
+    std::vector<Slab> slabs;
+    for (const DrainPiece& pc : pieces)
+        for (int64_t o = 0; o < pc.bytes; o += SLOT)
+            slabs.push_back({(char*)pc.dst + o, (const char*)pc.src + o, std::min(SLOT, pc.bytes - o), pc.ready});
+    std::atomic<int> failed{0};
+    const int device = p->device;
+    std::vector<std::thread> th;
+    for (int t = 0; t < K; t++)
+        th.emplace_back([&, t]() {
+            cudaStream_t s = nullptr;
+            cudaEvent_t ev[SLOTS] = {};
+            bool ok = cudaSetDevice(device) == cudaSuccess && cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) == cudaSuccess;
+            for (int i = 0; ok && i < SLOTS; i++) ok = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) == cudaSuccess;
+            // slab j of this thread sits in slot j % SLOTS: queue the copy of slab j+1, then move slab j out
+            std::vector<size_t> mine;
+            for (size_t j = (size_t)t; j < slabs.size(); j += K) mine.push_back(j);
+            auto queue = [&](size_t q) {
+                const Slab& sl = slabs[mine[q]];
+                if (sl.ready) ok = ok && cudaStreamWaitEvent(s, sl.ready, 0) == cudaSuccess;
+                ok = ok && cudaMemcpyAsync(p->h_down[t][q % SLOTS], sl.src, (size_t)sl.bytes, cudaMemcpyDeviceToHost, s) == cudaSuccess &&
+                     cudaEventRecord(ev[q % SLOTS], s) == cudaSuccess;
+            };
+            if (ok && !mine.empty()) queue(0);
+            for (size_t q = 0; ok && q < mine.size(); q++) {
+                if (q + 1 < mine.size()) queue(q + 1);
+                ok = ok && cudaEventSynchronize(ev[q % SLOTS]) == cudaSuccess;
+                if (ok) memcpy(slabs[mine[q]].dst, p->h_down[t][q % SLOTS], (size_t)slabs[mine[q]].bytes);
+            }
+            if (s) cudaStreamSynchronize(s);
+            for (int i = 0; i < SLOTS; i++)
+                if (ev[i]) cudaEventDestroy(ev[i]);
+            if (s) cudaStreamDestroy(s);
+            if (!ok) failed.store(1);
+        });
+    for (auto& t : th) t.join();
+    cudaGetLastError();
+    return failed.load() == 0;
+}
 
 }  // namespace gb
 
@@ -761,11 +846,19 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
         for (int t = 0; t < nt; t++)
             fill.emplace_back([=]() { std::fill(dst + cnt * t / nt, dst + cnt * (t + 1) / nt, mval); });
     }
-    // The copies are issued only now, after every kernel of the chunk is in the queue: into pinned memory they are
-    // asynchronous anyway; into pageable memory each call blocks this thread until its segment has been computed and
-    // copied (the driver stages it), while the GPU already works on the next segments - so the download overlaps the
-    // tensor work for either kind of caller buffer.
-    for (size_t i = 0; i < segs.size() && i < evs.size() && !rc; i++) {
+    // The copies are issued only now, after every kernel of the chunk is in the queue, so the GPU keeps computing the later
+    // segments whatever the host does: into pinned memory they are asynchronous copies on the copy stream; pageable memory
+    // is served by the Drainer's helper threads (or, for small bands, by the driver's own staging, which blocks this thread
+    // piece by piece).
+    const bool drain = !rc && p->band_count * 4 >= (64ll << 20) && host_is_pageable(out->A_lower) &&
+                       !(getenv("GCTA_B200_STAGE") && atoi(getenv("GCTA_B200_STAGE")) == 0);
+    if (drain) {
+        std::vector<DrainPiece> pieces;
+        for (size_t i = 0; i < segs.size() && i < evs.size(); i++)
+            pieces.push_back({out->A_lower + segs[i].base, p->d_A_lower + (segs[i].base - band_base), segs[i].cnt * 4, evs[i]});
+        if (!drain_to_pageable(p, pieces)) rc = set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: CUDA call failed in the pipelined download (pinned staging).");
+    }
+    for (size_t i = 0; !drain && i < segs.size() && i < evs.size() && !rc; i++) {
         cudaError_t e = cudaStreamWaitEvent(p->stream_copy, evs[i], 0);
         if (e == cudaSuccess)
             e = cudaMemcpyAsync(out->A_lower + segs[i].base, p->d_A_lower + (segs[i].base - band_base), (size_t)segs[i].cnt * 4, cudaMemcpyDeviceToHost, p->stream_copy);
@@ -1123,9 +1216,20 @@ extern "C" int gcta_b200_plan_download(gcta_b200_plan* p, gcta_b200_out* out, ch
     const int64_t base = p->row_begin * (p->row_begin + 1) / 2;
     // plan_run_to_host already delivered A (and N) behind the last SYRK - into these very buffers?
     const bool have = p->downloaded && p->streamed_A == out->A_lower && (!out->N_lower || p->streamed_N == out->N_lower);
-    if (!have) GB_CUDA(cudaMemcpyAsync(out->A_lower + base, p->d_A_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
-    if (out->N_lower && p->total_missing > 0)
-        GB_CUDA(cudaMemcpyAsync(out->N_lower + base, p->d_N_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
+    // large pageable destinations go through the Drainer's helper threads (everything on p->stream has completed: plan_run
+    // synchronises before it returns)
+    const bool big = p->band_count * 4 >= (64ll << 20) && !(getenv("GCTA_B200_STAGE") && atoi(getenv("GCTA_B200_STAGE")) == 0);
+    std::vector<DrainPiece> pieces;
+    if (!have) {
+        if (big && host_is_pageable(out->A_lower)) pieces.push_back({out->A_lower + base, p->d_A_lower, p->band_count * 4, nullptr});
+        else GB_CUDA(cudaMemcpyAsync(out->A_lower + base, p->d_A_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
+    }
+    if (out->N_lower && p->total_missing > 0) {
+        if (big && host_is_pageable(out->N_lower)) pieces.push_back({out->N_lower + base, p->d_N_lower, p->band_count * 4, nullptr});
+        else GB_CUDA(cudaMemcpyAsync(out->N_lower + base, p->d_N_lower, (size_t)p->band_count * 4, cudaMemcpyDeviceToHost, p->stream));
+    }
+    if (!pieces.empty() && !drain_to_pageable(p, pieces))
+        return set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: CUDA call failed in plan_download (pinned staging).");
     if (out->mu_out) GB_CUDA(cudaMemcpyAsync(out->mu_out, p->d_mu, (size_t)p->m * 8, cudaMemcpyDeviceToHost, p->stream));
     if (out->N_lower && p->total_missing == 0 && !have) {
         // nothing missing: N_ij == m for every pair (what grm.cpp:291 yields); fill on the host while the copies run

@@ -6,6 +6,7 @@
 // option.cpp:42-50).  Flags of GCTA analyses outside the path are rejected like unknown flags.
 // Extra flags (not in the reference): --gpus N, --operand fp16|bf16, --chunk-snps K.
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <ctime>
 #include <iostream>
@@ -157,7 +158,12 @@ static void option(int argc, char* argv_in[])
         if (!extract_snp_name.empty()) g.extract_single_snp(extract_snp_name);
         if (!exclude_snp_name.empty()) g.exclude_single_snp(exclude_snp_name);
         if (!update_refA_file.empty()) g.update_ref_A(update_refA_file);
-        g.read_bedfile(bfile + ".bed");
+        {
+            const auto t_r0 = std::chrono::steady_clock::now();
+            g.read_bedfile(bfile + ".bed");
+            if (getenv("GCTA_B200_TIMING"))   // phase split for tools/cli_cfg3.sh; the .fam / .bim parsing came before
+                std::cerr << "{\"read_bed_s\": " << std::chrono::duration<double>(std::chrono::steady_clock::now() - t_r0).count() << "}" << std::endl;
+        }
         if (!update_freq_file.empty()) g.update_freq(update_freq_file);
         if (maf > 0) g.filter_snp_maf(maf);
         if (max_maf > 0.0) g.filter_snp_max_maf(max_maf);

@@ -100,13 +100,15 @@ def test_config5_shape_streamed_through_a_4_gib_allowance(monkeypatch):
     assert abs(A1[~off].astype(np.float64).mean() - 1.0) < 1e-3
 
 
-def test_pageable_host_genotypes_go_through_pinned_staging(monkeypatch):
-    """a pageable .bed payload of 150 MB: the one-shot call stages it through pinned slots with helper threads
-    (GCTA_B200_STAGE=0: the driver's own staging); same result either way, with an include list and without"""
+@pytest.mark.parametrize("miss", [0.01, 0.0])
+def test_pageable_host_buffers_go_through_pinned_staging(monkeypatch, miss):
+    """pageable buffers of 70 .. 150 MB (numpy memory): the one-shot call moves the genotypes in and the results out through
+    pinned slots with helper threads (GCTA_B200_STAGE=0: the driver's own staging); same result either way.
+    miss = 0 takes the pipelined last chunk (segments drained behind the SYRK), miss > 0 the plain download of A and N."""
     n, m, seed = 6000, 100_000, 321
-    bed = np.empty((m, (n + 3) // 4), dtype=np.uint8)           # numpy memory is pageable
+    bed = np.empty((m, (n + 3) // 4), dtype=np.uint8)
     with abi.Plan(n, m) as p:
-        p.synth(seed, synth.snp_thresholds(seed, m, miss_rate=0.01))
+        p.synth(seed, synth.snp_thresholds(seed, m, miss_rate=miss))
         p.download_bed(bed)
     inc = np.sort(np.random.default_rng(1).choice(m, 60_000, replace=False)).astype(np.int32)
     for include in (None, inc):
