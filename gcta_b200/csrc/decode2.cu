@@ -119,6 +119,8 @@ struct FusedParams {
     double* diag;
     int32_t* nii;
     int64_t diag_f0, diag_f1;   // file individuals whose diagonal is wanted
+    uint8_t* OK;                // optional: 8-bit E4M3 non-missing indicators [ok_pad][ldz] for the counting pass
+    int64_t ok_pad;             // kc rounded up to 128 (the 8-bit K block of the SYRK kernel)
     int64_t rows_per_cta;
 };
 
@@ -127,52 +129,24 @@ __device__ __forceinline__ uint32_t f2h16(float z, int bf16)
     return bf16 ? (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(z)) : (uint32_t)__half_as_ushort(__float2half_rn(z));
 }
 
+// no "memory" clobber on the stores: nothing in the kernel reads Z or OK, and the table look-ups of the next row may move above them
 __device__ __forceinline__ void st_z256(uint16_t* dst, const uint32_t (&o)[8])
 {
     asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]),
-                 "r"(o[5]), "r"(o[6]), "r"(o[7]));   // no "memory" clobber: nothing in the kernel reads Z, and the table look-ups of the next row may move above it
+                 "r"(o[5]), "r"(o[6]), "r"(o[7]));
 }
 
-// one packed word = 16 genotypes of one SNP: look the eight nibbles up, store, accumulate.
-// `row_addr` is the shared-memory address of the SNP's 256-byte table row (256-byte aligned, so the
-// nibble's byte offset is OR-ed in by the same LOP3 that masks it): z pairs at [8 nib], squares at [128 + 8 nib].
-template <bool DIAG>
-__device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_t* zdst, int nvalid, float (&acc)[16])
-{
-    uint32_t o[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-        // entries are 8 bytes apart: offset ((w >> 4j) & 15) * 8
-        const uint32_t a = (j == 0 ? (w << 3) & 0x78u : (w >> (4 * j - 3)) & 0x78u) | row_addr;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(o[j]) : "r"(a));
-        if (DIAG) {
-            float qx, qy;
-            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2+128];" : "=f"(qx), "=f"(qy) : "r"(a));
-            acc[2 * j] += qx;
-            acc[2 * j + 1] += qy;
-        }
-    }
-    if (nvalid >= 16) st_z256(zdst, o);
-    else {   // the one column that straddles n_out, and the zero padding behind it
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            if (2 * j >= nvalid) o[j] = 0;
-            else if (2 * j + 1 >= nvalid) o[j] &= 0xFFFFu;
-        }
-        reinterpret_cast<uint4*>(zdst)[0] = make_uint4(o[0], o[1], o[2], o[3]);
-        reinterpret_cast<uint4*>(zdst)[1] = make_uint4(o[4], o[5], o[6], o[7]);
-    }
-}
-
-// The same with fewer instructions per genotype: the eight nibble offsets come out of two masked copies of the word by
-// PRMT, which also merges them into the (256-byte aligned) table address, and the squares are added two at a time by
-// the packed FADD2 (acc2[j] = sums of individuals 2j and 2j+1 as a float pair).
-template <bool DIAG>
-__device__ __forceinline__ void emit_word2(uint32_t w, uint32_t row_addr, uint16_t* zdst, int nvalid, unsigned long long (&acc2)[8])
+// One packed word = 16 genotypes of one SNP.  `row_addr` is the shared-memory address of the SNP's 256-byte table row
+// (256-byte aligned): 16 nibble entries of 8 bytes - the two 16-bit z values of the nibble's two individuals, then their
+// two E4M3 non-missing indicators - followed from byte 128 by 16 float2 entries with the squares of the z values.
+// The eight nibble offsets come out of two masked copies of the word by PRMT, which also merges them into the table
+// address; the squares are added two at a time by the packed FADD2 (acc2[j] = sums of individuals 2j and 2j+1).
+template <bool DIAG, bool OKP>
+__device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_t* zdst, uint8_t* okdst, int nvalid, unsigned long long (&acc2)[8])
 {
     const uint32_t ev = (w << 3) & 0x78787878u;   // 8 x nibbles 0, 2, 4, 6 in bytes 0..3
     const uint32_t od = (w >> 1) & 0x78787878u;   // 8 x nibbles 1, 3, 5, 7
-    uint32_t o[8];
+    uint32_t o[8], k[8];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         uint32_t a;
@@ -182,15 +156,23 @@ __device__ __forceinline__ void emit_word2(uint32_t w, uint32_t row_addr, uint16
         else if ((j >> 1) == 1) asm("prmt.b32 %0, %1, %2, 0x7651;" : "=r"(a) : "r"(src), "r"(row_addr));
         else if ((j >> 1) == 2) asm("prmt.b32 %0, %1, %2, 0x7652;" : "=r"(a) : "r"(src), "r"(row_addr));
         else asm("prmt.b32 %0, %1, %2, 0x7653;" : "=r"(a) : "r"(src), "r"(row_addr));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(o[j]) : "r"(a));
+        if (OKP) asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(o[j]), "=r"(k[j]) : "r"(a));
+        else asm volatile("ld.shared.u32 %0, [%1];" : "=r"(o[j]) : "r"(a));
         if (DIAG) {
             unsigned long long q;
             asm volatile("ld.shared.b64 %0, [%1+128];" : "=l"(q) : "r"(a));
             asm("add.rn.f32x2 %0, %0, %1;" : "+l"(acc2[j]) : "l"(q));
         }
     }
-    if (nvalid >= 16) st_z256(zdst, o);
-    else {
+    uint32_t ok4[4];
+    if (OKP) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) ok4[j] = (k[2 * j] & 0xFFFFu) | (k[2 * j + 1] << 16);
+    }
+    if (nvalid >= 16) {
+        st_z256(zdst, o);
+        if (OKP) asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(okdst), "r"(ok4[0]), "r"(ok4[1]), "r"(ok4[2]), "r"(ok4[3]));
+    } else {   // the one column that straddles n_out, and the zero padding behind it
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             if (2 * j >= nvalid) o[j] = 0;
@@ -198,20 +180,25 @@ __device__ __forceinline__ void emit_word2(uint32_t w, uint32_t row_addr, uint16
         }
         reinterpret_cast<uint4*>(zdst)[0] = make_uint4(o[0], o[1], o[2], o[3]);
         reinterpret_cast<uint4*>(zdst)[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        if (OKP) {
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    if (4 * j + e >= nvalid) ok4[j] &= ~(0xFFu << (8 * e));
+            *reinterpret_cast<uint4*>(okdst) = make_uint4(ok4[0], ok4[1], ok4[2], ok4[3]);
+        }
     }
 }
 
-template <bool DIAG, int VAR>
+template <bool DIAG, bool OKP>
 __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64_t r1, int64_t col, bool in_z, bool can_load, int nvalid,
                                          uint8_t (*tab)[F_TB][256], int64_t (*row_off)[F_TB])
 {
     const int tid = threadIdx.x;
     const int64_t i0 = col * 16;
-    float acc[16];                 // VAR 0
-    unsigned long long acc2[8];    // VAR 1: float pairs
+    unsigned long long acc2[8];    // float pairs: the running sums of z^2 of individuals (2j, 2j+1)
     uint32_t m16[8];
-#pragma unroll
-    for (int e = 0; e < 16; e++) acc[e] = 0.0f;
 #pragma unroll
     for (int g = 0; g < 8; g++) { m16[g] = 0; acc2[g] = 0ull; }
     const bool tdiag = DIAG && in_z && i0 < p.diag_f1 && i0 + 16 > p.diag_f0;
@@ -223,7 +210,9 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
             const int row = idx >> 4, nib = idx & 15;
             const int64_t k = p.k0 + rbase + row;
             const float za = __ldg(p.zlut + k * 8 + (nib & 3)), zb = __ldg(p.zlut + k * 8 + (nib >> 2));
-            *reinterpret_cast<uint32_t*>(&tab[buf][row][8 * nib]) = f2h16(za, p.bf16) | (f2h16(zb, p.bf16) << 16);
+            // E4M3 1.0 = 0x38 for a non-missing genotype (code != 01b), 0 for a missing one
+            const uint32_t okp = ((nib & 3) != 1 ? 0x38u : 0u) | ((nib >> 2) != 1 ? 0x3800u : 0u);
+            *reinterpret_cast<uint2*>(&tab[buf][row][8 * nib]) = make_uint2(f2h16(za, p.bf16) | (f2h16(zb, p.bf16) << 16), okp);
             if (DIAG) *reinterpret_cast<float2*>(&tab[buf][row][128 + 8 * nib]) = make_float2(za * za, zb * zb);   // exact products rounded once to float
         }
         for (int row = tid; row < nr; row += F_THREADS) {
@@ -240,14 +229,12 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
                     // m16[g]: low half = individual g, high half = individual 8+g; m16[4+g]: individuals 4+g, 12+g
                     const int g = e & 3, hi = (e >> 2) & 1, top = e >> 3;
                     const int miss = (int)((m16[g + 4 * hi] >> (16 * top)) & 0xFFFFu);
-                    const float sum = VAR == 0 ? acc[e] : __uint_as_float((uint32_t)(acc2[e >> 1] >> (32 * (e & 1))));
+                    const float sum = __uint_as_float((uint32_t)(acc2[e >> 1] >> (32 * (e & 1))));
                     atomicAdd(p.diag + f, (double)sum);
                     atomicAdd(p.nii + f, rows_acc - miss);
                 }
             }
         }
-#pragma unroll
-        for (int e = 0; e < 16; e++) acc[e] = 0.0f;
 #pragma unroll
         for (int g = 0; g < 8; g++) { m16[g] = 0; acc2[g] = 0ull; }
         rows_acc = 0;
@@ -271,6 +258,7 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
         const int nr = (int)min((int64_t)F_TB, r1 - rbase);
         if (in_z) {
             uint16_t* zrow = p.Z + rbase * p.ldz + i0;
+            uint8_t* okrow = OKP ? p.OK + rbase * p.ldz + i0 : nullptr;
             const uint32_t tab_addr = smem_u32(&tab[buf][0][0]);
             uint32_t c8[4] = {0, 0, 0, 0};
             int row = 0;
@@ -289,8 +277,8 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
                     uint32_t c2 = 0;
 #pragma unroll
                     for (int u = 3 * h; u < 3 * h + 3; u++) {
-                        if (VAR == 0) emit_word<DIAG>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz, nvalid, acc);
-                        else emit_word2<DIAG>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz, nvalid, acc2);
+                        emit_word<DIAG, OKP>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz,
+                                             OKP ? okrow + (int64_t)(row + u) * p.ldz : nullptr, nvalid, acc2);
                         if (DIAG) c2 += (w[u] & 0x55555555u) & ~(w[u] >> 1);   // missing = code 01b, one count per 2-bit lane
                     }
                     if (DIAG) {
@@ -302,8 +290,7 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
             for (; row < nr; row++) {
                 const int64_t off = p.include ? row_off[buf][row] : (p.k0 + rbase + row) * p.pitch;
                 const uint32_t w = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + off)) : 0u;
-                if (VAR == 0) emit_word<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc);
-                else emit_word2<DIAG>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, nvalid, acc2);
+                emit_word<DIAG, OKP>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, OKP ? okrow + (int64_t)row * p.ldz : nullptr, nvalid, acc2);
                 if (DIAG) {
                     const uint32_t c2 = (w & 0x55555555u) & ~(w >> 1);
 #pragma unroll
@@ -326,13 +313,10 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
     if (DIAG) flush();
 }
 
-template <int MIN_CTAS, int VAR>
-__global__ void __launch_bounds__(F_THREADS, MIN_CTAS) decode_emit_diag_kernel(const FusedParams p)
+__global__ void __launch_bounds__(F_THREADS, 4) decode_emit_diag_kernel(const FusedParams p)
 {
-    // per SNP row 256 bytes: 16 nibble entries of 8 bytes holding the two 16-bit z values of the nibble's two individuals
-    // (4 bytes used; 16 entries x 8 bytes = every other bank, so a warp's look-ups never conflict), then 16 float2 squares
-    __shared__ __align__(256) uint8_t tab[2][F_TB][256];
-    __shared__ int64_t row_off[2][F_TB];                 // byte offset of each SNP row
+    __shared__ __align__(256) uint8_t tab[2][F_TB][256];   // per SNP row 256 bytes, see emit_word
+    __shared__ int64_t row_off[2][F_TB];                   // byte offset of each SNP row
     const int64_t col = (int64_t)blockIdx.x * F_THREADS + threadIdx.x;   // packed 32-bit column = individuals [16 col, 16 col + 16)
     const int64_t i0 = col * 16;
     const bool in_z = i0 < p.ldz;                        // threads behind ldz only help with the tables and the barriers
@@ -343,16 +327,23 @@ __global__ void __launch_bounds__(F_THREADS, MIN_CTAS) decode_emit_diag_kernel(c
     const int64_t s0 = (int64_t)blockIdx.x * F_SLAB;
     const bool cta_diag = p.diag != nullptr && s0 < p.diag_f1 && s0 + F_SLAB > p.diag_f0;
     if (r0 < r1) {
-        if (cta_diag) run_rows<true, VAR>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
-        else run_rows<false, VAR>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+        if (p.OK) {
+            if (cta_diag) run_rows<true, true>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+            else run_rows<false, true>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+        } else {
+            if (cta_diag) run_rows<true, false>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+            else run_rows<false, false>(p, r0, r1, col, in_z, can_load, nvalid, tab, row_off);
+        }
     }
-    // padding rows of the last 64-SNP block: zero
+    // padding rows of the last K block: zero
     if (blockIdx.y == gridDim.y - 1 && in_z) {
         for (int64_t kk = p.kc; kk < p.kc_pad; kk++) {
             uint4* d = reinterpret_cast<uint4*>(p.Z + kk * p.ldz + i0);
             d[0] = make_uint4(0, 0, 0, 0);
             d[1] = make_uint4(0, 0, 0, 0);
         }
+        if (p.OK)
+            for (int64_t kk = p.kc; kk < p.ok_pad; kk++) *reinterpret_cast<uint4*>(p.OK + kk * p.ldz + i0) = make_uint4(0, 0, 0, 0);
     }
 }
 
@@ -373,7 +364,9 @@ extern "C" int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t 
     int dev = 0, sms = 0;
     GB_CUDA(cudaGetDevice(&dev));
     GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int64_t ctas = std::min<int64_t>((kc + 7) / 8, (int64_t)sms * 8);   // 8 CTAs of 256 threads fill an SM
+    int per_sm = 0;   // resident CTAs per SM (6 at 40 registers): the grid is exactly one wave
+    GB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, snp_stats_kernel, 256, 0));
+    const int64_t ctas = std::min<int64_t>((kc + 7) / 8, (int64_t)sms * std::max(per_sm, 1));
     snp_stats_kernel<<<(unsigned)ctas, 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, n, d_keepmask, d_include, k0, kc, d_mu_in,
                                                                                   alg == 0, d_mu, d_cnt, d_sum, d_zlut, d_total_missing);
     GB_CUDA(cudaGetLastError());
@@ -383,7 +376,7 @@ extern "C" int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t 
 // K1f through the C ABI (device pointers).  Every file individual is kept (n == n_file), autosomes, one 16-bit plane.
 extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_include,
                                           int64_t k0, int64_t kc, const float* d_zlut, int32_t operand, void* d_Z, int64_t ldz,
-                                          double* d_diag, int32_t* d_nii, int64_t diag_f0, int64_t diag_f1,
+                                          double* d_diag, int32_t* d_nii, int64_t diag_f0, int64_t diag_f1, void* d_OK,
                                           void* stream, char* err, size_t errcap)
 {
     using namespace gb;
@@ -392,7 +385,7 @@ extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, i
     GB_ARG(pitch > 0 && pitch % 16 == 0 && ((uintptr_t)d_bed & 15) == 0, "decode_emit_diag: bed pitch and pointer must be multiples of 16 bytes");
     GB_ARG(pitch * 4 >= n_file && n_file > 0, "decode_emit_diag: pitch too small for n_file");
     GB_ARG(ldz > 0 && ldz % 256 == 0, "decode_emit_diag: ldz must be a positive multiple of 256");
-    GB_ARG(((uintptr_t)d_Z & 31) == 0, "decode_emit_diag: Z must be 32-byte aligned");
+    GB_ARG(((uintptr_t)d_Z & 31) == 0 && ((uintptr_t)d_OK & 15) == 0, "decode_emit_diag: Z must be 32-byte aligned, the indicator plane 16-byte aligned");
     GB_ARG(kc > 0 && k0 >= 0, "decode_emit_diag: empty SNP range");
     GB_ARG(operand == GCTA_B200_FP16 || operand == GCTA_B200_BF16, "decode_emit_diag: operand must be FP16 or BF16");
     FusedParams p;
@@ -400,6 +393,7 @@ extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, i
     p.zlut = d_zlut; p.bf16 = operand == GCTA_B200_BF16; p.Z = (uint16_t*)d_Z; p.ldz = ldz;
     p.n_out = n_file < ldz ? n_file : ldz;   // a Z narrower than n keeps only the first ldz individuals (row bands need no more)
     p.diag = d_diag; p.nii = d_nii;
+    p.OK = (uint8_t*)d_OK; p.ok_pad = (kc + 127) / 128 * 128;
     p.diag_f0 = d_diag ? std::max<int64_t>(0, diag_f0) : 0;
     p.diag_f1 = d_diag ? std::min<int64_t>(n_file, diag_f1) : 0;
     int dev = 0, sms = 0;
@@ -407,11 +401,10 @@ extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, i
     GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int64_t slabs = (ldz / 16 + F_THREADS - 1) / F_THREADS;
     // Rows per CTA.  All CTAs do the same work (except those of a partly filled last slab), so the launch should be a whole
-    // number of waves of the resident capacity (4 CTAs per SM; 6 with GCTA_B200_DECODE_OCC=6): groups of rows = (capacity / slabs) x waves, with about
+    // number of waves of the resident capacity (4 CTAs per SM): groups of rows = (capacity / slabs) x waves, with about
     // 384 rows per CTA - long enough to amortise the table set-up and the final atomics, short enough for a few waves.
     const int64_t rows_env = getenv("GCTA_B200_DECODE_ROWS") ? atoll(getenv("GCTA_B200_DECODE_ROWS")) : 0;
-    const int occ = getenv("GCTA_B200_DECODE_OCC") ? atoi(getenv("GCTA_B200_DECODE_OCC")) : 4;
-    const int64_t per_wave = std::max<int64_t>(1, (int64_t)sms * (occ >= 6 ? 6 : 4) / slabs);
+    const int64_t per_wave = std::max<int64_t>(1, (int64_t)sms * 4 / slabs);
     const int64_t waves = std::max<int64_t>(1, (kc + per_wave * 384 - 1) / (per_wave * 384));
     int64_t groups = per_wave * waves;
     int64_t rows = rows_env > 0 ? rows_env : (kc + groups - 1) / groups;
@@ -420,17 +413,7 @@ extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, i
     GB_ARG(groups <= 65535, "decode_emit_diag: SNP range too long for one launch");
     p.rows_per_cta = rows;
     dim3 grid((unsigned)slabs, (unsigned)groups);
-    // resident CTAs per SM the kernel is compiled for: 4 (104 registers) by default, GCTA_B200_DECODE_OCC=6 selects the
-    // 80-register build (a few spilled bytes, half again as many warps in flight)
-    // GCTA_B200_DECODE_VAR=0: plain shift/mask addressing and scalar FADDs (kept for A/B runs)
-    const int var = getenv("GCTA_B200_DECODE_VAR") ? atoi(getenv("GCTA_B200_DECODE_VAR")) : 1;
-    if (occ >= 6) {
-        if (var == 0) decode_emit_diag_kernel<6, 0><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
-        else decode_emit_diag_kernel<6, 1><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
-    } else {
-        if (var == 0) decode_emit_diag_kernel<4, 0><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
-        else decode_emit_diag_kernel<4, 1><<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
-    }
+    decode_emit_diag_kernel<<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
     GB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -179,6 +179,7 @@ struct gcta_b200_plan {
     int64_t npairs = 0;
     double *d_mu_in = nullptr, *d_mu = nullptr, *d_diag = nullptr, *d_dk = nullptr, *d_dw = nullptr;   // d_dk, d_dw: --grm-alg 1
     float* d_Dtiles = nullptr;
+    uint8_t* d_OKbuf = nullptr;   // E4M3 non-missing indicators of one SNP chunk, written by K1f when the counts run chunk by chunk
     float *d_zlut = nullptr, *d_S = nullptr, *d_A_lower = nullptr;
     void* d_Zbuf[2] = {nullptr, nullptr};
     unsigned long long* d_total_missing = nullptr;
@@ -957,14 +958,14 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     // from the tensor loop (K2 +30 %), so by default both run on one stream; GCTA_B200_OVERLAP=1 enables it.
     cudaStream_t st = p->stream, sd = p->overlap ? p->stream2 : p->stream;
     const int64_t nchunks = p->nchunks();
-    // events: [0] start, [1] buffers cleared, then 4 per chunk (decode start/end, syrk start/end), then 2
-    const size_t need = (size_t)(4 * nchunks + 4);
+    // events: [0] start, [1] buffers cleared, then 6 per chunk (decode start/end, syrk start/end, counts start/end), then 2
+    const size_t need = (size_t)(6 * nchunks + 4);
     while (p->events.size() < need) {
         cudaEvent_t ev;
         GB_CUDA(cudaEventCreate(&ev));
         p->events.push_back(ev);
     }
-    auto EV = [&](int64_t c, int which) { return p->events[(size_t)(2 + 4 * c + which)]; };
+    auto EV = [&](int64_t c, int which) { return p->events[(size_t)(2 + 6 * c + which)]; };
     int launches = 0;
     // K2 dispatch: out (+)= Za^T Zb over the band's tiles, as single CTAs (syrk.cu) or as CTA pairs (syrk2.cu)
     auto syrk = [&](const void* Za, const void* Zb, int64_t kp, int op, void* outp, bool int_acc, cudaStream_t s) -> int {
@@ -988,6 +989,15 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     if (p->d_dw) GB_CUDA(cudaMemsetAsync(p->d_dw, 0, (size_t)p->n_file * 8, st));
     GB_CUDA(cudaEventRecord(p->events[1], st));
     GB_CUDA(cudaStreamWaitEvent(sd, p->events[1], 0));
+    // Pair counts chunk by chunk (grm.cpp:270, 291): when the first chunk already shows missing genotypes, K1f writes the
+    // E4M3 indicators of each chunk next to its Z in the same pass over the packed rows, and the counting SYRK of the chunk
+    // follows its S SYRK at once - no second decode of the file (and, for streamed genotypes, no second trip over PCIe).
+    // If missing genotypes only turn up in a later chunk, the separate indicator pass after the loop does the counting.
+    const char* nmode = getenv("GCTA_B200_N_MODE");
+    const bool inline_ok = p->fused_decode && !p->d_pairs && !p->overlap && p->ntiles > 0 && !(nmode && *nmode) &&
+                           !(getenv("GCTA_B200_COUNT_INLINE") && atoi(getenv("GCTA_B200_COUNT_INLINE")) == 0);
+    bool count_inline = false;
+    void* okbuf = nullptr;
     for (int64_t c = 0; c < nchunks; c++) {
         const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
         void* Z = (p->overlap && p->d_Zbuf[1]) ? p->d_Zbuf[c & 1] : p->d_Zbuf[0];
@@ -1005,9 +1015,24 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         if (p->fused_decode) {
             rc = gcta_b200_snp_stats(bedc, p->pitch, p->n_file, p->d_keepmask, p->n, p->d_include, k0, kc, p->d_mu_in, p->alg, p->d_mu,
                                      p->d_cnt, p->d_sum, p->d_zlut, p->d_total_missing, sd, err, errcap);
-            // Z and the band's diagonal in one pass over the packed rows
+            if (!rc && c == 0 && inline_ok) {
+                // anything missing in the first chunk?  (one small wait at the very start of the run)
+                unsigned long long tm0 = 0;
+                GB_CUDA(cudaMemcpyAsync(&tm0, p->d_total_missing, 8, cudaMemcpyDeviceToHost, sd));
+                GB_CUDA(cudaStreamSynchronize(sd));
+                if (tm0 > 0) {
+                    if (!p->d_OKbuf) rc = dev_alloc(p, &p->d_OKbuf, (size_t)round_up(p->chunk, 128) * p->ldz, err, errcap);
+                    if (!rc && !p->d_Ntiles) rc = dev_alloc(p, &p->d_Ntiles, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap);
+                    if (!rc && !p->d_N_lower) rc = dev_alloc(p, &p->d_N_lower, (size_t)p->band_count, err, errcap);
+                    if (rc) return rc;
+                    GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
+                    count_inline = true;
+                    okbuf = p->d_OKbuf;
+                }
+            }
+            // Z and the band's diagonal (and the indicators) in one pass over the packed rows
             if (!rc) rc = gcta_b200_decode_emit_diag(bedc, p->pitch, p->n_file, p->d_include, k0, kc, p->d_zlut, p->operand, Z, p->ldz,
-                                                     p->d_diag, p->d_nii, p->diag_f0, p->diag_f1, sd, err, errcap);
+                                                     p->d_diag, p->d_nii, p->diag_f0, p->diag_f1, okbuf, sd, err, errcap);
             if (rc) return rc;
         } else {
         rc = gcta_b200_bed_decode_ex(bedc, p->pitch, p->n_file, p->d_keepmask, p->d_keep, p->n, p->d_sexmale, p->d_include, k0, kc,
@@ -1047,6 +1072,13 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         if (rc) return rc;
         GB_CUDA(cudaEventRecord(EV(c, 3), st));
         launches += 3;
+        GB_CUDA(cudaEventRecord(EV(c, 4), st));
+        if (count_inline) {
+            rc = gcta_b200_count_tiles(okbuf, p->ldz, round_up(kc, 128), GCTA_B200_E4M3, p->d_tiles, p->ntiles, p->d_Ntiles, st, err, errcap);
+            if (rc) return rc;
+            launches++;
+        }
+        GB_CUDA(cudaEventRecord(EV(c, 5), st));
         if (!stager) GB_CUDA(issue_upload(c + 1));
     }
     if (stager) stager->finish();
@@ -1054,12 +1086,11 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     GB_CUDA(cudaMemcpyAsync(&tm, p->d_total_missing, 8, cudaMemcpyDeviceToHost, st));
     GB_CUDA(cudaStreamSynchronize(st));
     p->total_missing = (int64_t)tm;
-    const size_t e_pc = 2 + 4 * nchunks, e_fin = e_pc + 1;
+    const size_t e_pc = 2 + 6 * nchunks, e_fin = e_pc + 1;
     // N_ij is only needed when something is missing (otherwise N == m, which is what grm.cpp:291 yields).
     // Default: indicator matrix + the SYRK kernel in counting mode (exact, tensor rate).  GCTA_B200_N_MODE=popc
     // selects the AND+popc kernel over bit planes instead (same integers, ~8x slower; kept as the cross-check).
     const int op16 = p->operand == GCTA_B200_FP16X2 ? GCTA_B200_FP16 : p->operand;   // indicator matrices are single-plane
-    const char* nmode = getenv("GCTA_B200_N_MODE");
     const bool use_popc = nmode && strcmp(nmode, "popc") == 0;
     if (tm > 0 && !p->d_Ntiles) {
         int rc = dev_alloc(p, &p->d_Ntiles, (size_t)p->ntiles * TILE_M * TILE_N, err, errcap);
@@ -1076,7 +1107,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         cudaError_t e = release_slot(seq, st);
         return e != cudaSuccess ? e : (p->stream_bed ? issue_upload(c + 1) : cudaSuccess);
     };
-    if (tm > 0 && !use_popc) {
+    if (tm > 0 && !use_popc && !count_inline) {
         GB_CUDA(cudaMemsetAsync(p->d_Ntiles, 0, (size_t)p->ntiles * TILE_M * TILE_N * 4, st));
         const int64_t seq0 = seq_next;
         GB_CUDA(restage_begin());
@@ -1166,7 +1197,12 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         out->ms_decode += a;
         out->ms_syrk += b;
     }
-    GB_CUDA(cudaEventElapsedTime(&out->ms_paircount, EV(nchunks - 1, 3), p->events[e_pc]));
+    GB_CUDA(cudaEventElapsedTime(&out->ms_paircount, EV(nchunks - 1, 5), p->events[e_pc]));
+    for (int64_t c = 0; c < nchunks; c++) {   // counts that ran chunk by chunk
+        float a = 0.f;
+        GB_CUDA(cudaEventElapsedTime(&a, EV(c, 4), EV(c, 5)));
+        out->ms_paircount += a;
+    }
     GB_CUDA(cudaEventElapsedTime(&out->ms_finalize, p->events[e_pc], p->events[e_fin]));
     GB_CUDA(cudaEventElapsedTime(&out->ms_total, p->events[0], p->events[e_fin]));
     out->launches = launches;

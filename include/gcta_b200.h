@@ -241,14 +241,17 @@ int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
  *   gcta_b200_decode_emit_diag reads each packed row once more and writes the 16-bit Z chunk (make_XMat / std_XMat,
  *                              data.cpp:982-1056) AND, in the same pass, adds sum_k z_fk^2 (float64) and the non-missing
  *                              counts of file individuals [diag_f0, diag_f1) into d_diag / d_nii (grm.cpp:265-275);
- *                              d_diag == d_nii == NULL skips the diagonal.  d_Z 32-byte aligned, layout as above. */
+ *                              d_diag == d_nii == NULL skips the diagonal.  d_Z 32-byte aligned, layout as above.
+ *                              d_OK != NULL: the same pass also writes the 8-bit E4M3 non-missing indicators (1.0 / 0) of
+ *                              every genotype as a matrix [kc rounded up to 128][ldz] bytes, what gcta_b200_nonmiss_matrix
+ *                              with GCTA_B200_E4M3 produces (the operand of the counting pass, grm.cpp:270, 291). */
 int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_keepmask, int64_t n,
                         const int32_t* d_include, int64_t k0, int64_t kc, const double* d_mu_in, int32_t alg,
                         double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
                         unsigned long long* d_total_missing, void* stream, char* err, size_t errcap);
 int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const int32_t* d_include,
                                int64_t k0, int64_t kc, const float* d_zlut, int32_t operand, void* d_Z, int64_t ldz,
-                               double* d_diag, int32_t* d_nii, int64_t diag_f0, int64_t diag_f1,
+                               double* d_diag, int32_t* d_nii, int64_t diag_f0, int64_t diag_f1, void* d_OK,
                                void* stream, char* err, size_t errcap);
 
 /* K1d - exact per-individual diagonal: diag[f] += sum_k z_fk^2 in float64 and nii[f] += number

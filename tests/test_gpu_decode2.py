@@ -19,7 +19,7 @@ torch = pytest.importorskip("torch")
 P, I64, I32 = C.c_void_p, C.c_int64, C.c_int32
 
 
-def run_fused(bed, n, include=None, mu_in=None, operand=abi.FP16, k0=0, kc=None, ldz=None, diag_range=None, want_diag=True):
+def run_fused(bed, n, include=None, mu_in=None, operand=abi.FP16, k0=0, kc=None, ldz=None, diag_range=None, want_diag=True, want_ok=False):
     bedp, pitch = pitched(bed, n)
     m = bed.shape[0] if include is None else len(include)
     kc = m - k0 if kc is None else kc
@@ -37,14 +37,15 @@ def run_fused(bed, n, include=None, mu_in=None, operand=abi.FP16, k0=0, kc=None,
     tot = torch.zeros(1, dtype=torch.int64, device="cuda")
     diag = torch.zeros(n, dtype=torch.float64, device="cuda")
     nii = torch.zeros(n, dtype=torch.int32, device="cuda")
+    OK = torch.full(((kc + 127) // 128 * 128, ldz), 9, dtype=torch.uint8, device="cuda") if want_ok else None   # poisoned too
     ptr = lambda t: P(None if t is None else t.data_ptr())
     abi.call("gcta_b200_snp_stats", ptr(d_bed), I64(pitch), I64(n), ptr(d_km), I64(n), ptr(d_inc), I64(k0), I64(kc), ptr(d_mu_in),
              I32(0), ptr(mu), ptr(cnt), ptr(sm), ptr(zlut), ptr(tot), stream())
     f0, f1 = (0, n) if diag_range is None else diag_range
     abi.call("gcta_b200_decode_emit_diag", ptr(d_bed), I64(pitch), I64(n), ptr(d_inc), I64(k0), I64(kc), ptr(zlut), I32(operand),
-             ptr(Z), I64(ldz), ptr(diag if want_diag else None), ptr(nii if want_diag else None), I64(f0), I64(f1), stream())
+             ptr(Z), I64(ldz), ptr(diag if want_diag else None), ptr(nii if want_diag else None), I64(f0), I64(f1), ptr(OK), stream())
     torch.cuda.synchronize()
-    return dict(Z=Z.cpu().numpy(), mu=mu.cpu().numpy(), cnt=cnt.cpu().numpy(), sum=sm.cpu().numpy(),
+    return dict(OK=None if OK is None else OK.cpu().numpy(), Z=Z.cpu().numpy(), mu=mu.cpu().numpy(), cnt=cnt.cpu().numpy(), sum=sm.cpu().numpy(),
                 zlut=zlut.cpu().numpy().reshape(m, 8), total_missing=int(tot.item()), diag=diag.cpu().numpy(), nii=nii.cpu().numpy())
 
 
@@ -138,3 +139,17 @@ def test_fused_decode_long_run_flushes_partial_sums(monkeypatch):
     assert np.array_equal(r["Z"][:m, :n], z16_expected(z, abi.FP16))
     d_ref, n_ref = oracle_diag(z, ok)
     assert np.array_equal(r["nii"], n_ref) and np.allclose(r["diag"], d_ref, rtol=1e-6)
+
+
+@pytest.mark.parametrize("n,m,miss,want_diag", [(203, 300, 0.1, True), (5003, 259, 0.3, True), (4100, 130, 0.02, False)])
+def test_fused_decode_indicator_plane(n, m, miss, want_diag):
+    """the E4M3 non-missing indicators written in the same pass: 0x38 (1.0) / 0 per genotype, zero padding to a multiple
+    of 128 rows and behind n; Z and the diagonal unchanged by asking for them"""
+    bed = synth.make_bed_payload(41 + n, n, m, miss_rate=miss)
+    r = run_fused(bed, n, want_ok=True, want_diag=want_diag)
+    r0 = run_fused(bed, n, want_ok=False, want_diag=want_diag)
+    z, ok, _ = oracle.standardise(oracle.decode_x(bed, n))
+    assert np.array_equal(r["OK"][:m, :n], np.where(ok, 0x38, 0).astype(np.uint8))
+    assert not r["OK"][m:, :].any() and not r["OK"][:, n:].any()
+    assert np.array_equal(r["Z"], r0["Z"]) and np.array_equal(r["nii"], r0["nii"])
+    assert np.allclose(r["diag"], r0["diag"], rtol=1e-12)

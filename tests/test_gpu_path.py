@@ -314,3 +314,23 @@ def test_grm_alg1(miss, xchr):
     # and it is a different matrix from the default algorithm
     A0, _, _, _ = abi.make_grm(bed, n, m, xchr=xchr, sex=sex)
     assert np.abs(A0 - A).max() > 1e-3
+
+
+def test_counts_chunk_by_chunk_equal_the_separate_pass(monkeypatch):
+    """With missing genotypes in the first SNP chunk the indicators are written with Z and counted chunk by chunk; when
+    they only turn up later, a separate indicator pass counts after the loop.  Same N (and A) either way."""
+    n, m = 1100, 9000
+    bed = synth.make_bed_payload(71, n, m, miss_rate=0.03)
+    A0, N0, mu0, o0 = abi.make_grm(bed, n, m, chunk_snps=1024)                 # chunk by chunk
+    monkeypatch.setenv("GCTA_B200_COUNT_INLINE", "0")
+    A1, N1, mu1, o1 = abi.make_grm(bed, n, m, chunk_snps=1024)                 # separate pass
+    monkeypatch.delenv("GCTA_B200_COUNT_INLINE")
+    assert np.array_equal(N0, N1) and np.array_equal(A0, A1) and o0.launches < o1.launches
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n)
+    check_grm(A0, N0, pack_lower(Aref), pack_lower(Nref))
+    # nothing missing in the first two chunks, 5 % afterwards
+    late = np.concatenate([synth.make_bed_payload(72, n, 2048, miss_rate=0.0), synth.make_bed_payload(73, n, m - 2048, miss_rate=0.05)])
+    A2, N2, _, o2 = abi.make_grm(late, n, m, chunk_snps=1024)
+    assert o2.total_missing > 0
+    Aref, Nref, _ = oracle.make_grm_numpy(late, n)
+    check_grm(A2, N2, pack_lower(Aref), pack_lower(Nref))
