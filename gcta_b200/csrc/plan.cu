@@ -73,7 +73,9 @@ extern "C" int gcta_b200_partition(int64_t n, int32_t part_rank, int32_t part_wo
     // the ratios do not depend on M).  Boundaries minimise the largest band.  The model reproduces the measured
     // per-rank times of that run within 3 %; counting whole waves instead of tiles moves the 8-GPU bands so that no
     // rank needs an 18th wave (predicted step 236 ms against 241 ms).
-    const double ALPHA = 1.33, BETA = 0.83;
+    double ALPHA = 1.33, BETA = 0.83;
+    if (const char* e = getenv("GCTA_B200_PART_ALPHA")) ALPHA = atof(e);   // for re-calibration runs
+    if (const char* e = getenv("GCTA_B200_PART_BETA")) BETA = atof(e);
     const int64_t SMS = 148;
     std::vector<int64_t> pref(nrb + 1, 0);
     for (int64_t b = 0; b < nrb; b++) pref[b + 1] = pref[b] + tiles_in_row_block(b, n);
@@ -169,8 +171,11 @@ struct gcta_b200_plan {
     int64_t ring_rows = 0;
     cudaEvent_t slot_free[2] = {nullptr, nullptr};   // the last kernel that reads ring slot j has finished
     // pinned bounce slots of the helper threads that move pageable host buffers (Stager: genotypes in, Drainer: results out)
-    static constexpr int HELPERS = 6, HSLOTS = 2;
-    static constexpr int64_t HSLOT_BYTES = 16ll << 20;
+    // (pinning host memory costs ~1.5 ms per MB on this box, so the slots are few and small and the helpers only serve
+    // transfers of GBs: STAGE_MIN_BYTES / DRAIN_MIN_BYTES)
+    static constexpr int HELPERS = 4, HSLOTS = 2;
+    static constexpr int64_t HSLOT_BYTES = 8ll << 20;
+    static constexpr int64_t STAGE_MIN_BYTES = 2ll << 30, DRAIN_MIN_BYTES = 1ll << 30;
     uint8_t* h_up[HELPERS][HSLOTS] = {};
     uint8_t* h_down[HELPERS][HSLOTS] = {};
     uint32_t *d_keepmask = nullptr, *d_sexmale = nullptr, *d_planes = nullptr;
@@ -719,6 +724,19 @@ namespace gb {
 
 struct DrainPiece { void* dst; const void* src; int64_t bytes; cudaEvent_t ready; };
 
+// smallest transfers the helper threads take over; GCTA_B200_STAGE_MIN_MB overrides both (tests use it to reach the code
+// with small inputs)
+static int64_t stage_min_bytes()
+{
+    if (const char* e = getenv("GCTA_B200_STAGE_MIN_MB")) return atoll(e) << 20;
+    return gcta_b200_plan::STAGE_MIN_BYTES;
+}
+static int64_t drain_min_bytes()
+{
+    if (const char* e = getenv("GCTA_B200_STAGE_MIN_MB")) return atoll(e) << 20;
+    return gcta_b200_plan::DRAIN_MIN_BYTES;
+}
+
 static bool host_is_pageable(const void* ptr)
 {
     cudaPointerAttributes attr;
@@ -851,7 +869,7 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
     // segments whatever the host does: into pinned memory they are asynchronous copies on the copy stream; pageable memory
     // is served by the Drainer's helper threads (or, for small bands, by the driver's own staging, which blocks this thread
     // piece by piece).
-    const bool drain = !rc && p->band_count * 4 >= (64ll << 20) && host_is_pageable(out->A_lower) &&
+    const bool drain = !rc && p->band_count * 4 >= drain_min_bytes() && host_is_pageable(out->A_lower) &&
                        !(getenv("GCTA_B200_STAGE") && atoi(getenv("GCTA_B200_STAGE")) == 0);
     if (drain) {
         std::vector<DrainPiece> pieces;
@@ -944,7 +962,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         cudaPointerAttributes attr;
         const bool pageable = cudaPointerGetAttributes(&attr, bed_host) != cudaSuccess || attr.type == cudaMemoryTypeUnregistered;
         cudaGetLastError();
-        if (pageable && p->pitch * p->m_file >= (64ll << 20)) {
+        if (pageable && p->pitch * p->m_file >= stage_min_bytes()) {
             std::vector<int64_t> rb((size_t)nch_up), re((size_t)nch_up);
             for (int64_t c = 0; c < nch_up; c++) chunk_rows(c, rb[(size_t)c], re[(size_t)c]);
             stager.reset(new Stager());
@@ -1254,7 +1272,7 @@ extern "C" int gcta_b200_plan_download(gcta_b200_plan* p, gcta_b200_out* out, ch
     const bool have = p->downloaded && p->streamed_A == out->A_lower && (!out->N_lower || p->streamed_N == out->N_lower);
     // large pageable destinations go through the Drainer's helper threads (everything on p->stream has completed: plan_run
     // synchronises before it returns)
-    const bool big = p->band_count * 4 >= (64ll << 20) && !(getenv("GCTA_B200_STAGE") && atoi(getenv("GCTA_B200_STAGE")) == 0);
+    const bool big = p->band_count * 4 >= drain_min_bytes() && !(getenv("GCTA_B200_STAGE") && atoi(getenv("GCTA_B200_STAGE")) == 0);
     std::vector<DrainPiece> pieces;
     if (!have) {
         if (big && host_is_pageable(out->A_lower)) pieces.push_back({out->A_lower + base, p->d_A_lower, p->band_count * 4, nullptr});

@@ -111,6 +111,7 @@ def test_pageable_host_buffers_go_through_pinned_staging(monkeypatch, miss):
         p.synth(seed, synth.snp_thresholds(seed, m, miss_rate=miss))
         p.download_bed(bed)
     inc = np.sort(np.random.default_rng(1).choice(m, 60_000, replace=False)).astype(np.int32)
+    monkeypatch.setenv("GCTA_B200_STAGE_MIN_MB", "32")   # the helpers normally only take transfers of GBs
     for include in (None, inc):
         monkeypatch.setenv("GCTA_B200_STAGE", "0")
         A0, N0, mu0, _ = abi.make_grm(bed, n, m, include=include)
