@@ -6,17 +6,14 @@
 //                        row once, writes ~50 bytes.  Replaces calcu_mu / mu_func
 //                        (data.cpp:759-803) and the per-SNP constants of std_XMat (data.cpp:1027-1040).
 // K1f decode_emit_diag : CTA = a slab of 2048 individuals x a run of SNP rows.  A thread owns one
-//                        32-bit packed column (16 individuals) and walks down the rows, six at a time
-//                        with the next six words already in flight: per row one 4-byte load, eight
-//                        nibble look-ups (two genotypes each) in a per-SNP table in shared memory
-//                        that yield the 16-bit z values, and one 32-byte store of the Z row segment;
-//                        per PAIR of rows sixteen look-ups in a 16-entry table of summed squares (one
-//                        per individual: its two codes form the index) and sixteen float adds into
+//                        32-bit packed column (16 individuals) and walks down the rows: per row one
+//                        4-byte load, eight nibble look-ups (two genotypes each) in a per-SNP table
+//                        in shared memory that yield the two 16-bit z values and their two float
+//                        squares, one 32-byte store of the Z row segment, and sixteen float adds into
 //                        the thread's own diagonal sums.  Missing genotypes are counted bit-sliced.
-//                        Optionally the 8-bit non-missing indicators of the counting pass come out of
-//                        the same look-ups.  Replaces make_XMat / std_XMat (data.cpp:982-1056) and the
-//                        diagonal of the triple loop (grm.cpp:265-275) in ONE pass: the separate
-//                        diagonal kernel and its re-read of the packed rows are gone.
+//                        Replaces make_XMat / std_XMat (data.cpp:982-1056) and the diagonal of the
+//                        triple loop (grm.cpp:265-275) in ONE pass: the separate diagonal kernel and
+//                        its re-read of the packed rows are gone.
 //
 // Both are HBM-bound byte kernels.  Algorithmic bytes per SNP: ceil(n/4) (K1s) and
 // ceil(n/4) + 2*ldz (K1f).  This is the path for the common case (every individual kept,
@@ -45,7 +42,7 @@ __device__ __forceinline__ int warp_sum2(int v)
 // ------------------------------------------------------------------------------------------------
 // K1s
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) snp_stats_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n_kept,
+__global__ void __launch_bounds__(256, 4) snp_stats_kernel(const uint8_t* __restrict__ bed, int64_t pitch, int64_t n_kept,
                                                          const uint32_t* __restrict__ keepmask,
                                                          const int32_t* __restrict__ include, int64_t k0, int64_t kc,
                                                          const double* __restrict__ mu_in, int divide, double* __restrict__ mu_out,
@@ -62,18 +59,32 @@ __global__ void __launch_bounds__(256) snp_stats_kernel(const uint8_t* __restric
         const uint4* km16 = reinterpret_cast<const uint4*>(keepmask);
         int cnt = 0, sum = 0;
         const int nvec = (int)(pitch / 16);
-#pragma unroll 4
-        for (int v = lane; v < nvec; v += 32) {
-            const uint4 w = __ldg(row16 + v), km = __ldg(km16 + v);
+        // 16 bytes = 64 genotypes per lane and step.  All masks live on the even bit positions, so two of them share one
+        // POPC (a | b << 1): 6 POPCs per 16 bytes instead of 12 - the quarter-rate POPC unit would otherwise bound this
+        // kernel at about the HBM rate.  Four row vectors are fetched before any is counted (memory-level parallelism:
+        // one load in flight per warp reaches ~4.3 TB/s, measured).
+        auto count16 = [&](const uint4& w, const uint4& km) {
             const uint32_t ww[4] = {w.x, w.y, w.z, w.w}, kw[4] = {km.x, km.y, km.z, km.w};
+            uint32_t nm[4], x[4], y[4];
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 const uint32_t lo = ww[q] & 0x55555555u, hi = (ww[q] >> 1) & 0x55555555u;
-                const uint32_t nm = ~(lo & ~hi) & kw[q];   // kept and not missing (even bit positions)
-                cnt += __popc(nm);
-                sum += __popc(nm & ~hi) + __popc(nm & ~lo);
+                nm[q] = ~(lo & ~hi) & kw[q];   // kept and not missing
+                x[q] = nm[q] & ~hi;            // allele-1 dosage = [not hi] + [not lo] among those
+                y[q] = nm[q] & ~lo;
             }
+            cnt += __popc(nm[0] | (nm[1] << 1)) + __popc(nm[2] | (nm[3] << 1));
+            sum += __popc(x[0] | (y[0] << 1)) + __popc(x[1] | (y[1] << 1)) + __popc(x[2] | (y[2] << 1)) + __popc(x[3] | (y[3] << 1));
+        };
+        int v = lane;
+        for (; v + 96 < nvec; v += 128) {
+            uint4 w[4], km[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) { w[u] = __ldg(row16 + v + 32 * u); km[u] = __ldg(km16 + v + 32 * u); }
+#pragma unroll
+            for (int u = 0; u < 4; u++) count16(w[u], km[u]);
         }
+        for (; v < nvec; v += 32) count16(__ldg(row16 + v), __ldg(km16 + v));
         cnt = warp_sum2(cnt);
         sum = warp_sum2(sum);
         if (lane == 0) {
@@ -141,10 +152,11 @@ __device__ __forceinline__ void st_z256(uint16_t* dst, const uint32_t (&o)[8])
 
 // One packed word = 16 genotypes of one SNP.  `row_addr` is the shared-memory address of the SNP's 256-byte table row
 // (256-byte aligned): 16 nibble entries of 8 bytes - the two 16-bit z values of the nibble's two individuals, then their
-// two E4M3 non-missing indicators.  The eight nibble offsets come out of two masked copies of the word by PRMT, which
-// also merges them into the table address.
-template <bool OKP>
-__device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_t* zdst, uint8_t* okdst, int nvalid)
+// two E4M3 non-missing indicators - followed from byte 128 by 16 float2 entries with the squares of the z values.
+// The eight nibble offsets come out of two masked copies of the word by PRMT, which also merges them into the table
+// address; the squares are added two at a time by the packed FADD2 (acc2[j] = sums of individuals 2j and 2j+1).
+template <bool DIAG, bool OKP>
+__device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_t* zdst, uint8_t* okdst, int nvalid, unsigned long long (&acc2)[8])
 {
     const uint32_t ev = (w << 3) & 0x78787878u;   // 8 x nibbles 0, 2, 4, 6 in bytes 0..3
     const uint32_t od = (w >> 1) & 0x78787878u;   // 8 x nibbles 1, 3, 5, 7
@@ -160,6 +172,11 @@ __device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_
         else asm("prmt.b32 %0, %1, %2, 0x7653;" : "=r"(a) : "r"(src), "r"(row_addr));
         if (OKP) asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(o[j]), "=r"(k[j]) : "r"(a));
         else asm volatile("ld.shared.u32 %0, [%1];" : "=r"(o[j]) : "r"(a));
+        if (DIAG) {
+            unsigned long long q;
+            asm volatile("ld.shared.b64 %0, [%1+128];" : "=l"(q) : "r"(a));
+            asm("add.rn.f32x2 %0, %0, %1;" : "+l"(acc2[j]) : "l"(q));
+        }
     }
     uint32_t ok4[4];
     if (OKP) {
@@ -188,47 +205,16 @@ __device__ __forceinline__ void emit_word(uint32_t w, uint32_t row_addr, uint16_
     }
 }
 
-// The diagonal's share of TWO SNP rows at once: for each of the 16 individuals the two 2-bit codes (one per row) form a
-// nibble that indexes a 16-entry float table  T[c0 + 4 c1] = z0[c0]^2 + z1[c1]^2  of the row pair (64 bytes at offset 128
-// of the even row's table slot).  One 4-byte look-up and one add per individual and row pair: half the shared-memory
-// traffic of a look-up per genotype - the kernel's load/store pipe is its busiest unit next to HBM.
-__device__ __forceinline__ void diag_pair(uint32_t w0, uint32_t w1, uint32_t pair_addr, float (&acc)[16])
-{
-    const uint32_t u = (w0 & 0x33333333u) | ((w1 << 2) & 0xCCCCCCCCu);   // nibble j: individual 2j, codes of (row, row + 1)
-    const uint32_t v = ((w0 >> 2) & 0x33333333u) | (w1 & 0xCCCCCCCCu);   // nibble j: individual 2j + 1
-    // byte b = 128 + 4 x nibble: [0] nibbles 0,2,4,6 of u (individuals 0,4,8,12)  [1] nibbles 1,3,5,7 of u (2,6,10,14)
-    //                            [2] the same of v (individuals 1,5,9,13)          [3] (individuals 3,7,11,15)
-    const uint32_t src[4] = {((u << 2) & 0x3C3C3C3Cu) | 0x80808080u, ((u >> 2) & 0x3C3C3C3Cu) | 0x80808080u,
-                             ((v << 2) & 0x3C3C3C3Cu) | 0x80808080u, ((v >> 2) & 0x3C3C3C3Cu) | 0x80808080u};
-#pragma unroll
-    for (int g = 0; g < 4; g++) {
-        const int first = g == 0 ? 0 : (g == 1 ? 2 : (g == 2 ? 1 : 3));   // individual of byte 0; the bytes are 4 individuals apart
-#pragma unroll
-        for (int b = 0; b < 4; b++) {
-            uint32_t a;
-            if (b == 0) asm("prmt.b32 %0, %1, %2, 0x7650;" : "=r"(a) : "r"(src[g]), "r"(pair_addr));
-            else if (b == 1) asm("prmt.b32 %0, %1, %2, 0x7651;" : "=r"(a) : "r"(src[g]), "r"(pair_addr));
-            else if (b == 2) asm("prmt.b32 %0, %1, %2, 0x7652;" : "=r"(a) : "r"(src[g]), "r"(pair_addr));
-            else asm("prmt.b32 %0, %1, %2, 0x7653;" : "=r"(a) : "r"(src[g]), "r"(pair_addr));
-            float q;
-            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(q) : "r"(a));
-            acc[first + 4 * b] += q;
-        }
-    }
-}
-
 template <bool DIAG, bool OKP>
 __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64_t r1, int64_t col, bool in_z, bool can_load, int nvalid,
                                          uint8_t (*tab)[F_TB][256], int64_t (*row_off)[F_TB])
 {
     const int tid = threadIdx.x;
     const int64_t i0 = col * 16;
-    float acc[16];                 // running sums of z^2 of the thread's 16 individuals
+    unsigned long long acc2[8];    // float pairs: the running sums of z^2 of individuals (2j, 2j+1)
     uint32_t m16[8];
 #pragma unroll
-    for (int e = 0; e < 16; e++) acc[e] = 0.0f;
-#pragma unroll
-    for (int g = 0; g < 8; g++) m16[g] = 0;
+    for (int g = 0; g < 8; g++) { m16[g] = 0; acc2[g] = 0ull; }
     const bool tdiag = DIAG && in_z && i0 < p.diag_f1 && i0 + 16 > p.diag_f0;
     int rows_acc = 0;
 
@@ -241,13 +227,7 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
             // E4M3 1.0 = 0x38 for a non-missing genotype (code != 01b), 0 for a missing one
             const uint32_t okp = ((nib & 3) != 1 ? 0x38u : 0u) | ((nib >> 2) != 1 ? 0x3800u : 0u);
             *reinterpret_cast<uint2*>(&tab[buf][row][8 * nib]) = make_uint2(f2h16(za, p.bf16) | (f2h16(zb, p.bf16) << 16), okp);
-            if (DIAG && (row & 1) == 0) {
-                // pair table of rows (row, row + 1): entry nib = squares of row's code (nib & 3) and row + 1's code (nib >> 2);
-                // a block's last row without a partner pairs with nothing (its partner's word is passed as 0)
-                const float qa = za * za;                                      // exact product rounded once to float
-                const float zc = row + 1 < nr ? __ldg(p.zlut + (k + 1) * 8 + (nib >> 2)) : 0.0f;
-                *reinterpret_cast<float*>(&tab[buf][row][128 + 4 * nib]) = qa + zc * zc;
-            }
+            if (DIAG) *reinterpret_cast<float2*>(&tab[buf][row][128 + 8 * nib]) = make_float2(za * za, zb * zb);   // exact products rounded once to float
         }
         for (int row = tid; row < nr; row += F_THREADS) {
             const int64_t k = p.k0 + rbase + row;
@@ -263,15 +243,14 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
                     // m16[g]: low half = individual g, high half = individual 8+g; m16[4+g]: individuals 4+g, 12+g
                     const int g = e & 3, hi = (e >> 2) & 1, top = e >> 3;
                     const int miss = (int)((m16[g + 4 * hi] >> (16 * top)) & 0xFFFFu);
-                    atomicAdd(p.diag + f, (double)acc[e]);
+                    const float sum = __uint_as_float((uint32_t)(acc2[e >> 1] >> (32 * (e & 1))));
+                    atomicAdd(p.diag + f, (double)sum);
                     atomicAdd(p.nii + f, rows_acc - miss);
                 }
             }
         }
 #pragma unroll
-        for (int e = 0; e < 16; e++) acc[e] = 0.0f;
-#pragma unroll
-        for (int g = 0; g < 8; g++) m16[g] = 0;
+        for (int g = 0; g < 8; g++) { m16[g] = 0; acc2[g] = 0ull; }
         rows_acc = 0;
     };
 
@@ -308,39 +287,26 @@ __device__ __forceinline__ void run_rows(const FusedParams& p, int64_t r0, int64
                 if (row + 12 <= nr) { load6(wn, buf, rbase, row + 6); have_next = true; }
                 else if (!p.include && nr == F_TB && row + 6 == nr && rbase + F_TB + 6 <= r1) { load6(wn, buf ^ 1, rbase + F_TB, 0); have_next = true; }
 #pragma unroll
-                for (int u = 0; u < 6; u++)
-                    emit_word<OKP>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz,
-                                   OKP ? okrow + (int64_t)(row + u) * p.ldz : nullptr, nvalid);
-                if (DIAG) {
+                for (int h = 0; h < 2; h++) {
+                    uint32_t c2 = 0;
 #pragma unroll
-                    for (int u = 0; u < 6; u += 2) diag_pair(w[u], w[u + 1], tab_addr + (uint32_t)(row + u) * 256u, acc);
-#pragma unroll
-                    for (int h = 0; h < 2; h++) {   // missing = code 01b, one count per 2-bit lane, three rows at a time
-                        uint32_t c2 = 0;
-#pragma unroll
-                        for (int u = 3 * h; u < 3 * h + 3; u++) c2 += (w[u] & 0x55555555u) & ~(w[u] >> 1);
+                    for (int u = 3 * h; u < 3 * h + 3; u++) {
+                        emit_word<DIAG, OKP>(w[u], tab_addr + (uint32_t)(row + u) * 256u, zrow + (int64_t)(row + u) * p.ldz,
+                                             OKP ? okrow + (int64_t)(row + u) * p.ldz : nullptr, nvalid, acc2);
+                        if (DIAG) c2 += (w[u] & 0x55555555u) & ~(w[u] >> 1);   // missing = code 01b, one count per 2-bit lane
+                    }
+                    if (DIAG) {
 #pragma unroll
                         for (int g = 0; g < 4; g++) c8[g] += (c2 >> (2 * g)) & 0x03030303u;
                     }
                 }
             }
-            for (; row < nr; row += 2) {   // the rows left over by the groups of six, in pairs (the last one may be single)
-                const bool two = row + 1 < nr;
-                uint32_t w0, w1 = 0u;
-                {
-                    const int64_t off = p.include ? row_off[buf][row] : (p.k0 + rbase + row) * p.pitch;
-                    w0 = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + off)) : 0u;
-                }
-                emit_word<OKP>(w0, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, OKP ? okrow + (int64_t)row * p.ldz : nullptr, nvalid);
-                if (two) {
-                    const int64_t off = p.include ? row_off[buf][row + 1] : (p.k0 + rbase + row + 1) * p.pitch;
-                    w1 = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + off)) : 0u;
-                    emit_word<OKP>(w1, tab_addr + (uint32_t)(row + 1) * 256u, zrow + (int64_t)(row + 1) * p.ldz,
-                                   OKP ? okrow + (int64_t)(row + 1) * p.ldz : nullptr, nvalid);
-                }
+            for (; row < nr; row++) {
+                const int64_t off = p.include ? row_off[buf][row] : (p.k0 + rbase + row) * p.pitch;
+                const uint32_t w = can_load ? __ldg(reinterpret_cast<const uint32_t*>(colp + off)) : 0u;
+                emit_word<DIAG, OKP>(w, tab_addr + (uint32_t)row * 256u, zrow + (int64_t)row * p.ldz, OKP ? okrow + (int64_t)row * p.ldz : nullptr, nvalid, acc2);
                 if (DIAG) {
-                    diag_pair(w0, w1, tab_addr + (uint32_t)row * 256u, acc);   // a single row: partner word 0, partner squares 0
-                    const uint32_t c2 = ((w0 & 0x55555555u) & ~(w0 >> 1)) + (two ? (w1 & 0x55555555u) & ~(w1 >> 1) : 0u);
+                    const uint32_t c2 = (w & 0x55555555u) & ~(w >> 1);
 #pragma unroll
                     for (int g = 0; g < 4; g++) c8[g] += (c2 >> (2 * g)) & 0x03030303u;
                 }
@@ -412,7 +378,7 @@ extern "C" int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t 
     int dev = 0, sms = 0;
     GB_CUDA(cudaGetDevice(&dev));
     GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    int per_sm = 0;   // resident CTAs per SM (6 at 40 registers): the grid is exactly one wave
+    int per_sm = 0;   // resident CTAs per SM: the grid is exactly one wave
     GB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, snp_stats_kernel, 256, 0));
     const int64_t ctas = std::min<int64_t>((kc + 7) / 8, (int64_t)sms * std::max(per_sm, 1));
     snp_stats_kernel<<<(unsigned)ctas, 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, n, d_keepmask, d_include, k0, kc, d_mu_in,
