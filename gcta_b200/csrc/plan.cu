@@ -68,12 +68,11 @@ extern "C" int gcta_b200_partition(int64_t n, int32_t part_rank, int32_t part_wo
     //                                     of SMS tiles together, so a launch takes whole waves
     // + ALPHA * b1                        K1 standardises columns [0, 256*b1) for this band (HBM-bound, replicated per GPU)
     // + BETA * (b1 - b0)                  K1d sums the diagonal of the band's own individuals
-    // ALPHA and BETA are measured ratios on B200 (8-GPU run of the headline workload with the wave-barrier kernel: a
-    // wave of 148 tiles 12.2 ms, K1 0.110 ms and K1d 0.069 ms per block of 256 individuals; all three scale with M, so
-    // the ratios do not depend on M).  Boundaries minimise the largest band.  The model reproduces the measured
-    // per-rank times of that run within 3 %; counting whole waves instead of tiles moves the 8-GPU bands so that no
-    // rank needs an 18th wave (predicted step 236 ms against 241 ms).
-    double ALPHA = 1.33, BETA = 0.83;
+    // ALPHA and BETA are measured ratios on B200, re-measured in round 2 with the fused decode (2-GPU run of the headline
+    // workload: a 256x256 tile 0.087 ms = a wave of 148 tiles 12.8 ms; K1f 0.083 ms per block of 256 individuals at M = 1M,
+    // the diagonal of a band's own rows ~0.004 ms per block; all scale with M, so the ratios do not depend on M; round 1's
+    // two-kernel decode had 1.33 / 0.83).  Boundaries minimise the largest band, counted in whole waves.
+    double ALPHA = 0.96, BETA = 0.05;
     if (const char* e = getenv("GCTA_B200_PART_ALPHA")) ALPHA = atof(e);   // for re-calibration runs
     if (const char* e = getenv("GCTA_B200_PART_BETA")) BETA = atof(e);
     const int64_t SMS = 148;
