@@ -450,6 +450,15 @@ def main_ours(a, rank, world, local_rank):
                                     "sample": f"oracle/_ref/gcta_ref --make-grm-bin on n={a.ref_n} x M={a.ref_m} of the same generator (single thread: the reference has no threading)"}
         except Exception as ex:  # noqa: BLE001
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 1, "kind": "reference", "sample": f"failed: {ex}"}
+    # the reference on BASELINE config 1 IN FULL (n = 2,000 x M = 50,000, ~7 minutes of one core): once per round, on request
+    if rank == 0 and world == 1 and a.cpu_full:
+        try:
+            with tempfile.TemporaryDirectory() as d:
+                v, dt, cores = run_reference_sample(2000, 50000, 0.0, 1234, d)
+            line["cpu_baseline_cfg1_full"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "seconds": dt,
+                                              "sample": "oracle/_ref/gcta_ref --make-grm-bin on BASELINE config 1 in full (n=2000 x M=50000), single thread"}
+        except Exception as ex:  # noqa: BLE001
+            line["cpu_baseline_cfg1_full"] = {"value": None, "sample": f"failed: {ex}"}
     if rank == 0:
         print(json.dumps(line))
     plan.close()
@@ -485,6 +494,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-full", action="store_true", help="also time the reference on BASELINE config 1 in full (about 7 minutes)")
     ap.add_argument("--config", default="cfg3", choices=sorted(CONFIGS), help="BASELINE.json configuration (cfg3 = the one the metric is quoted on)")
     ap.add_argument("--force", action="store_true", help="run a configuration on a GPU count BASELINE.json does not name it on")
     ap.add_argument("--no-parity", action="store_true")

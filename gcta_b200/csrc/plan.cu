@@ -161,6 +161,7 @@ struct gcta_b200_plan {
     bool downloaded = false;   // the last run already streamed A (and filled N) into the caller's buffers ...
     const float* streamed_A = nullptr;   // ... namely these (plan_download into other buffers still copies)
     const int32_t* streamed_N = nullptr;
+    const int32_t* prefilled_N = nullptr;   // this N band was filled with m on the host while the last run computed
     int64_t diag_f0 = 0, diag_f1 = 0;   // file individuals whose diagonal this band needs (multiple of 16 at the low end)
     uint8_t *d_bed = nullptr, *d_bed_own = nullptr;   // d_bed: the buffer the kernels read; d_bed_own: the plan's allocation
     // Packed file larger than its HBM allowance: no resident copy; the rows of one SNP chunk at a time pass through two
@@ -856,7 +857,7 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
     // every launch of the chunk is queued: only now start the host threads that fill N (== m everywhere), so that
     // nothing competes with the launching thread for cores while the GPU waits for its next kernel
     std::vector<std::thread> fill;
-    if (out->N_lower) {
+    if (out->N_lower && p->prefilled_N != out->N_lower) {
         const int nt = (int)std::min<int64_t>(16, std::max<int64_t>(1, p->band_count >> 22));
         int32_t* dst = out->N_lower + band_base;
         const int32_t mval = (int32_t)p->m;
@@ -1015,6 +1016,16 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
                            !(getenv("GCTA_B200_COUNT_INLINE") && atoi(getenv("GCTA_B200_COUNT_INLINE")) == 0);
     bool count_inline = false;
     void* okbuf = nullptr;
+    // Results that go to host buffers: when nothing is missing N_ij == m for every pair (what grm.cpp:291 yields), filled
+    // by host threads.  They start as soon as the first chunk is queued - not behind the last chunk, whose compute is too
+    // short to hide 0.6 - 5 GB of host writes once several GPUs share the work (measured: +55 ms on a 233 ms step at
+    // 8 GPUs) - and are joined before this call returns.  If genotypes turn out to be missing, the real counts are
+    // downloaded over the fill afterwards.
+    struct FillGuard {
+        std::vector<std::thread> th;
+        ~FillGuard() { for (auto& t : th) t.join(); }
+    } nfill;
+    p->prefilled_N = nullptr;
     for (int64_t c = 0; c < nchunks; c++) {
         const int64_t k0 = p->cstart[c], kc = p->cstart[c + 1] - k0;
         void* Z = (p->overlap && p->d_Zbuf[1]) ? p->d_Zbuf[c & 1] : p->d_Zbuf[0];
@@ -1096,6 +1107,15 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             launches++;
         }
         GB_CUDA(cudaEventRecord(EV(c, 5), st));
+        if (c == 0 && !pipelined && to_host && out->N_lower && p->band_count > 0) {
+            const int nt = (int)std::min<int64_t>(8, std::max<int64_t>(1, p->band_count >> 22));
+            int32_t* dst = out->N_lower + p->row_begin * (p->row_begin + 1) / 2;
+            const int32_t mval = (int32_t)p->m;
+            const int64_t cnt = p->band_count;
+            for (int t = 0; t < nt; t++)
+                nfill.th.emplace_back([=]() { std::fill(dst + cnt * t / nt, dst + cnt * (t + 1) / nt, mval); });
+            p->prefilled_N = out->N_lower;
+        }
         if (!stager) GB_CUDA(issue_upload(c + 1));
     }
     if (stager) stager->finish();
@@ -1284,7 +1304,7 @@ extern "C" int gcta_b200_plan_download(gcta_b200_plan* p, gcta_b200_out* out, ch
     if (!pieces.empty() && !drain_to_pageable(p, pieces))
         return set_err(err, errcap, GCTA_B200_ERR_CUDA, "Error: CUDA call failed in plan_download (pinned staging).");
     if (out->mu_out) GB_CUDA(cudaMemcpyAsync(out->mu_out, p->d_mu, (size_t)p->m * 8, cudaMemcpyDeviceToHost, p->stream));
-    if (out->N_lower && p->total_missing == 0 && !have) {
+    if (out->N_lower && p->total_missing == 0 && !have && p->prefilled_N != out->N_lower) {
         // nothing missing: N_ij == m for every pair (what grm.cpp:291 yields); fill on the host while the copies run
         const int nt = (int)std::min<int64_t>(16, std::max<int64_t>(1, p->band_count >> 22));
         std::vector<std::thread> th;

@@ -195,6 +195,39 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
             tc_fence_after();
             float4* Stile = reinterpret_cast<float4*>(S + (size_t)t * (TILE_M * TILE_N));
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * TILE_N;
+            if (!INT_ACC && epi_red) {
+                // Fire-and-forget vector reductions in L2 (red.global.add.v4.f32): every element of S belongs to exactly one
+                // CTA of a launch and launches are stream-ordered, so the sum is the same round-to-nearest add as a
+                // read-modify-write, without the epilogue waiting for S to arrive from HBM.  The TMEM reads are ping-ponged
+                // (the next 32 columns are in flight while the current ones go out), and the accumulators are handed back to
+                // the MMA issuer as soon as the last columns sit in registers - before their reductions are issued.
+                auto red8 = [&](int c0, const uint32_t (&v)[32]) {
+#pragma unroll
+                    for (int g = 0; g < 8; g++) {
+                        float4* p = Stile + (size_t)(c0 / 4 + g) * TILE_M + r;
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v[4 * g + 0]), "r"(v[4 * g + 1]),
+                                     "r"(v[4 * g + 2]), "r"(v[4 * g + 3])
+                                     : "memory");
+                    }
+                };
+                uint32_t va[32], vb[32];
+                tmem_ld_32x32(taddr, va);
+#pragma unroll 1
+                for (int c0 = 0; c0 < TILE_N; c0 += 64) {
+                    tmem_ld_wait();                        // va = columns c0 .. c0+31
+                    tmem_ld_32x32(taddr + c0 + 32, vb);
+                    red8(c0, va);
+                    tmem_ld_wait();                        // vb = columns c0+32 .. c0+63
+                    if (c0 + 64 < TILE_N) tmem_ld_32x32(taddr + c0 + 64, va);
+                    else {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tempty_bar);
+                    }
+                    red8(c0 + 32, vb);
+                }
+                continue;
+            }
 #pragma unroll 1
             for (int c0 = 0; c0 < TILE_N; c0 += 32) {
                 uint32_t v[32];
@@ -211,13 +244,6 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                         o.z += __float2int_rn(__uint_as_float(v[4 * g + 2]));
                         o.w += __float2int_rn(__uint_as_float(v[4 * g + 3]));
                         *pi = o;
-                    } else if (epi_red) {
-                        // fire-and-forget vector reduction in L2: every element of S belongs to exactly one CTA of a launch
-                        // and launches are stream-ordered, so the sum is the same round-to-nearest add as the read-modify-write
-                        // below, without the epilogue waiting for S to arrive from HBM
-                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v[4 * g + 0]), "r"(v[4 * g + 1]),
-                                     "r"(v[4 * g + 2]), "r"(v[4 * g + 3])
-                                     : "memory");
                     } else {
                         float4 o = *p;
                         o.x += __uint_as_float(v[4 * g + 0]);
