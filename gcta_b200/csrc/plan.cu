@@ -404,9 +404,18 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         int64_t head = round_up((m + 63) / 64, 64);
         if (const char* e = getenv("GCTA_B200_HEAD_CHUNK")) head = round_up(std::max<int64_t>(0, atoll(e)), 64);
         if (a->chunk_snps > 0 || m < 65536 || head >= kc) head = 0;
+        // Lengths in ascending order, so that the remainder is not the last chunk: a run that delivers to host buffers
+        // downloads its band behind the last chunk's SYRK (run_last_chunk_pipelined), and with several GPUs the band's
+        // copy (0.6 - 2.5 GB per rank) does not fit behind a short remainder (measured at 8 GPUs: the last chunk was 8 %
+        // of the SNPs = 18 ms of compute against 25 ms of copy).
+        std::vector<int64_t> lens;
+        for (int64_t len = head > 0 ? head : kc, done = 0; done < m; len = std::min<int64_t>(kc, 2 * len)) {
+            lens.push_back(std::min<int64_t>(len, m - done));
+            done += lens.back();
+        }
+        std::stable_sort(lens.begin(), lens.end());
         p->cstart.assign(1, 0);
-        for (int64_t len = head > 0 ? head : kc; p->cstart.back() < m; len = std::min<int64_t>(kc, 2 * len))
-            p->cstart.push_back(std::min<int64_t>(m, p->cstart.back() + len));
+        for (int64_t l : lens) p->cstart.push_back(p->cstart.back() + l);
         PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz * planes, err, errcap));
         if (p->stream_bed) {
             // two ring buffers, each large enough for the file rows any one chunk reads
