@@ -25,6 +25,8 @@ def main():
     lines = [("f_bench_cfg1.json", "cfg1, 1 GPU"), ("f_bench_cfg2.json", "cfg2, 1 GPU"), ("f_bench_cfg3.json", "cfg3, 1 GPU (with --cpu-full)"),
              ("f_bench_cfg5.json", "cfg5, 1 GPU"), ("f_bench_reference.json", "--impl reference"), ("n8b_bench_cfg3_n2.json", "cfg3, 2 GPUs"),
              ("n8b_bench_cfg3_n4.json", "cfg3, 4 GPUs"), ("n8c_bench_cfg3.json", "cfg3, 8 GPUs"), ("n8b_bench_cfg4.json", "cfg4, 8 GPUs"),
+             ("f_bench_cfg4_n1.json", "cfg4, 1 GPU (--force: BASELINE names it on 8)"), ("n2b_bench_cfg1.json", "cfg1, 2 GPUs (--force)"),
+             ("n2b_bench_cfg2.json", "cfg2, 2 GPUs (--force)"), ("n2b_bench_cfg5.json", "cfg5, 2 GPUs (--force)"), ("n2b_bench_cfg4.json", "cfg4, 2 GPUs (--force)"),
              ("n8_bench_cfg3_prefetch.json", "cfg3, 8 GPUs, GCTA_B200_E2E_PREFETCH=1 (diagnosis run, before the two e2e fixes)")]
     with open(os.path.join(P, "r02_bench_lines.jsonl"), "w") as f:
         for fn, what in lines:
