@@ -219,6 +219,12 @@ def main_ours(a, rank, world, local_rank):
     k1_bytes = m * ((n + 3) // 4 + 2 * ldz_rank)
     k1_gbps = k1_bytes * a.steps / (dec_ms * 1e-3) / 1e9 if dec_ms > 0 else 0.0
     k1_gbps_min = -max_over_ranks(-k1_gbps)
+    # the same two kernels timed alone (outside every timed region)
+    alone = None
+    if not a.no_decode_alone and a.miss == 0:
+        time.sleep(0.5)   # let the board fall below its power cap
+        alone = decode_alone(plan, n, m, row_begin, row_end)
+    alone_gbps_min = -max_over_ranks(-(alone[1] if alone else 0.0))
 
     # ---------------- end to end through the C ABI with host buffers ("e2e") ----------------
     e2e = None
@@ -429,7 +435,11 @@ def main_ours(a, rank, world, local_rank):
                          "traffic": k2_traffic(n, world, chain, m), "launches_per_step": k2_launches},
             "roofline_decode": {"kernel": "snp_stats_kernel + decode_emit_diag_kernel (K1s + K1f)", "bound": "hbm", "achieved": k1_gbps_min,
                                 "peak": hbm, "unit": "GB/s", "frac": k1_gbps_min / hbm, "peak_source": which + " (copy bandwidth)",
-                                "bytes_per_step_rank0": k1_bytes, "traffic": None,
+                                "bytes_per_step_rank0": k1_bytes, "traffic": k1_traffic(n, world),
+                                "achieved_alone": alone_gbps_min or None, "frac_alone": (alone_gbps_min / hbm) if alone_gbps_min else None,
+                                "alone": (f"the same kernels on one {alone[2]}-SNP chunk with no SYRK launch between them, so not under the step's power cap "
+                                          f"(SM at its maximum clock, the condition the copy peak was measured under): rank 0 {alone[0]:.3f} ms per chunk; "
+                                          "CUDA events, 3 warm-up + 10 timed passes, outside every timed region") if alone else None,
                                 "note": "min over ranks; per-rank algorithmic bytes M x (ceil(n/4) + 2 ldz_rank) / that rank's decode event time"},
             "clocks": clocks, "gpu_launches": launches_total,
             "per_rank": [{"rows": [int(r[0]), int(r[1])], "ms_total": round(r[2], 2), "ms_syrk": round(r[3], 2), "ms_decode": round(r[4], 2),
@@ -463,6 +473,71 @@ def main_ours(a, rank, world, local_rank):
         print(json.dumps(line))
     plan.close()
     ranks.close()
+
+
+def decode_alone(plan, n, m, row_begin, row_end):
+    """K1s + K1f of this rank on one Z chunk, timed ALONE (CUDA events on torch's stream, 3 warm-up passes, 10 timed): no SYRK
+    between the launches, so the board is below its power cap and the SM clock at its maximum - the condition the HBM
+    copy peak of MEASURED_PEAKS.json was measured under.  -> (ms per chunk, algorithmic GB/s, SNPs in the chunk)"""
+    import ctypes as C
+    import torch
+    from gcta_b200 import abi
+    P, I64, I32 = C.c_void_p, C.c_int64, C.c_int32
+    L = abi.lib()
+    L.gcta_b200_plan_own_bed.restype = C.c_void_p
+    bed_ptr = L.gcta_b200_plan_own_bed(plan._h)
+    if not bed_ptr:
+        return None
+    pitch = plan.use_device_bed(None)
+    kc = min(m, 171136)
+    ldz = (max(row_end, 1) + 255) // 256 * 256
+    km = np.zeros(pitch // 4, dtype=np.uint32)
+    km[: n // 16] = np.uint32(0x55555555)
+    for f in range(n // 16 * 16, n):
+        km[f >> 4] |= np.uint32(1 << ((f & 15) * 2))
+    d_km = torch.from_numpy(km).cuda()
+    try:
+        Z = torch.empty(((kc + 63) // 64 * 64, ldz), dtype=torch.int16, device="cuda")
+    except RuntimeError:
+        return None   # not enough free HBM for a second Z chunk next to the plan's
+    mu = torch.zeros(kc, dtype=torch.float64, device="cuda")
+    cnt = torch.zeros(kc, dtype=torch.int32, device="cuda")
+    sm = torch.zeros(kc, dtype=torch.int32, device="cuda")
+    zlut = torch.zeros(kc * 8, dtype=torch.float32, device="cuda")
+    tot = torch.zeros(1, dtype=torch.int64, device="cuda")
+    diag = torch.zeros(n, dtype=torch.float64, device="cuda")
+    nii = torch.zeros(n, dtype=torch.int32, device="cuda")
+    st = P(torch.cuda.current_stream().cuda_stream)
+
+    def once():
+        abi.call("gcta_b200_snp_stats", P(bed_ptr), I64(pitch), I64(n), P(d_km.data_ptr()), I64(n), P(None), I64(0), I64(kc), P(None), I32(0),
+                 P(mu.data_ptr()), P(cnt.data_ptr()), P(sm.data_ptr()), P(zlut.data_ptr()), P(tot.data_ptr()), st)
+        abi.call("gcta_b200_decode_emit_diag", P(bed_ptr), I64(pitch), I64(n), P(None), I64(0), I64(kc), P(zlut.data_ptr()), I32(abi.FP16),
+                 P(Z.data_ptr()), I64(ldz), P(diag.data_ptr()), P(nii.data_ptr()), I64(row_begin), I64(row_end), P(None), st)
+
+    for _ in range(3):
+        once()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(10):
+        once()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    del Z
+    torch.cuda.empty_cache()
+    return ms, kc * ((n + 3) // 4 + 2 * ldz) / ms / 1e6, kc
+
+
+def k1_traffic(n, world):
+    """dram bytes (read + write) of K1s + K1f per full-length Z chunk from the committed ncu capture, when this run has
+    the captured shape (n individuals, whole triangle on one GPU); else None."""
+    p = os.path.join(ROOT, "profiles", "k1_traffic.json")
+    if world != 1 or not os.path.exists(p):
+        return None
+    d = json.load(open(p))
+    return d["dram_bytes_total"] if d.get("n") == n else None   # per launch pair of 171,136 SNPs; algorithmic: d["algorithmic_bytes"]
 
 
 def k2_traffic(n, world, chain, m):
@@ -499,6 +574,7 @@ def main():
     ap.add_argument("--force", action="store_true", help="run a configuration on a GPU count BASELINE.json does not name it on")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-cold", action="store_true")
+    ap.add_argument("--no-decode-alone", action="store_true")
     ap.add_argument("--parity-sub", type=int, default=256, help="individuals in the sub-block parity check")
     a = ap.parse_args()
     global SEED
