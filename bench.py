@@ -212,7 +212,8 @@ def main_ours(a, rank, world, local_rank):
     syrk_tflops_min = -max_over_ranks(-syrk_tflops)
     chain = int(os.environ.get("GCTA_B200_CHAIN_SNPS", "32768")) or (1 << 40)
     chain = max(128, chain // 128 * 128)
-    k2_launches = sum(-(-((e - b + 63) // 64 * 64) // chain) for b, e in plan.chunk_rows())   # K2 launches per step on this rank
+    k2_chains = sum(-(-((e - b + 63) // 64 * 64) // chain) for b, e in plan.chunk_rows())   # TMEM chains per step on this rank
+    k2_launches = len(plan.chunk_rows())   # all chains of a Z chunk run in one launch
     # Decode stage (K1s + K1f, HBM bound), SURVEY.md 8d: algorithmic bytes of THIS rank = M x (packed row read once +
     # 16-bit Z row of the band's ldz columns written once); the second read of the packed rows by K1f is not algorithmic
     ldz_rank = (max(row_end, 1) + 255) // 256 * 256
@@ -432,7 +433,8 @@ def main_ours(a, rank, world, local_rank):
             "roofline": {"kernel": "syrk_tiles_kernel (K2)", "bound": "tensor", "achieved": syrk_tflops_min, "peak": burst, "unit": "TFLOP/s",
                          "frac": syrk_tflops_min / burst, "frac_of_sustained_peak": syrk_tflops_min / sust, "sustained_peak": sust,
                          "peak_source": which + " (burst bf16; min over ranks of algorithmic flops / K2 event time)",
-                         "traffic": k2_traffic(n, world, chain, m), "launches_per_step": k2_launches},
+                         "traffic": k2_traffic(n, world, chain, m), "launches_per_step": k2_launches, "tmem_chains_per_step": k2_chains,
+                         "traffic_note": "dram bytes of the captured full-length launch (171,136 SNPs = 6 chains of 32,768) when this run launches that shape"},
             "roofline_decode": {"kernel": "snp_stats_kernel + decode_emit_diag_kernel (K1s + K1f)", "bound": "hbm", "achieved": k1_gbps_min,
                                 "peak": hbm, "unit": "GB/s", "frac": k1_gbps_min / hbm, "peak_source": which + " (copy bandwidth)",
                                 "bytes_per_step_rank0": k1_bytes, "traffic": k1_traffic(n, world),
@@ -548,7 +550,7 @@ def k2_traffic(n, world, chain, m):
     if world != 1 or not os.path.exists(p):
         return None
     d = json.load(open(p))
-    if d.get("n") != n or d.get("snps_per_launch") != min(chain, m):
+    if d.get("n") != n or d.get("chain_snps") != chain or d.get("snps_per_launch") > m:
         return None
     return d["dram_bytes_read"] + d["dram_bytes_write"]
 

@@ -845,12 +845,8 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
         const int64_t r0 = (b0 + (int64_t)gi * R) * TILE_M, r1 = std::min<int64_t>((b0 + (int64_t)ge * R) * TILE_M, p->row_end);
         gi = ge;
         if (t1 <= t0) continue;
-        for (int64_t ks = 0; ks < kp && !rc; ks += p->chain) {   // one launch per TMEM chain, as in plan_run_impl
-            const uint16_t* Zs = (const uint16_t*)Z + ks * p->ldz;
-            rc = gcta_b200_syrk_tiles_ab(Zs, Zs, p->ldz, std::min<int64_t>(p->chain, kp - ks), p->operand, p->d_tiles + 2 * t0, t1 - t0,
-                                         p->d_S + t0 * (TILE_M * TILE_N), st, err, errcap);
-            if (ks > 0) ++*launches;
-        }
+        rc = gcta_b200_syrk_tiles_chained(Z, Z, p->ldz, kp, std::min<int64_t>(p->chain, round_up(kp, 128)), p->operand, p->d_tiles + 2 * t0, t1 - t0,
+                                          p->d_S + t0 * (TILE_M * TILE_N), st, err, errcap);   // TMEM chains as in plan_run_impl
         if (rc) break;
         const int64_t seg_base = r0 * (r0 + 1) / 2, seg_cnt = r1 * (r1 + 1) / 2 - seg_base;
         rc = gcta_b200_finalize_tiles(p->d_S + t0 * (TILE_M * TILE_N), nullptr, (int32_t)p->m, p->d_tiles + 2 * t0, t1 - t0, p->n, p->d_keep, p->d_diag,
@@ -998,14 +994,10 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     auto syrk = [&](const void* Za, const void* Zb, int64_t kp, int op, void* outp, bool int_acc, cudaStream_t s) -> int {
         if (p->d_pairs) return gcta_b200_syrk_pairs(Za, Zb, p->ldz, kp, op, p->d_pairs, p->npairs, outp, int_acc, s, err, errcap);
         if (int_acc) return gcta_b200_count_tiles(Za, p->ldz, kp, op, p->d_tiles, p->ntiles, (int32_t*)outp, s, err, errcap);
-        // one launch per TMEM chain (p->chain SNPs): see plan_create
-        for (int64_t ks = 0; ks < kp; ks += p->chain) {
-            const int64_t kl = std::min<int64_t>(p->chain, kp - ks);
-            int rc = gcta_b200_syrk_tiles_ab((const uint16_t*)Za + ks * p->ldz, (const uint16_t*)Zb + ks * p->ldz, p->ldz, kl, op, p->d_tiles,
-                                             p->ntiles, (float*)outp, s, err, errcap);
-            if (rc) return rc;
-            if (ks > 0) launches++;
-        }
+        // TMEM chains of p->chain SNPs (see plan_create), all inside one launch
+        int rc = gcta_b200_syrk_tiles_chained(Za, Zb, p->ldz, kp, std::min<int64_t>(p->chain, round_up(kp, 128)), op, p->d_tiles, p->ntiles,
+                                              (float*)outp, s, err, errcap);
+        if (rc) return rc;
         return 0;
     };
     GB_CUDA(cudaEventRecord(p->events[0], st));

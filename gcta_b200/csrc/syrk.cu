@@ -18,6 +18,7 @@
 //                       in HBM (S carries the sum over SNP chunks)
 #include <cuda.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cstdlib>
 #include <map>
@@ -79,9 +80,14 @@ template <bool INT_ACC, int EB = 2>
 __global__ void __launch_bounds__(SYRK_THREADS, 1)
 syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                   const int2* __restrict__ tiles, int ntiles, int nkb, float* __restrict__ S, uint32_t idesc,
-                  unsigned int* wave_counter, int epi_red)
+                  unsigned int* wave_counter, int epi_red, int ckb)
 {
     using G = Geo<EB>;
+    // Work items = (chain, tile), chain-major: the K blocks of the launch are cut into chains of `ckb` blocks, each of
+    // which is one accumulation in TMEM followed by an epilogue into S (ckb == nkb: one chain, items == tiles).  Running
+    // all chains of a Z chunk in ONE launch leaves one partly filled last wave per chunk instead of one per chain.
+    const int nchains = (nkb + ckb - 1) / ckb;
+    const int nitems = ntiles * nchains;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = (uint64_t*)(smem + NUM_STAGES * STAGE_BYTES);
@@ -118,9 +124,9 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            const int nwaves = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;
+            const int nwaves = (nitems + (int)gridDim.x - 1) / (int)gridDim.x;
             for (int w = 0; w < nwaves; w++) {
-                const int t = blockIdx.x + w * (int)gridDim.x;
+                const int u = blockIdx.x + w * (int)gridDim.x;
                 if (wave_counter) {
                     // Wave barrier (cooperative launch): every CTA starts wave w together.  CTAs that share
                     // an operand panel then stream it within the few k-blocks of history L2 keeps per CTA, instead of
@@ -129,10 +135,12 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                     const unsigned int target = gridDim.x * (unsigned int)(w + 1);
                     while (*reinterpret_cast<volatile unsigned int*>(wave_counter) < target) {}
                 }
-                if (t >= ntiles) break;
-                const int2 tl = tiles[t];
+                if (u >= nitems) break;
+                const int chain = u / ntiles;
+                const int2 tl = tiles[u - chain * ntiles];
                 const int row0 = tl.x * TILE_M, col0 = tl.y * TILE_N;
-                for (int kb = 0; kb < nkb; kb++) {
+                const int kb0 = chain * ckb, kb1 = min(nkb, kb0 + ckb);
+                for (int kb = kb0; kb < kb1; kb++) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* st = smem + stage * STAGE_BYTES;
                     mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
@@ -154,10 +162,11 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+            for (int u = blockIdx.x; u < nitems; u += gridDim.x, it++) {
                 mbar_wait(tempty_bar, (it & 1) ^ 1);  // epilogue has drained the previous tile
                 tc_fence_after();
-                for (int kb = 0; kb < nkb; kb++) {
+                const int kb0 = (u / ntiles) * ckb, kb1 = min(nkb, kb0 + ckb);
+                for (int kb = kb0; kb < kb1; kb++) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
@@ -168,7 +177,7 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                     for (int k4 = 0; k4 < G::KB / G::UK; k4++) {
                         // one MMA consumes UK SNPs = UK/8 swizzle atoms of 8 rows x 128 B further along K
                         const uint64_t adv = (uint64_t)((k4 * G::K_STEP_BYTES) >> 4);
-                        const uint32_t acc = (kb | k4) != 0 ? 1u : 0u;
+                        const uint32_t acc = (kb != kb0 || k4 != 0) ? 1u : 0u;   // a chain starts from zero
                         if (EB == 2) {
                             umma_f16(tmem_base, a0_desc + adv, b_desc + adv, idesc, acc);
                             umma_f16(tmem_base + TILE_N, a1_desc + adv, b_desc + adv, idesc, acc);
@@ -190,9 +199,10 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         const int half = (warp - 2) >> 2;    // which accumulator / 128-row half of the tile
         const int r = half * UMMA_M + q * 32 + lane;
         int it = 0;
-        for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
+        for (int u = blockIdx.x; u < nitems; u += gridDim.x, it++) {
             mbar_wait(tfull_bar, it & 1);
             tc_fence_after();
+            const int t = u % ntiles;
             float4* Stile = reinterpret_cast<float4*>(S + (size_t)t * (TILE_M * TILE_N));
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * TILE_N;
             if (!INT_ACC && epi_red) {
@@ -308,7 +318,7 @@ static EncodeTiledFn get_encode_fn()
 }  // namespace gb
 
 static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,
-                       int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
+                       int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap, int64_t chain_snps = 0)
 {
     using namespace gb;
     GB_ARG(d_Z && d_Zb && d_tiles && d_S, "syrk: null pointer");
@@ -356,16 +366,27 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
         GB_CUDA(cudaFuncSetAttribute(syrk_tiles_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SYRK_SMEM));
         attr_set[dev] = true;
     }
-    int grid = (int)(ntiles < sms ? ntiles : sms);
     const int2* tl = reinterpret_cast<const int2*>(d_tiles);
     int nt = (int)ntiles, nkb = (int)(kc_pad / kblock);
     uint32_t id = idesc;
-    typedef void (*KernelFn)(const CUtensorMap, const CUtensorMap, const int2*, int, int, float*, uint32_t, unsigned int*, int);
+    typedef void (*KernelFn)(const CUtensorMap, const CUtensorMap, const int2*, int, int, float*, uint32_t, unsigned int*, int, int);
     const KernelFn kfn = eb == 1 ? (KernelFn)syrk_tiles_kernel<true, 1> : (int_acc ? (KernelFn)syrk_tiles_kernel<true> : (KernelFn)syrk_tiles_kernel<false>);
+    // GCTA_B200_EPI_RED=0: epilogue as read-modify-write instead of red.global.add.v4.f32
+    static const int epi_red_env = !(getenv("GCTA_B200_EPI_RED") && atoi(getenv("GCTA_B200_EPI_RED")) == 0);
+    int epi_red = epi_red_env && !int_acc;
+    // chains inside one launch need the reduction epilogue (two chains of a tile are added into S by different CTAs)
+    int ckb = nkb;
+    if (chain_snps > 0 && chain_snps < kc_pad) {
+        GB_ARG(epi_red && chain_snps % kblock == 0, "syrk: chains inside a launch need the reduction epilogue and a chain length that is a multiple of the K block");
+        ckb = (int)(chain_snps / kblock);
+    }
+    const int64_t nitems = (int64_t)nt * ((nkb + ckb - 1) / ckb);
+    GB_ARG(nitems < (1ll << 31), "syrk: too many work items for one launch");
+    int grid = (int)(nitems < sms ? nitems : sms);
     unsigned int* counter = nullptr;
     // Wave barrier on by default (cfg3: +10 % whole-job, HBM reads of K2 -40 %; profiles/README.md); GCTA_B200_WAVESYNC=0 disables
     static const bool wave_sync = !(getenv("GCTA_B200_WAVESYNC") && atoi(getenv("GCTA_B200_WAVESYNC")) == 0);
-    if (wave_sync && ntiles > grid) {
+    if (wave_sync && nitems > grid) {
         static std::atomic<unsigned int*> cached[64] = {};
         const int slot = wave_slot_of(dev, stream);
         if (slot >= 0) {
@@ -377,23 +398,20 @@ static int syrk_launch(bool int_acc, const void* d_Z, const void* d_Zb, int64_t 
             counter = base + slot;
         }
     }
-    // GCTA_B200_EPI_RED=0: epilogue as read-modify-write instead of red.global.add.v4.f32
-    static const int epi_red_env = !(getenv("GCTA_B200_EPI_RED") && atoi(getenv("GCTA_B200_EPI_RED")) == 0);
-    int epi_red = epi_red_env && !int_acc;
     if (counter) {
         // the barrier needs all CTAs resident at once: cooperative launch guarantees it (or fails loudly)
         GB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), (cudaStream_t)stream));
-        void* args[] = {&tmap, &tmapB, &tl, &nt, &nkb, &d_S, &id, &counter, &epi_red};
+        void* args[] = {&tmap, &tmapB, &tl, &nt, &nkb, &d_S, &id, &counter, &epi_red, &ckb};
         cudaError_t ce = cudaLaunchCooperativeKernel((const void*)kfn, dim3(grid), dim3(SYRK_THREADS), args, SYRK_SMEM, (cudaStream_t)stream);
         if (ce == cudaErrorCooperativeLaunchTooLarge || ce == cudaErrorNotSupported || ce == cudaErrorLaunchOutOfResources) {
             // e.g. part of the GPU is held by another context: run the same kernel without the barrier
             cudaGetLastError();
             counter = nullptr;
-            kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter, epi_red);
+            kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter, epi_red, ckb);
         } else
             GB_CUDA(ce);
     } else
-        kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter, epi_red);
+        kfn<<<grid, SYRK_THREADS, SYRK_SMEM, (cudaStream_t)stream>>>(tmap, tmapB, tl, nt, nkb, d_S, id, counter, epi_red, ckb);
     GB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -409,6 +427,25 @@ extern "C" int gcta_b200_syrk_tiles_ab(const void* d_Za, const void* d_Zb, int64
                                        const int32_t* d_tiles, int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
 {
     return syrk_launch(false, d_Za, d_Zb, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap);
+}
+
+// S += Za^T Zb with the contraction cut into chains of chain_snps SNPs (see the kernel): one launch when the reduction
+// epilogue is on (the default), else one launch per chain
+extern "C" int gcta_b200_syrk_tiles_chained(const void* d_Za, const void* d_Zb, int64_t ldz, int64_t kc_pad, int64_t chain_snps, int32_t operand,
+                                            const int32_t* d_tiles, int64_t ntiles, float* d_S, void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(chain_snps > 0 && chain_snps % 128 == 0, "syrk_tiles_chained: chain_snps must be a positive multiple of 128");
+    static const bool red = !(getenv("GCTA_B200_EPI_RED") && atoi(getenv("GCTA_B200_EPI_RED")) == 0);
+    static const bool one_launch = !(getenv("GCTA_B200_CHAIN_LAUNCHES") && atoi(getenv("GCTA_B200_CHAIN_LAUNCHES")) != 0);
+    if (chain_snps >= kc_pad) return syrk_launch(false, d_Za, d_Zb, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap);
+    if (red && one_launch) return syrk_launch(false, d_Za, d_Zb, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap, chain_snps);
+    for (int64_t ks = 0; ks < kc_pad; ks += chain_snps) {
+        int rc = syrk_launch(false, (const uint16_t*)d_Za + ks * ldz, (const uint16_t*)d_Zb + ks * ldz, ldz, std::min<int64_t>(chain_snps, kc_pad - ks),
+                             operand, d_tiles, ntiles, d_S, stream, err, errcap);
+        if (rc) return rc;
+    }
+    return 0;
 }
 
 extern "C" int gcta_b200_count_tiles(const void* d_OK, int64_t ldz, int64_t kc_pad, int32_t operand, const int32_t* d_tiles,

@@ -303,6 +303,14 @@ int gcta_b200_syrk_tiles_ab(const void* d_Za, const void* d_Zb, int64_t ldz, int
                             const int32_t* d_tiles, int64_t ntiles, float* d_S,
                             void* stream, char* err, size_t errcap);
 
+/* K2 with the contraction cut into TMEM chains of chain_snps SNPs (a multiple of 128): each chain is one FP32 accumulation
+ * on the tensor cores, added into S by a round-to-nearest reduction - long chains of same-sign products (related
+ * individuals) otherwise drift by the accumulator's truncation (grm.cpp:288-289 accumulates in double).  All chains run
+ * in one launch.  What the plan calls with its default chain of 32,768 SNPs. */
+int gcta_b200_syrk_tiles_chained(const void* d_Za, const void* d_Zb, int64_t ldz, int64_t kc_pad, int64_t chain_snps, int32_t operand,
+                                 const int32_t* d_tiles, int64_t ntiles, float* d_S,
+                                 void* stream, char* err, size_t errcap);
+
 /* K2 as CTA pairs (tcgen05.mma.cta_group::2): two SMs work on two vertically adjacent 256x256 tiles and share the
  * column operand, each staging only half of it (csrc/syrk2.cu).  Same tile storage as gcta_b200_syrk_tiles.
  *   gcta_b200_pair_list  host helper: from a band's tile list (gcta_b200_tile_list order = storage order) to the work

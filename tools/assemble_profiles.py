@@ -67,7 +67,7 @@ def main():
                         ", ".join(f"{k} {v:.2f} ({100 * v / tt:.2f} %)" for k, v in ph.items()) + f"; step {d['ms_per_step']:.1f} ms\n")
     # ncu summaries
     for rep, out in (("r02_decode_final_n50000_m171136.ncu-rep", "r02_decode_ncu_full_n50000_m171136.txt"),
-                     ("r02_syrk_final_n50000_m32768.ncu-rep", "r02_syrk_ncu_full_n50000_m32768.txt")):
+                     ("r02_syrk_final_n50000_m171136.ncu-rep", "r02_syrk_ncu_full_n50000_m171136.txt")):
         src = os.path.join(G, rep)
         if os.path.exists(src):
             txt = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_summary.py"), src], capture_output=True, text=True).stdout
@@ -75,9 +75,9 @@ def main():
             if "syrk" in rep:
                 m = {k: float(v) for k, v in re.findall(r"(dram__bytes_(?:read|write)\.sum) \| Gbyte \| ([0-9.]+)", txt)[:2]}
                 json.dump({"kernel": "syrk_tiles_kernel", "source": "profiles/" + out + " (ncu --set full, first launch)", "n": 50000,
-                           "snps_per_launch": 32768, "dram_bytes_read": int(m["dram__bytes_read.sum"] * 1e9),
-                           "dram_bytes_write": int(m["dram__bytes_write.sum"] * 1e9), "unique_operand_bytes": 32768 * 50176 * 2,
-                           "note": "per launch of one 32,768-SNP chain over the whole triangle of n = 50,000 (the default bench launches this shape)"},
+                           "snps_per_launch": 171136, "chain_snps": 32768, "dram_bytes_read": int(m["dram__bytes_read.sum"] * 1e9),
+                           "dram_bytes_write": int(m["dram__bytes_write.sum"] * 1e9), "unique_operand_bytes": 171136 * 50176 * 2,
+                           "note": "per launch over one full-length Z chunk (171,136 SNPs = 6 TMEM chains of 32,768) of the whole triangle of n = 50,000 - the largest launch of the default bench"},
                           open(os.path.join(P, "k2_traffic.json"), "w"), indent=1)
     # SASS histogram
     with open(os.path.join(P, "r02_sass_histogram.txt"), "w") as f:
