@@ -992,7 +992,15 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     int launches = 0;
     // K2 dispatch: out (+)= Za^T Zb over the band's tiles, as single CTAs (syrk.cu) or as CTA pairs (syrk2.cu)
     auto syrk = [&](const void* Za, const void* Zb, int64_t kp, int op, void* outp, bool int_acc, cudaStream_t s) -> int {
-        if (p->d_pairs) return gcta_b200_syrk_pairs(Za, Zb, p->ldz, kp, op, p->d_pairs, p->npairs, outp, int_acc, s, err, errcap);
+        if (p->d_pairs) {   // CTA-pair kernel: one launch per TMEM chain (counts need no chains: exact)
+            const int64_t step = int_acc ? kp : p->chain, eb = op == GCTA_B200_E4M3 ? 1 : 2;
+            for (int64_t ks = 0; ks < kp; ks += step) {
+                int rc = gcta_b200_syrk_pairs((const uint8_t*)Za + ks * p->ldz * eb, (const uint8_t*)Zb + ks * p->ldz * eb, p->ldz, std::min<int64_t>(step, kp - ks), op,
+                                              p->d_pairs, p->npairs, outp, int_acc, s, err, errcap);
+                if (rc) return rc;
+            }
+            return 0;
+        }
         if (int_acc) return gcta_b200_count_tiles(Za, p->ldz, kp, op, p->d_tiles, p->ntiles, (int32_t*)outp, s, err, errcap);
         // TMEM chains of p->chain SNPs (see plan_create), all inside one launch
         int rc = gcta_b200_syrk_tiles_chained(Za, Zb, p->ldz, kp, std::min<int64_t>(p->chain, round_up(kp, 128)), op, p->d_tiles, p->ntiles,

@@ -436,10 +436,17 @@ extern "C" int gcta_b200_syrk_tiles_chained(const void* d_Za, const void* d_Zb, 
 {
     using namespace gb;
     GB_ARG(chain_snps > 0 && chain_snps % 128 == 0, "syrk_tiles_chained: chain_snps must be a positive multiple of 128");
-    static const bool red = !(getenv("GCTA_B200_EPI_RED") && atoi(getenv("GCTA_B200_EPI_RED")) == 0);
-    static const bool one_launch = !(getenv("GCTA_B200_CHAIN_LAUNCHES") && atoi(getenv("GCTA_B200_CHAIN_LAUNCHES")) != 0);
+    const bool red = !(getenv("GCTA_B200_EPI_RED") && atoi(getenv("GCTA_B200_EPI_RED")) == 0);
+    const bool one_launch = !(getenv("GCTA_B200_CHAIN_LAUNCHES") && atoi(getenv("GCTA_B200_CHAIN_LAUNCHES")) != 0);
     if (chain_snps >= kc_pad) return syrk_launch(false, d_Za, d_Zb, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap);
-    if (red && one_launch) return syrk_launch(false, d_Za, d_Zb, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap, chain_snps);
+    // Two chains of one tile are added into S by different CTAs.  With at least four waves of tiles they run waves apart
+    // (items are chain-major and every wave starts at a grid-wide barrier), so the additions keep their order and the
+    // result is reproducible bit for bit; smaller tile lists get one launch per chain.
+    int dev = 0, sms = 0;
+    GB_CUDA(cudaGetDevice(&dev));
+    GB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (red && one_launch && ntiles >= 4 * (int64_t)sms)
+        return syrk_launch(false, d_Za, d_Zb, ldz, kc_pad, operand, d_tiles, ntiles, d_S, stream, err, errcap, chain_snps);
     for (int64_t ks = 0; ks < kc_pad; ks += chain_snps) {
         int rc = syrk_launch(false, (const uint16_t*)d_Za + ks * ldz, (const uint16_t*)d_Zb + ks * ldz, ldz, std::min<int64_t>(chain_snps, kc_pad - ks),
                              operand, d_tiles, ntiles, d_S, stream, err, errcap);

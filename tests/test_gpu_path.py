@@ -334,3 +334,25 @@ def test_counts_chunk_by_chunk_equal_the_separate_pass(monkeypatch):
     assert o2.total_missing > 0
     Aref, Nref, _ = oracle.make_grm_numpy(late, n)
     check_grm(A2, N2, pack_lower(Aref), pack_lower(Nref))
+
+
+def test_short_tmem_chains_and_the_cta_pair_kernel(monkeypatch):
+    """GCTA_B200_CHAIN_SNPS cuts the contraction into TMEM chains (all in one launch by default, one launch per chain with
+    GCTA_B200_CHAIN_LAUNCHES=1 or with the CTA-pair kernel, GCTA_B200_2CTA=1): the same GRM up to FP32 summation order"""
+    n, m = 9000, 9000      # 630 tiles: enough waves for the one-launch form (smaller tile lists always launch per chain)
+    bed = synth.make_bed_payload(81, n, m, miss_rate=0.02)
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n)
+    res = {}
+    for name, env in [("whole", {"GCTA_B200_CHAIN_SNPS": "0"}), ("c256", {"GCTA_B200_CHAIN_SNPS": "256"}),
+                      ("c256_launches", {"GCTA_B200_CHAIN_SNPS": "256", "GCTA_B200_CHAIN_LAUNCHES": "1"}),
+                      ("pairs_c512", {"GCTA_B200_CHAIN_SNPS": "512", "GCTA_B200_2CTA": "1"})]:
+        for k in ("GCTA_B200_CHAIN_SNPS", "GCTA_B200_CHAIN_LAUNCHES", "GCTA_B200_2CTA"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        A, N, _, _ = abi.make_grm(bed, n, m, chunk_snps=4096)
+        check_grm(A, N, pack_lower(Aref), pack_lower(Nref))
+        res[name] = A
+    assert np.array_equal(res["c256"], res["c256_launches"])          # same chains, same order of additions
+    assert np.abs(res["c256"].astype(np.float64) - res["whole"]).max() < 2e-6
+    assert np.abs(res["pairs_c512"].astype(np.float64) - res["whole"]).max() < 2e-6
