@@ -20,7 +20,7 @@ IPC_HANDLE_BYTES = 64   # GCTA_B200_IPC_HANDLE_BYTES
 EXPORTS = [
     "gcta_b200_make_grm", "gcta_b200_make_grm_multi", "gcta_b200_plan_set_chunk_hook", "gcta_b200_plan_own_bed", "gcta_b200_plan_create", "gcta_b200_plan_upload", "gcta_b200_plan_synth", "gcta_b200_plan_download_bed",
     "gcta_b200_plan_run", "gcta_b200_plan_run_streamed", "gcta_b200_plan_download", "gcta_b200_plan_device_results", "gcta_b200_plan_destroy",
-    "gcta_b200_bed_decode", "gcta_b200_snp_stats", "gcta_b200_decode_emit_diag", "gcta_b200_diag_accum", "gcta_b200_diag_accum_static", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles", "gcta_b200_syrk_tiles_chained",
+    "gcta_b200_bed_decode", "gcta_b200_snp_stats", "gcta_b200_compact_rows", "gcta_b200_decode_emit_diag", "gcta_b200_diag_accum", "gcta_b200_diag_accum_static", "gcta_b200_nonmiss_planes", "gcta_b200_syrk_tiles", "gcta_b200_syrk_tiles_chained",
     "gcta_b200_paircount_tiles", "gcta_b200_finalize_tiles", "gcta_b200_version", "gcta_b200_device_count",
     "gcta_b200_partition", "gcta_b200_tile_list", "gcta_b200_allele_counts", "gcta_b200_nonmiss_matrix", "gcta_b200_count_tiles",
     "gcta_b200_plan_use_device_bed", "gcta_b200_plan_upload_rows", "gcta_b200_plan_run_to_host",

@@ -16,9 +16,10 @@
 //                        its re-read of the packed rows are gone.
 //
 // Both are HBM-bound byte kernels.  Algorithmic bytes per SNP: ceil(n/4) (K1s) and
-// ceil(n/4) + 2*ldz (K1f).  This is the path for the common case (every individual kept,
-// autosomes, --grm-alg 0, one 16-bit plane); keep lists, the X chromosome, --grm-alg 1 and the
-// split-FP16 mode stay on the row-per-CTA kernels of decode.cu.
+// ceil(n/4) + 2*ldz (K1f).  This is the path for the common case (autosomes, --grm-alg 0, one
+// 16-bit plane; with a keep list after K1c below has compacted the chunk's rows to the kept
+// individuals); the X chromosome, --grm-alg 1 and the split-FP16 mode stay on the row-per-CTA
+// kernels of decode.cu.
 #include <algorithm>
 #include <cstdlib>
 
@@ -361,6 +362,41 @@ __global__ void __launch_bounds__(F_THREADS, 4) decode_emit_diag_kernel(const Fu
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// K1c: a keep list (--keep / --remove, data.cpp:657-673) on the packed rows.  One thread writes one 32-bit word of the
+// output row = the 2-bit codes of 16 kept individuals, fetched from wherever the keep list says they sit in the file
+// row.  The output is a packed chunk in which "every individual is kept", so K1s / K1f (and the indicator kernel) run
+// their plain paths on it; the per-individual gathers of the row kernels in decode.cu are gone.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) compact_rows_kernel(const uint8_t* __restrict__ bed, int64_t pitch, const int32_t* __restrict__ include,
+                                                            int64_t k0, int64_t kc, const int32_t* __restrict__ keep, int64_t n,
+                                                            uint32_t* __restrict__ out, int64_t words_out)
+{
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t kk = blockIdx.y;
+    if (w >= words_out || kk >= kc) return;
+    const int64_t k = k0 + kk;
+    const uint8_t* row = bed + (include ? (int64_t)include[k] : k) * pitch;
+    uint32_t o = 0;
+    const int64_t i0 = w * 16;
+    if (i0 + 16 <= n) {
+        const int4* kp = reinterpret_cast<const int4*>(keep + i0);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int4 f4 = __ldg(kp + q);
+            const int f[4] = {f4.x, f4.y, f4.z, f4.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) o |= (uint32_t)((__ldg(row + (f[e] >> 2)) >> ((f[e] & 3) * 2)) & 3u) << (2 * (4 * q + e));
+        }
+    } else {
+        for (int e = 0; e < 16 && i0 + e < n; e++) {
+            const int f = keep[i0 + e];
+            o |= (uint32_t)((row[f >> 2] >> ((f & 3) * 2)) & 3u) << (2 * e);
+        }
+    }
+    out[kk * words_out + w] = o;   // pad individuals: code 00, masked out by the keep mask / n_out downstream
+}
+
 }  // namespace gb
 
 // K1s through the C ABI (device pointers).  d_mu / d_cnt / d_sum / d_zlut / d_total_missing as for gcta_b200_bed_decode.
@@ -428,6 +464,27 @@ extern "C" int gcta_b200_decode_emit_diag(const uint8_t* d_bed, int64_t pitch, i
     p.rows_per_cta = rows;
     dim3 grid((unsigned)slabs, (unsigned)groups);
     decode_emit_diag_kernel<<<grid, F_THREADS, 0, (cudaStream_t)stream>>>(p);
+    GB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// K1c through the C ABI (device pointers): packed rows of included SNPs [k0, k0+kc) restricted to the kept individuals,
+// row kk of the output at d_out + kk * pitch_out (pitch_out % 16 == 0, >= ceil(n/4)); d_keep 16-byte aligned.
+extern "C" int gcta_b200_compact_rows(const uint8_t* d_bed, int64_t pitch, const int32_t* d_include, int64_t k0, int64_t kc,
+                                      const int32_t* d_keep, int64_t n, uint8_t* d_out, int64_t pitch_out, void* stream, char* err, size_t errcap)
+{
+    using namespace gb;
+    GB_ARG(d_bed && d_keep && d_out, "compact_rows: null pointer");
+    GB_ARG(pitch > 0 && n > 0 && kc > 0 && k0 >= 0, "compact_rows: empty range");
+    GB_ARG(pitch_out % 16 == 0 && pitch_out * 4 >= n && ((uintptr_t)d_out & 15) == 0 && ((uintptr_t)d_keep & 15) == 0,
+           "compact_rows: output pitch must be a multiple of 16 bytes that holds n individuals; d_out and d_keep 16-byte aligned");
+    const int64_t words = pitch_out / 4;
+    for (int64_t r0 = 0; r0 < kc; r0 += 65535) {   // grid.y limit
+        const int64_t rows = std::min<int64_t>(65535, kc - r0);
+        dim3 grid((unsigned)((words + 255) / 256), (unsigned)rows);
+        compact_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, d_include, k0 + r0, rows, d_keep, n,
+                                                                   reinterpret_cast<uint32_t*>(d_out + r0 * pitch_out), words);
+    }
     GB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -191,6 +191,12 @@ struct gcta_b200_plan {
     std::vector<cudaEvent_t> events;
     bool ran = false, overlap = false;
     bool fused_decode = false;   // K1s + K1f (decode2.cu) instead of K1 + K1d
+    // keep list: each chunk's rows are first compacted to the kept individuals (K1c), and the fused kernels then see a
+    // chunk in which everyone is kept - pitch cpitch, all-ones keep mask, row kk of the chunk at d_cbed + kk * cpitch
+    bool compact = false;
+    uint8_t* d_cbed = nullptr;
+    uint32_t* d_ckeepmask = nullptr;
+    int64_t cpitch = 0;
     int64_t chain = 32768;       // SNPs accumulated in one TMEM chain before the accumulator is added into S
     int64_t total_missing = 0;
     std::vector<void*> allocs;
@@ -283,8 +289,12 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
     p->has_include = a->include != nullptr;
     p->has_mu = a->mu != nullptr;
     // the two streaming passes of decode2.cu cover the common case; GCTA_B200_DECODE=legacy forces the row-per-CTA kernels
-    p->fused_decode = !p->has_keep && !a->xchr && a->alg == 0 && p->operand != GCTA_B200_FP16X2 &&
-                      !(getenv("GCTA_B200_DECODE") && strcmp(getenv("GCTA_B200_DECODE"), "legacy") == 0);
+    {
+        const bool fast_ok = !a->xchr && a->alg == 0 && p->operand != GCTA_B200_FP16X2 &&
+                             !(getenv("GCTA_B200_DECODE") && strcmp(getenv("GCTA_B200_DECODE"), "legacy") == 0);
+        p->compact = fast_ok && p->has_keep && !(getenv("GCTA_B200_COMPACT") && atoi(getenv("GCTA_B200_COMPACT")) == 0);
+        p->fused_decode = fast_ok && (!p->has_keep || p->compact);
+    }
 #define PLAN_TRY(x) do { int rc_ = (x); if (rc_) { gcta_b200_plan_destroy(p); return rc_; } } while (0)
 #define PLAN_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { gcta_b200_plan_destroy(p); \
         return set_err(err, errcap, GCTA_B200_ERR_CUDA, std::string("Error: CUDA call failed: ") + #x + ": " + cudaGetErrorString(e_)); } } while (0)
@@ -348,6 +358,15 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         PLAN_TRY(dev_alloc(p, &p->d_keep, (size_t)n, err, errcap));
         PLAN_CUDA(cudaMemcpy(p->d_keep, a->keep, (size_t)n * 4, cudaMemcpyHostToDevice));
         if (p->row_end > p->row_begin) { p->diag_f0 = a->keep[p->row_begin] / 16 * 16; p->diag_f1 = (int64_t)a->keep[p->row_end - 1] + 1; }
+        if (p->compact) {   // the diagonal is indexed by kept individual
+            p->diag_f0 = p->row_begin;
+            p->diag_f1 = p->row_end;
+            p->cpitch = round_up((n + 3) / 4, 16);
+            std::vector<uint32_t> ckm((size_t)p->cpitch / 4, 0u);
+            for (int64_t i = 0; i < n; i++) ckm[i >> 4] |= 1u << ((i & 15) * 2);
+            PLAN_TRY(dev_alloc(p, &p->d_ckeepmask, ckm.size(), err, errcap));
+            PLAN_CUDA(cudaMemcpy(p->d_ckeepmask, ckm.data(), ckm.size() * 4, cudaMemcpyHostToDevice));
+        }
     }
     if (p->has_include) {
         PLAN_TRY(dev_alloc(p, &p->d_include, (size_t)m, err, errcap));
@@ -417,6 +436,7 @@ extern "C" int gcta_b200_plan_create(const gcta_b200_args* a, gcta_b200_plan** o
         p->cstart.assign(1, 0);
         for (int64_t l : lens) p->cstart.push_back(p->cstart.back() + l);
         PLAN_TRY(dev_alloc(p, (uint16_t**)&p->d_Zbuf[0], (size_t)kc * p->ldz * planes, err, errcap));
+        if (p->compact) PLAN_TRY(dev_alloc(p, &p->d_cbed, (size_t)kc * p->cpitch, err, errcap));
         if (p->stream_bed) {
             // two ring buffers, each large enough for the file rows any one chunk reads
             for (int64_t c = 0; c < p->nchunks(); c++) {
@@ -849,7 +869,7 @@ static int run_last_chunk_pipelined(gcta_b200_plan* p, const void* Z, int64_t kp
                                           p->d_S + t0 * (TILE_M * TILE_N), st, err, errcap);   // TMEM chains as in plan_run_impl
         if (rc) break;
         const int64_t seg_base = r0 * (r0 + 1) / 2, seg_cnt = r1 * (r1 + 1) / 2 - seg_base;
-        rc = gcta_b200_finalize_tiles(p->d_S + t0 * (TILE_M * TILE_N), nullptr, (int32_t)p->m, p->d_tiles + 2 * t0, t1 - t0, p->n, p->d_keep, p->d_diag,
+        rc = gcta_b200_finalize_tiles(p->d_S + t0 * (TILE_M * TILE_N), nullptr, (int32_t)p->m, p->d_tiles + 2 * t0, t1 - t0, p->n, p->compact ? nullptr : p->d_keep, p->d_diag,
                                       p->d_nii, r0, r1, p->d_A_lower + (seg_base - band_base), nullptr, st, err, errcap);
         if (rc) break;
         *launches += 2;
@@ -1050,7 +1070,19 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         int rc = 0;
         const uint8_t* bedc = bed_of(c, c);   // first pass: chunk c is the c-th staged chunk
         if (p->fused_decode) {
-            rc = gcta_b200_snp_stats(bedc, p->pitch, p->n_file, p->d_keepmask, p->n, p->d_include, k0, kc, p->d_mu_in, p->alg, p->d_mu,
+            // what K1s / K1f take as the packed file: the file itself, or this chunk compacted to the kept individuals
+            const uint8_t* fb = bedc;
+            int64_t fpitch = p->pitch, fn = p->n_file;
+            const uint32_t* fkm = p->d_keepmask;
+            const int32_t* finc = p->d_include;
+            if (p->compact) {
+                rc = gcta_b200_compact_rows(bedc, p->pitch, p->d_include, k0, kc, p->d_keep, p->n, p->d_cbed, p->cpitch, sd, err, errcap);
+                if (rc) return rc;
+                launches++;
+                fb = p->d_cbed - k0 * p->cpitch;   // row k of the "file" = row k - k0 of the chunk
+                fpitch = p->cpitch; fn = p->n; fkm = p->d_ckeepmask; finc = nullptr;
+            }
+            rc = gcta_b200_snp_stats(fb, fpitch, fn, fkm, p->n, finc, k0, kc, p->d_mu_in, p->alg, p->d_mu,
                                      p->d_cnt, p->d_sum, p->d_zlut, p->d_total_missing, sd, err, errcap);
             if (!rc && c == 0 && inline_ok) {
                 // anything missing in the first chunk?  (one small wait at the very start of the run)
@@ -1068,7 +1100,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
                 }
             }
             // Z and the band's diagonal (and the indicators) in one pass over the packed rows
-            if (!rc) rc = gcta_b200_decode_emit_diag(bedc, p->pitch, p->n_file, p->d_include, k0, kc, p->d_zlut, p->operand, Z, p->ldz,
+            if (!rc) rc = gcta_b200_decode_emit_diag(fb, fpitch, fn, finc, k0, kc, p->d_zlut, p->operand, Z, p->ldz,
                                                      p->d_diag, p->d_nii, p->diag_f0, p->diag_f1, okbuf, sd, err, errcap);
             if (rc) return rc;
         } else {
@@ -1163,7 +1195,14 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
             // 8-bit E4M3 indicators (kind::f8f6f4: twice the MMA rate, half the bytes) unless the CTA-pair kernel or
             // GCTA_B200_N_MODE=tensor16 asks for the 16-bit route; both give the same integers
             const int opN = (p->d_pairs || (nmode && strcmp(nmode, "tensor16") == 0)) ? op16 : GCTA_B200_E4M3;
-            int rc = gcta_b200_nonmiss_matrix(bed_of(c, seq0 + c), p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, opN,
+            int rc = 0;
+            if (p->compact) {   // the indicator kernel too runs on the compacted chunk
+                rc = gcta_b200_compact_rows(bed_of(c, seq0 + c), p->pitch, p->d_include, k0, kc, p->d_keep, p->n, p->d_cbed, p->cpitch, st, err, errcap);
+                if (!rc) rc = gcta_b200_nonmiss_matrix(p->d_cbed - k0 * p->cpitch, p->cpitch, p->n, nullptr, p->n, nullptr, k0, kc, opN,
+                                                        p->d_Zbuf[0], p->ldz, st, err, errcap);
+                launches++;
+            } else
+                rc = gcta_b200_nonmiss_matrix(bed_of(c, seq0 + c), p->pitch, p->n_file, p->d_keep, p->n, p->d_include, k0, kc, opN,
                                               p->d_Zbuf[0], p->ldz, st, err, errcap);
             if (rc) return rc;
             GB_CUDA(restage_next(c, seq0 + c));
@@ -1227,7 +1266,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
     }
     else {
         int rc = gcta_b200_finalize_tiles_ex(p->d_S, tm > 0 ? p->d_Ntiles : nullptr, (int32_t)p->m, (p->alg == 1 && tm > 0) ? p->d_Dtiles : nullptr,
-                                             d_const, p->alg == 1 ? p->d_dw : nullptr, p->d_tiles, p->ntiles, p->n, p->d_keep,
+                                             d_const, p->alg == 1 ? p->d_dw : nullptr, p->d_tiles, p->ntiles, p->n, p->compact ? nullptr : p->d_keep,
                                              p->d_diag, p->d_nii, p->row_begin, p->row_end, p->d_A_lower, tm > 0 ? p->d_N_lower : nullptr, st, err, errcap);
         if (rc) return rc;
         launches++;

@@ -232,9 +232,9 @@ int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
                          double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,
                          unsigned long long* d_total_missing, void* stream, char* err, size_t errcap);
 
-/* K1s + K1f - the same stage as two streaming passes, used by the plan whenever every file individual is kept, the
- * SNPs are autosomal, alg == 0 and the operand is one 16-bit plane (the other cases stay on gcta_b200_bed_decode +
- * gcta_b200_diag_accum).
+/* K1s + K1f - the same stage as two streaming passes, used by the plan whenever the SNPs are autosomal, alg == 0 and the
+ * operand is one 16-bit plane (with a keep list: on the rows compacted by gcta_b200_compact_rows; the other cases stay on
+ * gcta_b200_bed_decode + gcta_b200_diag_accum).
  *   gcta_b200_snp_stats        per included SNP in [k0, k0+kc): allele counts of the kept individuals, 2p, and the
  *                              doubly-rounded standardised values (calcu_mu / mu_func data.cpp:759-803; the per-SNP
  *                              constants of std_XMat data.cpp:1027-1040).  Outputs as for gcta_b200_bed_decode.
@@ -245,6 +245,12 @@ int gcta_b200_bed_decode(const uint8_t* d_bed, int64_t pitch, int64_t n_file,
  *                              d_OK != NULL: the same pass also writes the 8-bit E4M3 non-missing indicators (1.0 / 0) of
  *                              every genotype as a matrix [kc rounded up to 128][ldz] bytes, what gcta_b200_nonmiss_matrix
  *                              with GCTA_B200_E4M3 produces (the operand of the counting pass, grm.cpp:270, 291). */
+/* K1c - a keep list applied to the packed rows (keep_indi / remove_indi, data.cpp:657-673, as read_bedfile applies them,
+ * data.cpp:171-185): the 2-bit codes of kept individuals 0..n-1 of included SNPs [k0, k0+kc) packed densely, row kk at
+ * d_out + kk * pitch_out.  The plan runs it per SNP chunk so that the stages above never gather per individual. */
+int gcta_b200_compact_rows(const uint8_t* d_bed, int64_t pitch, const int32_t* d_include, int64_t k0, int64_t kc,
+                           const int32_t* d_keep, int64_t n, uint8_t* d_out, int64_t pitch_out,
+                           void* stream, char* err, size_t errcap);
 int gcta_b200_snp_stats(const uint8_t* d_bed, int64_t pitch, int64_t n_file, const uint32_t* d_keepmask, int64_t n,
                         const int32_t* d_include, int64_t k0, int64_t kc, const double* d_mu_in, int32_t alg,
                         double* d_mu, int32_t* d_cnt, int32_t* d_sum, float* d_zlut,

@@ -153,3 +153,30 @@ def test_fused_decode_indicator_plane(n, m, miss, want_diag):
     assert not r["OK"][m:, :].any() and not r["OK"][:, n:].any()
     assert np.array_equal(r["Z"], r0["Z"]) and np.array_equal(r["nii"], r0["nii"])
     assert np.allclose(r["diag"], r0["diag"], rtol=1e-12)
+
+
+def test_compact_rows_kernel():
+    """K1c: the packed rows restricted to a keep list equal numpy's re-pack of the kept columns (with an include list,
+    a chunk in the middle, n not a multiple of 16)"""
+    n_file, m_file = 1003, 300
+    bed = synth.make_bed_payload(77, n_file, m_file, miss_rate=0.1)
+    rng = np.random.default_rng(3)
+    keep = np.sort(rng.choice(n_file, 611, replace=False)).astype(np.int32)
+    inc = np.sort(rng.choice(m_file, 200, replace=False)).astype(np.int32)
+    bedp, pitch = pitched(bed, n_file)
+    n = len(keep)
+    pitch_out = ((n + 3) // 4 + 15) // 16 * 16
+    k0, kc = 32, 150
+    out = torch.full((kc, pitch_out), 0xAB, dtype=torch.uint8, device="cuda")
+    d_bed, d_keep, d_inc = dev(bedp), dev(keep), dev(inc)
+    abi.call("gcta_b200_compact_rows", P(d_bed.data_ptr()), I64(pitch), P(d_inc.data_ptr()), I64(k0), I64(kc), P(d_keep.data_ptr()), I64(n),
+             P(out.data_ptr()), I64(pitch_out), stream())
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    x = oracle.decode_x(bed, n_file, keep, inc)[k0:k0 + kc]                 # copies of allele 1, -1 = missing
+    codes = np.array([3, 2, 0, 1], dtype=np.uint8)[x.astype(np.int64)]      # 0 -> 11, 1 -> 10b, 2 -> 00, missing -> 01b
+    pad = np.zeros((kc, pitch_out * 4), dtype=np.uint8)
+    pad[:, :n] = codes
+    pad = pad.reshape(kc, pitch_out, 4)
+    want = pad[:, :, 0] | (pad[:, :, 1] << 2) | (pad[:, :, 2] << 4) | (pad[:, :, 3] << 6)
+    assert np.array_equal(got, want)

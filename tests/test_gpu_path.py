@@ -356,3 +356,34 @@ def test_short_tmem_chains_and_the_cta_pair_kernel(monkeypatch):
     assert np.array_equal(res["c256"], res["c256_launches"])          # same chains, same order of additions
     assert np.abs(res["c256"].astype(np.float64) - res["whole"]).max() < 2e-6
     assert np.abs(res["pairs_c512"].astype(np.float64) - res["whole"]).max() < 2e-6
+
+
+def test_keep_list_goes_through_compaction(monkeypatch):
+    """--keep / --remove on a long contraction: each chunk's rows are compacted to the kept individuals and then take the
+    plain fused path; same N and off-diagonal A as the per-individual gathers of the row kernels (GCTA_B200_COMPACT=0)"""
+    n_file, m = 2500, 9000
+    bed = synth.make_bed_payload(91, n_file, m, miss_rate=0.02)
+    rng = np.random.default_rng(9)
+    keep = np.sort(rng.choice(n_file, 1801, replace=False)).astype(np.int32)
+    inc = np.sort(rng.choice(m, 8500, replace=False)).astype(np.int32)
+    Aref, Nref, _ = oracle.make_grm_numpy(bed, n_file, keep=keep, include=inc)
+    A0, N0, mu0, o0 = abi.make_grm(bed, n_file, m, keep=keep, include=inc, chunk_snps=2048)
+    check_grm(A0, N0, pack_lower(Aref), pack_lower(Nref))
+    monkeypatch.setenv("GCTA_B200_COMPACT", "0")
+    A1, N1, mu1, o1 = abi.make_grm(bed, n_file, m, keep=keep, include=inc, chunk_snps=2048)
+    monkeypatch.delenv("GCTA_B200_COMPACT")
+    assert np.array_equal(N0, N1) and np.array_equal(mu0, mu1)
+    n = len(keep)
+    off = np.ones(len(A0), dtype=bool)
+    i = np.arange(n, dtype=np.int64)
+    off[i * (i + 1) // 2 + i] = False
+    assert np.array_equal(A0[off], A1[off]) and np.abs(A0[~off].astype(np.float64) - A1[~off]).max() <= 1e-6
+    # two row bands with a keep list (the multi-GPU partition)
+    A = np.full_like(A0, np.nan)
+    N = np.full_like(N0, -1)
+    for r in range(2):
+        with abi.Plan(n_file, m, keep=keep, include=inc, chunk_snps=2048, part_rank=r, part_world=2) as p:
+            p.upload(bed)
+            p.run()
+            p.download(A, N)
+    assert np.array_equal(N, N0) and np.array_equal(A[off], A0[off])

@@ -11,7 +11,11 @@ n = int(os.environ.get("PROF_N", "50000"))
 m = int(os.environ.get("PROF_M", "65536"))
 chunk = int(os.environ.get("PROF_CHUNK", "32768"))
 miss = float(os.environ.get("PROF_MISS", "0"))
-with abi.Plan(n, m, chunk_snps=chunk) as p:
+keep = None
+if os.environ.get("PROF_KEEP"):   # a keep list that drops every 10th individual (--remove of 10 % of the sample)
+    import numpy as np
+    keep = np.array([i for i in range(n) if i % 10 != 9], dtype=np.int32)
+with abi.Plan(n, m, chunk_snps=chunk, keep=keep) as p:
     p.synth(1236, synth.snp_thresholds(1236, m, miss_rate=miss))
     for _ in range(int(os.environ.get("PROF_RUNS", "2"))):
         o = p.run()
