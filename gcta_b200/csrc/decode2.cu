@@ -368,33 +368,48 @@ __global__ void __launch_bounds__(F_THREADS, 4) decode_emit_diag_kernel(const Fu
 // row.  The output is a packed chunk in which "every individual is kept", so K1s / K1f (and the indicator kernel) run
 // their plain paths on it; the per-individual gathers of the row kernels in decode.cu are gone.
 // ------------------------------------------------------------------------------------------------
+constexpr int C_ROWS = 64;   // SNP rows per CTA of K1c: the 16 keep indices of a thread are fetched once and serve all of them
+
 __global__ void __launch_bounds__(256) compact_rows_kernel(const uint8_t* __restrict__ bed, int64_t pitch, const int32_t* __restrict__ include,
                                                             int64_t k0, int64_t kc, const int32_t* __restrict__ keep, int64_t n,
                                                             uint32_t* __restrict__ out, int64_t words_out)
 {
     const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t kk = blockIdx.y;
-    if (w >= words_out || kk >= kc) return;
-    const int64_t k = k0 + kk;
-    const uint8_t* row = bed + (include ? (int64_t)include[k] : k) * pitch;
-    uint32_t o = 0;
+    if (w >= words_out) return;
     const int64_t i0 = w * 16;
-    if (i0 + 16 <= n) {
+    const int cnt = (int)max((int64_t)0, min((int64_t)16, n - i0));
+    // file positions of this thread's 16 kept individuals (the same for every SNP row); unused slots repeat the last one
+    int f[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) f[e] = 0;
+    if (cnt == 16) {
         const int4* kp = reinterpret_cast<const int4*>(keep + i0);
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const int4 f4 = __ldg(kp + q);
-            const int f[4] = {f4.x, f4.y, f4.z, f4.w};
-#pragma unroll
-            for (int e = 0; e < 4; e++) o |= (uint32_t)((__ldg(row + (f[e] >> 2)) >> ((f[e] & 3) * 2)) & 3u) << (2 * (4 * q + e));
+            f[4 * q] = f4.x; f[4 * q + 1] = f4.y; f[4 * q + 2] = f4.z; f[4 * q + 3] = f4.w;
         }
     } else {
-        for (int e = 0; e < 16 && i0 + e < n; e++) {
-            const int f = keep[i0 + e];
-            o |= (uint32_t)((row[f >> 2] >> ((f & 3) * 2)) & 3u) << (2 * e);
-        }
+#pragma unroll
+        for (int e = 0; e < 16; e++)
+            if (e < cnt) f[e] = keep[i0 + e];
     }
-    out[kk * words_out + w] = o;   // pad individuals: code 00, masked out by the keep mask / n_out downstream
+    const int64_t kk_end = min(kc, ((int64_t)blockIdx.y + 1) * C_ROWS);
+    for (int64_t kk = (int64_t)blockIdx.y * C_ROWS; kk < kk_end; kk++) {
+        const int64_t k = k0 + kk;
+        const uint32_t* row32 = reinterpret_cast<const uint32_t*>(bed + (include ? (int64_t)include[k] : k) * pitch);
+        // The keep list ascends, so the 16 codes sit in two or three consecutive 32-bit words of the file row: a word is
+        // only fetched when the next individual has left the current one.
+        uint32_t o = 0, curw = 0;
+        int curi = -1;
+#pragma unroll
+        for (int e = 0; e < 16; e++) {
+            const int wi = f[e] >> 4;
+            if (wi != curi) { curw = __ldg(row32 + wi); curi = wi; }
+            if (e < cnt) o |= ((curw >> ((f[e] & 15) * 2)) & 3u) << (2 * e);
+        }
+        out[kk * words_out + w] = o;   // pad individuals: code 00, masked out by the keep mask / n_out downstream
+    }
 }
 
 }  // namespace gb
@@ -479,9 +494,9 @@ extern "C" int gcta_b200_compact_rows(const uint8_t* d_bed, int64_t pitch, const
     GB_ARG(pitch_out % 16 == 0 && pitch_out * 4 >= n && ((uintptr_t)d_out & 15) == 0 && ((uintptr_t)d_keep & 15) == 0,
            "compact_rows: output pitch must be a multiple of 16 bytes that holds n individuals; d_out and d_keep 16-byte aligned");
     const int64_t words = pitch_out / 4;
-    for (int64_t r0 = 0; r0 < kc; r0 += 65535) {   // grid.y limit
-        const int64_t rows = std::min<int64_t>(65535, kc - r0);
-        dim3 grid((unsigned)((words + 255) / 256), (unsigned)rows);
+    for (int64_t r0 = 0; r0 < kc; r0 += 65535ll * C_ROWS) {   // grid.y limit
+        const int64_t rows = std::min<int64_t>(65535ll * C_ROWS, kc - r0);
+        dim3 grid((unsigned)((words + 255) / 256), (unsigned)((rows + C_ROWS - 1) / C_ROWS));
         compact_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_bed, pitch, d_include, k0 + r0, rows, d_keep, n,
                                                                    reinterpret_cast<uint32_t*>(d_out + r0 * pitch_out), words);
     }
