@@ -42,6 +42,7 @@ inline int set_err(char* err, size_t cap, int code, const std::string& msg)
 
 // slot of the (device, stream) pair in the SYRK kernels' wave-barrier counter arrays (syrk.cu); -1 = none left
 int wave_slot_of(int dev, void* stream);
+void wave_slot_release(int dev, void* stream);   // before the stream is destroyed
 
 constexpr int TILE_M = 256;  // rows of S per tile (two UMMA M=128 halves, one TMEM accumulator each)
 constexpr int TILE_N = 256;  // columns of S per tile (= UMMA N, TMEM columns per accumulator)

@@ -229,8 +229,8 @@ extern "C" void gcta_b200_plan_destroy(gcta_b200_plan* p)
     if (p->stream2) cudaStreamSynchronize(p->stream2);
     for (cudaEvent_t e : p->events) cudaEventDestroy(e);
     for (void* q : p->allocs) cudaFree(q);
-    if (p->stream) cudaStreamDestroy(p->stream);
-    if (p->stream2) cudaStreamDestroy(p->stream2);
+    if (p->stream) { gb::wave_slot_release(p->device, p->stream); cudaStreamDestroy(p->stream); }
+    if (p->stream2) { gb::wave_slot_release(p->device, p->stream2); cudaStreamDestroy(p->stream2); }
     if (p->stream_copy) cudaStreamDestroy(p->stream_copy);
     for (cudaEvent_t e : p->upload_events) cudaEventDestroy(e);
     for (int j = 0; j < 2; j++)

@@ -23,6 +23,7 @@
 #include <cstdlib>
 #include <map>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -284,18 +285,35 @@ syrk_tiles_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 constexpr int WAVE_SLOTS = 64;
 static __device__ unsigned int g_wave_counter[WAVE_SLOTS];
 
+namespace {
+std::mutex g_slot_mu;
+std::map<std::pair<int, void*>, int> g_slots;
+std::vector<int> g_free_slots[64];
+int g_slots_used[64] = {};
+}  // namespace
+
 int wave_slot_of(int dev, void* stream)
 {
-    static std::mutex mu;
-    static std::map<std::pair<int, void*>, int> slots;
-    static int used[64] = {};
-    std::lock_guard<std::mutex> lock(mu);
-    auto it = slots.find({dev, stream});
-    if (it != slots.end()) return it->second;
-    if (dev < 0 || dev >= 64 || used[dev] >= WAVE_SLOTS) return -1;
-    const int slot = used[dev]++;
-    slots[{dev, stream}] = slot;
+    std::lock_guard<std::mutex> lock(g_slot_mu);
+    auto it = g_slots.find({dev, stream});
+    if (it != g_slots.end()) return it->second;
+    if (dev < 0 || dev >= 64) return -1;
+    int slot = -1;
+    if (!g_free_slots[dev].empty()) { slot = g_free_slots[dev].back(); g_free_slots[dev].pop_back(); }
+    else if (g_slots_used[dev] < WAVE_SLOTS) slot = g_slots_used[dev]++;
+    if (slot >= 0) g_slots[{dev, stream}] = slot;
     return slot;
+}
+
+// a stream is about to be destroyed (plan_destroy): its slot goes back to the pool, so a long-lived process that creates
+// many plans never runs out of counters
+void wave_slot_release(int dev, void* stream)
+{
+    std::lock_guard<std::mutex> lock(g_slot_mu);
+    auto it = g_slots.find({dev, stream});
+    if (it == g_slots.end()) return;
+    if (dev >= 0 && dev < 64) g_free_slots[dev].push_back(it->second);
+    g_slots.erase(it);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
