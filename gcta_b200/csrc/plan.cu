@@ -987,7 +987,7 @@ static int plan_run_impl(gcta_b200_plan* p, const uint8_t* bed_host, gcta_b200_o
         cudaPointerAttributes attr;
         const bool pageable = cudaPointerGetAttributes(&attr, bed_host) != cudaSuccess || attr.type == cudaMemoryTypeUnregistered;
         cudaGetLastError();
-        if (pageable && p->pitch * p->m_file >= stage_min_bytes()) {
+        if (pageable && p->pitch * p->m_file >= stage_min_bytes() && p->pitch <= gcta_b200_plan::HSLOT_BYTES) {   // a slot holds whole rows
             std::vector<int64_t> rb((size_t)nch_up), re((size_t)nch_up);
             for (int64_t c = 0; c < nch_up; c++) chunk_rows(c, rb[(size_t)c], re[(size_t)c]);
             stager.reset(new Stager());
