@@ -1,4 +1,6 @@
-// decode.cu - K1 / K1d / K1m: everything that reads the packed 2-bit genotypes.
+// decode.cu - K1 / K1d / K1m: the row-per-CTA kernels that read the packed 2-bit genotypes.
+// Since round 2 the plan uses them for the X chromosome, --grm-alg 1 and the split-FP16 operand
+// mode only; everything else goes through K1s / K1f (/ K1c) in decode2.cu.
 //
 // K1  bed_decode      : one pass per SNP row - count alleles (popc over bit planes, shuffle
 //                       reduction), derive 2p and the reference's doubly-rounded standardised

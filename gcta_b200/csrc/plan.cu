@@ -1,14 +1,19 @@
 // plan.cu - orchestration of the --make-grm path on one GPU (one row band of the GRM).
 //
-// Mirrors the sequence inside gcta::make_grm (grm.cpp:219-301):
-//   make_XMat + std_XMat  -> K1 bed_decode, one SNP chunk at a time into a reused Z buffer
-//   triple loop numerator -> K2 syrk_tiles accumulating FP32 S tiles over the chunks
-//   A_N counts            -> K1m + K3 (AND+popc), only when some kept genotype is missing
+// Mirrors the sequence inside gcta::make_grm (grm.cpp:219-301), one SNP chunk at a time into a reused Z buffer:
+//   keep list             -> K1c compact_rows (only with --keep / --remove)
+//   calcu_mu              -> K1s snp_stats
+//   make_XMat + std_XMat  -> K1f decode_emit_diag (also the diagonal and, with missing genotypes, the indicators);
+//                            K1 bed_decode + K1d diag_accum for the X chromosome, --grm-alg 1 and split-FP16 operands
+//   triple loop numerator -> K2 syrk_tiles accumulating FP32 S tiles over the chunks, in TMEM chains of <= 32,768 SNPs
+//   A_N counts            -> K2 in counting mode on the E4M3 indicators, chunk by chunk (K1m + K3 AND+popc: cross-check)
 //   A = S / N, zero rules -> K4 finalize_tiles into the packed lower triangle
-// Multi-GPU: the caller runs one plan per process / GPU with
-// (part_rank, part_world); each plan owns a contiguous band of rows [row_begin,row_end) of
-// the lower triangle, balanced by tile count, so outputs are disjoint contiguous ranges of
-// the packed triangle and no collective is needed on the data path.
+// Around it: uploads one chunk ahead of the kernels (resident buffer, or two ring buffers when the file exceeds its HBM
+// allowance), pinned staging by helper threads for pageable host buffers, and the download of the band behind the last
+// chunk's SYRK.
+// Multi-GPU: one plan per GPU with (part_rank, part_world); each plan owns a contiguous band of rows
+// [row_begin,row_end) of the lower triangle, balanced by cost, so outputs are disjoint contiguous ranges of the packed
+// triangle and no collective is needed on the data path (exchange.cu / multi.cu bring the packed rows to every GPU).
 #include <algorithm>
 #include <atomic>
 #include <cstdlib>
