@@ -348,18 +348,7 @@ def main_ours(a, rank, world, local_rank):
         if a.no_e2e:
             plan.run()
         plan.download(A_ptr, N_ptr, mu_dev.ctypes.data)   # the band as the last step left it on the device (+ 2p)
-        bounds = sorted({abi.partition(n, r, world)[0] for r in range(world)} - {0})
-        pick = {0, n - 1}
-        for b in bounds:
-            pick |= {b - 2, b - 1, b, b + 1}
-        pick = {int(x) for x in pick if 0 <= x < n}
-        rng = np.random.default_rng(SEED)
-        rest = rng.permutation(n)
-        for x in rest:
-            if len(pick) >= min(a.parity_sub, n):
-                break
-            pick.add(int(x))
-        sub = np.array(sorted(pick), dtype=np.int64)
+        sub, bounds = gdist.parity_subset(n, world, a.parity_sub, SEED)
         ns = len(sub)
         if rank == 0:
             t_or = time.perf_counter()
@@ -370,16 +359,7 @@ def main_ours(a, rank, world, local_rank):
             ref = np.zeros(2 * ns * ns)
         ref = ranks.broadcast(ref, 0)
         Aref, Nref = ref[:ns * ns].reshape(ns, ns), ref[ns * ns:].reshape(ns, ns)
-        mine = [t for t in range(ns) if row_begin <= sub[t] < row_end]
-        dA_max, n_bad, dsum, dn = 0.0, 0, 0.0, 0
-        An, Nn = h_A.numpy(), h_N
-        for t in mine:
-            i = int(sub[t])
-            idx = i * (i + 1) // 2 + sub[:t + 1] - base
-            dA_max = max(dA_max, float(np.abs(An[idx].astype(np.float64) - Aref[t, :t + 1]).max()))
-            n_bad += int((Nn[idx] != np.rint(Nref[t, :t + 1]).astype(np.int32)).sum())
-            dsum += float(An[idx[-1]]) - Aref[t, t]
-            dn += 1
+        dA_max, n_bad, dsum, dn = gdist.band_deltas(h_A.numpy(), h_N, base, row_begin, row_end, sub, Aref, Nref)
         dA_max = max_over_ranks(dA_max)
         n_bad = int(sum_over_ranks(n_bad))
         dmean = sum_over_ranks(dsum) / max(1.0, sum_over_ranks(dn))

@@ -88,6 +88,41 @@ class Ranks:
             self._dist = None
 
 
+def parity_subset(n: int, world: int, size: int, seed: int):
+    """Individuals of the bench line's parity check (SURVEY.md 8c sub-block identity): the same seeded set on every rank,
+    containing the first and last individual and both sides of every band boundary, filled up at random to `size`.
+    -> (sorted int64 array, list of the band boundaries it straddles)"""
+    import numpy as np
+    bounds = sorted({abi.partition(n, r, world)[0] for r in range(world)} - {0})
+    pick = {0, n - 1}
+    for b in bounds:
+        pick |= {b - 2, b - 1, b, b + 1}
+    pick = {int(x) for x in pick if 0 <= x < n}
+    for x in np.random.default_rng(seed).permutation(n):
+        if len(pick) >= min(size, n):
+            break
+        pick.add(int(x))
+    return np.array(sorted(pick), dtype=np.int64), bounds
+
+
+def band_deltas(A_band, N_band, base: int, row_begin: int, row_end: int, sub, Aref, Nref):
+    """This rank's share of the parity check: rows of `sub` inside [row_begin, row_end) against the oracle's block.
+    A_band / N_band hold the packed triangle from element `base` on.  -> (max |dA|, N mismatches, sum of diagonal
+    deltas, diagonal count)"""
+    import numpy as np
+    dA_max, n_bad, dsum, dn = 0.0, 0, 0.0, 0
+    for t in range(len(sub)):
+        i = int(sub[t])
+        if not (row_begin <= i < row_end):
+            continue
+        idx = i * (i + 1) // 2 + sub[:t + 1] - base
+        dA_max = max(dA_max, float(np.abs(A_band[idx].astype(np.float64) - Aref[t, :t + 1]).max()))
+        n_bad += int((N_band[idx] != np.rint(Nref[t, :t + 1]).astype(np.int32)).sum())
+        dsum += float(A_band[idx[-1]]) - Aref[t, t]
+        dn += 1
+    return dA_max, n_bad, dsum, dn
+
+
 def job_throughput(ranks: Ranks, n: int, m: int, steps: int, device_ms_this_rank: float) -> float:
     """Whole-job pair*SNP/s: all pairs of the triangle x SNPs x steps over the slowest rank's device time."""
     t = ranks.max(device_ms_this_rank) * 1e-3
