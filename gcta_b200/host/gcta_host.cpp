@@ -119,11 +119,15 @@ void gcta_host::read_bedfile(const string& bedfile)
     if (_include.empty()) throw("Error: No SNP is retained for analysis.");          // data.cpp:149
     if (_keep.empty()) throw("Error: No individual is retained for analysis.");      // data.cpp:150
     // a SNP / individual is read iff it is still in the name maps (get_rsnp / get_rindi, data.cpp:196-214)
-    vector<char> rsnp(_snp_num, 0);
-    for (int j = 0; j < _snp_num; j++) rsnp[j] = _snp_name_map.find(_snp_name[j]) != _snp_name_map.end();
+    // (a map as large as the file means no filter has removed anything and no name repeats: every look-up would succeed -
+    // a million string searches saved on the headline .bim)
+    vector<char> rsnp(_snp_num, 1);
+    if ((int64_t)_snp_name_map.size() != (int64_t)_snp_num)
+        for (int j = 0; j < _snp_num; j++) rsnp[j] = _snp_name_map.find(_snp_name[j]) != _snp_name_map.end();
     vector<int> keep;
+    const bool all_indi = (int64_t)_id_map.size() == (int64_t)_indi_num;
     for (int i = 0; i < _indi_num; i++)
-        if (_id_map.find(_fid[i] + ":" + _pid[i]) != _id_map.end()) keep.push_back(i);
+        if (all_indi || _id_map.find(_fid[i] + ":" + _pid[i]) != _id_map.end()) keep.push_back(i);
     const int fd = open(bedfile.c_str(), O_RDONLY);
     if (fd < 0) throw("Error: can not open the file [" + bedfile + "] to read.");
     cout << "Reading PLINK BED file from [" + bedfile + "] in SNP-major format ..." << endl;
@@ -174,7 +178,10 @@ void gcta_host::read_bedfile(const string& bedfile)
     _keep = keep;
     cout << "Genotype data for " << _keep.size() << " individuals and " << m_read << " SNPs to be included from [" + bedfile + "]." << endl;
 
-    // update_bim (data.cpp:216-245): SNP tables shrink to the rows that were read and are renumbered
+    // update_bim (data.cpp:216-245): SNP tables shrink to the rows that were read and are renumbered.  Every row read
+    // and the name map complete (see above): the tables, _include and the map already are what update_bim + init_include
+    // would rebuild - a million string copies and map insertions saved.
+    if (m_read == _snp_num && (int64_t)_snp_name_map.size() == (int64_t)_snp_num && (int64_t)_include.size() == (int64_t)_snp_num) return;
     vector<int> chr, bp;
     vector<char> a1, a2, ra;
     vector<string> nm;
