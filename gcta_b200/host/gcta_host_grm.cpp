@@ -17,6 +17,7 @@
 #include "../../include/gcta_b200.h"
 #include "gcta_host.h"
 #include "grm_bin_writer.h"
+#include "gz_member_writer.h"
 #include "grm_text_gz.h"
 
 using std::cout;
@@ -324,7 +325,7 @@ int gcta_host_selftest_gz()
     };
     const float specials[] = {0.0f, -0.0f, 1.0f, -1.0f, NAN, INFINITY, -INFINITY, 1e30f, -1e-30f, 1.17549435e-38f, 1e-45f, 3.4028235e38f, 9.9999995e-1f, 0.5f};
     const int32_t nspecial[] = {0, 1, -1, 9, 10, 99, 100, 2147483647, -2147483647 - 1, 1000000, 999999};
-    for (int64_t n : {1, 2, 3, 17, 60, 300}) {
+    for (int64_t n : {1, 2, 3, 17, 60, 300, 1500}) {
         const size_t tri = (size_t)(n * (n + 1) / 2);
         vector<float> A(tri);
         vector<int32_t> N(tri);
@@ -335,6 +336,16 @@ int gcta_host_selftest_gz()
         for (size_t o = 0; o < tri; o++) { A[o] = (float)((double)(int64_t)(next() % 2000001 - 1000000) * 1e-9); N[o] = 500000 - (int32_t)(next() % 3); }
         run("grm-like", A, N, 0, n);
         if (n >= 17) { run("mid-triangle", A, N, n / 2, n / 2 + 1); run("tail", A, N, n - 3, n); run("empty", A, N, 5, 5); }
+    }
+    {   // i and j passing 9,999 -> 10,000; values with and without sign, N constant, then changing in width
+        const int64_t n = 10050, r0 = 9995, r1 = 10005;
+        const size_t tri = (size_t)(n * (n + 1) / 2);
+        vector<float> A(tri, 0.0f);
+        vector<int32_t> N(tri, 1000000);
+        for (size_t o = (size_t)(r0 * (r0 + 1) / 2); o < (size_t)(r1 * (r1 + 1) / 2); o++) A[o] = (float)((double)(int64_t)(next() % 2000001 - 1000000) * 1.7e-9);
+        run("five-digit indices", A, N, r0, r1);
+        for (size_t o = (size_t)(r0 * (r0 + 1) / 2); o < (size_t)(r1 * (r1 + 1) / 2); o++) N[o] = 100005 - (int32_t)(next() % 10);
+        run("five-digit indices, N 99,996 .. 100,005", A, N, r0, r1);
     }
     printf("gz selftest: %d cases, %d failures\n", cases, bad);
     return bad ? 1 : 0;
@@ -385,10 +396,12 @@ void gcta_host::output_grm(const float* A, const int32_t* N, bool output_bin)
         // concatenated gzip members compressed in parallel; gzread - hence the reference's own reader
         // (read_grm_gz, grm.cpp:381) - decodes a multi-member file transparently.
         grm_file = _out + ".grm.gz";
-        FILE* f = fopen(grm_file.c_str(), "wb");
-        if (!f) throw("Error: can not open the file [" + grm_file + "] to write.");
+        {   // the reference opens the file before it prints the line below (grm.cpp:322-325)
+            FILE* f = fopen(grm_file.c_str(), "wb");
+            if (!f) throw("Error: can not open the file [" + grm_file + "] to write.");
+            fclose(f);
+        }
         cout << "Saving the genetic relationship matrix to the file [" + grm_file + "] (in compressed text format)." << endl;
-        const int T = (int)std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
         const int64_t lines_per_block = 1 << 20;
         vector<std::pair<int64_t, int64_t>> blocks;   // row ranges of ~1M lines
         for (int64_t i0 = 0; i0 < n;) {
@@ -397,72 +410,22 @@ void gcta_host::output_grm(const float* A, const int32_t* N, bool output_bin)
             blocks.emplace_back(i0, i1);
             i0 = i1;
         }
-        // T workers take blocks off a shared counter and compress them; this thread writes the members in order as
-        // they complete, so compression, formatting and file I/O overlap.  At most `window` blocks are in flight.
+        // Blocks are formatted, compressed and written by a pool of threads (gz_member_writer.h).
         // Default codec: the structure-aware encoder of grm_text_gz.cpp; GCTA_B200_GZ_LEVEL=<0..9> formats the text and
         // runs zlib's deflate at that level instead (6 = what the reference's gzopen(name, "w") uses).
         const bool use_zlib = getenv("GCTA_B200_GZ_LEVEL") != nullptr;
-        const size_t nb = blocks.size(), window = (size_t)(2 * T);
-        vector<string> gz(nb);
-        vector<char> done(nb, 0);
-        string first_error;
-        std::mutex mu;
-        std::condition_variable cv_done, cv_room;
-        size_t next_block = 0, next_write = 0;
-        vector<std::thread> th;
-        for (int t = 0; t < T && (size_t)t < nb; t++)
-            th.emplace_back([&]() {
-                for (;;) {
-                    size_t b;
-                    {
-                        std::unique_lock<std::mutex> lk(mu);
-                        cv_room.wait(lk, [&] { return next_block >= nb || next_block < next_write + window || !first_error.empty(); });
-                        if (next_block >= nb || !first_error.empty()) return;
-                        b = next_block++;
-                    }
-                    string member, err;
-                    try {
-                        if (use_zlib) {
-                            string text;
-                            grm_text_gz::format_rows(A, N, blocks[b].first, blocks[b].second, text);
-                            gz_member(text, member);
-                        } else
-                            grm_text_gz::encode_rows(A, N, blocks[b].first, blocks[b].second, member);
-                    } catch (const string& e) { err = e; }
-                    catch (const std::exception& e) { err = string("Error: ") + e.what(); }
-                    {
-                        std::lock_guard<std::mutex> lk(mu);
-                        gz[b].swap(member);
-                        done[b] = 1;
-                        if (!err.empty() && first_error.empty()) first_error = err;
-                    }
-                    cv_done.notify_all();
-                    if (!err.empty()) { cv_room.notify_all(); return; }
-                }
-            });
-        bool write_failed = false;
-        for (; next_write < nb;) {
-            string member;
-            {
-                std::unique_lock<std::mutex> lk(mu);
-                cv_done.wait(lk, [&] { return done[next_write] || !first_error.empty(); });
-                if (!first_error.empty()) break;
-                member.swap(gz[next_write]);
-                next_write++;
-            }
-            cv_room.notify_all();
-            if (fwrite(member.data(), 1, member.size(), f) != member.size()) {
-                std::lock_guard<std::mutex> lk(mu);
-                write_failed = true;
-                first_error = "Error: can not write to the file [" + grm_file + "].";
-                break;
-            }
-        }
-        cv_room.notify_all();
-        for (auto& t : th) t.join();
-        fclose(f);
-        if (!first_error.empty()) throw first_error;
-        (void)write_failed;
+        const string err = write_gz_members(
+            grm_file, blocks.size(),
+            [&](size_t b, string& member) {
+                if (use_zlib) {
+                    string text;
+                    grm_text_gz::format_rows(A, N, blocks[b].first, blocks[b].second, text);
+                    gz_member(text, member);
+                } else
+                    grm_text_gz::encode_rows(A, N, blocks[b].first, blocks[b].second, member);
+            },
+            "Error: can not open the file [" + grm_file + "] to write.", "Error: can not write to the file [" + grm_file + "].");
+        if (!err.empty()) throw err;
         cout << "The genetic relationship matrix has been saved in the file [" + grm_file + "] (in compressed text format)." << endl;
     }
     const string famfile = _out + ".grm.id";
@@ -486,6 +449,7 @@ int gcta_host::selftest_writer(int64_t n, bool output_bin)
     vector<int32_t> N(tri);
     uint64_t s = 0x9E3779B97F4A7C15ull;
     auto next = [&]() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return s; };
+    const bool const_n = getenv("GCTA_B200_SELFTEST_CONST_N") != nullptr;   // no missing genotypes: N = M everywhere
     size_t o = 0;
     for (int64_t i = 0; i < n; i++)
         for (int64_t j = 0; j <= i; j++, o++) {
@@ -493,7 +457,7 @@ int gcta_host::selftest_writer(int64_t n, bool output_bin)
             // sum of four uniforms, centred: close enough to a normal for the digit statistics
             const double u = ((double)(r & 0xFFFF) + (double)((r >> 16) & 0xFFFF) + (double)((r >> 32) & 0xFFFF) + (double)(r >> 48)) / 65536.0 - 2.0;
             A[o] = (float)(i == j ? 1.0 + 0.02 * u : 1.7e-3 * u);
-            N[o] = 500000 - (int32_t)(next() % 20000);
+            N[o] = const_n ? 1000000 : 500000 - (int32_t)(next() % 20000);
         }
     const auto t0 = std::chrono::steady_clock::now();
     output_grm(A.data(), N.data(), output_bin);

@@ -23,6 +23,7 @@
 
 #include "gcta_host.h"
 #include "grm_bin_writer.h"
+#include "gz_member_writer.h"
 #include "grm_text_gz.h"
 
 using std::cout;
@@ -558,10 +559,13 @@ void gcta_host::output_grm_g15(bool output_grm_bin)
         cout << "GRM of " << n << " individuals has been saved in the file [" + grm_file + "] (in binary format)." << endl;
     } else {
         grm_file = _out + ".grm.gz";
-        FILE* f = fopen(grm_file.c_str(), "wb");
-        if (!f) throw("Error: can not open the file [" + grm_file + "] to write.");
+        {
+            FILE* f = fopen(grm_file.c_str(), "wb");
+            if (!f) throw("Error: can not open the file [" + grm_file + "] to write.");
+            fclose(f);
+        }
         cout << "Saving the genetic relationship matrix to the file [" + grm_file + "] (in compressed text format)." << endl;
-        // same scheme as gcta_host::output_grm: blocks of ~1M lines encoded by a pool of threads, members written in order
+        // same scheme as gcta_host::output_grm: blocks of ~1M lines encoded and written by a pool of threads
         vector<std::pair<int64_t, int64_t>> blocks;
         for (int64_t i0 = 0; i0 < n;) {
             int64_t i1 = i0, lines = 0;
@@ -569,54 +573,11 @@ void gcta_host::output_grm_g15(bool output_grm_bin)
             blocks.emplace_back(i0, i1);
             i0 = i1;
         }
-        const int T = (int)std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
-        const size_t nb = blocks.size(), window = (size_t)(2 * T);
-        vector<string> gz(nb);
-        vector<char> done(nb, 0);
-        std::mutex mu;
-        std::condition_variable cv_done, cv_room;
-        size_t next_block = 0, next_write = 0;
-        bool failed = false;
-        vector<std::thread> th;
-        for (int t = 0; t < T && (size_t)t < nb; t++)
-            th.emplace_back([&]() {
-                for (;;) {
-                    size_t b;
-                    {
-                        std::unique_lock<std::mutex> lk(mu);
-                        cv_room.wait(lk, [&] { return failed || next_block >= nb || next_block < next_write + window; });
-                        if (failed || next_block >= nb) return;
-                        b = next_block++;
-                    }
-                    string member;
-                    grm_text_gz::encode_rows_g15(_grm.data(), _grm_N.data(), blocks[b].first, blocks[b].second, member);
-                    {
-                        std::lock_guard<std::mutex> lk(mu);
-                        gz[b].swap(member);
-                        done[b] = 1;
-                    }
-                    cv_done.notify_all();
-                }
-            });
-        while (next_write < nb) {
-            string member;
-            {
-                std::unique_lock<std::mutex> lk(mu);
-                cv_done.wait(lk, [&] { return done[next_write] != 0; });
-                member.swap(gz[next_write]);
-                next_write++;
-            }
-            cv_room.notify_all();
-            if (fwrite(member.data(), 1, member.size(), f) != member.size()) {
-                std::lock_guard<std::mutex> lk(mu);
-                failed = true;
-                break;
-            }
-        }
-        cv_room.notify_all();
-        for (auto& x : th) x.join();
-        fclose(f);
-        if (failed) throw("Error: can not write to the file [" + grm_file + "].");
+        const string err = write_gz_members(
+            grm_file, blocks.size(),
+            [&](size_t b, string& member) { grm_text_gz::encode_rows_g15(_grm.data(), _grm_N.data(), blocks[b].first, blocks[b].second, member); },
+            "Error: can not open the file [" + grm_file + "] to write.", "Error: can not write to the file [" + grm_file + "].");
+        if (!err.empty()) throw err;
         cout << "The genetic relationship matrix has been saved in the file [" + grm_file + "] (in compressed text format)." << endl;
     }
     const string famfile = _out + ".grm.id";
