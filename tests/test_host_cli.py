@@ -91,6 +91,13 @@ def test_structured_gz_encoder_writes_the_same_text_as_zlib(tmp_path):
         r = run_cli(["--grm", p, "--make-grm", "--out", "re_" + p], tmp_path)
         assert r.stderr.strip() == "", r.stderr
     assert gzip.decompress(open(tmp_path / "re_a.grm.gz", "rb").read()) == gzip.decompress(open(tmp_path / "re_b.grm.gz", "rb").read())
+    # without missing genotypes N is the same on every line: the encoder then takes "\t N \t" as one run without looking
+    const = {"GCTA_B200_SELFTEST_CONST_N": "1"}
+    _selftest_writer(1100, "c", tmp_path, env=const)
+    _selftest_writer(1100, "d", tmp_path, env={**const, "GCTA_B200_GZ_LEVEL": "1"})
+    tc = gzip.decompress(open(tmp_path / "c.grm.gz", "rb").read())
+    assert tc == gzip.decompress(open(tmp_path / "d.grm.gz", "rb").read())
+    assert tc.startswith(b"1\t1\t1000000\t") and tc.count(b"\n") == 1100 * 1101 // 2
 
 
 def test_single_stream_gz_is_read_in_blocks_by_several_parsers(tmp_path):
