@@ -59,7 +59,7 @@ def build_host(force: bool = False) -> str:
     """C++ front end (same CLI as the reference for the --make-grm path), linked against the C ABI."""
     hdir = os.path.join(HERE, "host")
     srcs = [os.path.join(hdir, s) for s in HOST_SOURCES]
-    deps = srcs + [os.path.join(hdir, "gcta_host.h"), os.path.join(hdir, "grm_text_gz.h"), os.path.join(hdir, "grm_bin_writer.h"), os.path.join(hdir, "gz_member_writer.h"), os.path.join(HERE, "..", "include", "gcta_b200.h"), LIB]
+    deps = srcs + [os.path.join(hdir, "gcta_host.h"), os.path.join(hdir, "grm_text_gz.h"), os.path.join(hdir, "grm_bin_writer.h"), os.path.join(hdir, "gz_member_writer.h"), os.path.join(hdir, "big_alloc.h"), os.path.join(HERE, "..", "include", "gcta_b200.h"), LIB]
     if force or _stale(HOST_BIN, deps):
         cxx = os.environ.get("CXX", "g++")
         cmd = [cxx, "-O2", "-std=c++17", "-pthread", "-o", HOST_BIN] + srcs + \

@@ -7,21 +7,13 @@
 // device decodes the 2-bit codes itself.  All O(nM) and O(n^2 M) work happens in
 // libgcta_b200.so; this file only parses, filters index lists and writes results.
 #pragma once
+#include "big_alloc.h"
 #include <cstdint>
 #include <map>
 #include <memory>
 #include <string>
 #include <utility>
 #include <vector>
-
-// std::allocator that leaves trivially constructible elements uninitialised: the .bed payload (12.5 GB at the headline
-// size) is filled completely by the reader, zeroing it first would cost seconds
-template <typename T>
-struct default_init_allocator : std::allocator<T> {
-    template <typename U> struct rebind { typedef default_init_allocator<U> other; };
-    template <typename U> void construct(U* p) noexcept { ::new (static_cast<void*>(p)) U; }
-    template <typename U, typename... Args> void construct(U* p, Args&&... args) { ::new (static_cast<void*>(p)) U(std::forward<Args>(args)...); }
-};
 
 class gcta_host {
 public:
@@ -105,7 +97,8 @@ private:
     std::vector<char> _allele1, _allele2, _ref_A;
     std::map<std::string, int> _snp_name_map;
     // genotypes: payload rows of the SNPs read (compact SNP index), all file individuals
-    std::vector<uint8_t, default_init_allocator<uint8_t>> _bed;
+    // (12.5 GB at the headline size: huge-page backed and never zero-filled - every byte comes from the file)
+    std::vector<uint8_t, big_alloc::allocator<uint8_t>> _bed;
     int64_t _bed_stride = 0;
     std::vector<double> _mu;   // 2p in the _ref_A orientation, indexed by compact SNP id (gcta.h:273)
     bool _mu_from_file = false; // set by update_freq: only then is 2p passed down instead of recomputed

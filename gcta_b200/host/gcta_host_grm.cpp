@@ -199,8 +199,8 @@ void gcta_host::make_grm(bool grm_xchr_flag, bool output_bin, int grm_mtd)
     const size_t tri = (size_t)n * (size_t)(n + 1) / 2;
     // not value-initialised: at n = 50,000 zero-filling these 10 GB would cost seconds before the first kernel starts,
     // and every element of the band(s) is written by the library
-    std::unique_ptr<float[]> A(new float[tri]);
-    std::unique_ptr<int32_t[]> N(output_bin ? nullptr : new int32_t[tri]);   // --make-grm-bin drops N (grm.cpp:307-318)
+    big_alloc::Array<float> A(tri);
+    big_alloc::Array<int32_t> N(output_bin ? 0 : tri);   // --make-grm-bin drops N (grm.cpp:307-318)
     const int G = std::max(1, std::min(n_gpus, gcta_b200_device_count() > 0 ? gcta_b200_device_count() : 1));
     vector<gcta_b200_out> outs(G);
     const auto t_c0 = std::chrono::steady_clock::now();
